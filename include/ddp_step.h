@@ -1,0 +1,181 @@
+/*
+ * ddp_step.h — C-ABI of libddp_step.so: the B200-native data-parallel training step.
+ *
+ * This is the drop-in boundary.  Every entry point is
+ * `extern "C"`, takes plain device/host pointers, element counts and a
+ * `cudaStream_t` (passed as void*), and returns an int:
+ *      0  success
+ *     >0  a cudaError_t
+ *     <0  -(ncclResult_t) for collective errors, or DDP_EINVAL / DDP_ENOSYS
+ * No C++ exception crosses the boundary; `ddp_last_error()` gives the message
+ * of the last failing call on the calling thread.
+ *
+ * Memory: the library allocates nothing on the device.  All buffers are owned
+ * by the caller (PyTorch's caching allocator in the Python host layer).  All
+ * launches are asynchronous on the given stream and are CUDA-graph capturable.
+ *
+ * "ref:" citations point at the reference interface each entry point replaces
+ * (/root/reference = ArnauGabrielAtienza/pytorch_distributed_examples);
+ * "torch:" citations point at the installed torch the reference scripts call into.
+ */
+#ifndef DDP_STEP_H_
+#define DDP_STEP_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DDP_ABI_VERSION 1
+#define DDP_EINVAL (-1000)
+#define DDP_ENOSYS (-1001)
+
+/* ---- flat parameter arena of the MNIST CNN `Net` --------------------------
+ * ref: horovod/mnist_horovod.py:9-16 (Net.__init__), horovod_mnist_elastic.py:16-23.
+ * Eight tensors in state_dict order, each padded to a multiple of 4 floats so
+ * every tensor starts 16-byte aligned:
+ *   conv1.weight[10,1,5,5] conv1.bias[10] conv2.weight[20,10,5,5] conv2.bias[20]
+ *   fc1.weight[50,320] fc1.bias[50] fc2.weight[10,50] fc2.bias[10]
+ * The gradient bucket and optimizer state arenas use the same layout.       */
+#define DDP_NET_NUM_TENSORS 8
+#define DDP_NET_ARENA_ELEMS 21848   /* 21,840 parameters + 8 pad floats */
+#define DDP_NET_PARAM_COUNT 21840
+
+int ddp_abi_version(void);
+const char* ddp_last_error(void);
+/* Binds the calling thread to a device (cudaSetDevice).  Call once per host thread. */
+int ddp_set_device(int device);
+
+/* offsets[8], sizes[8] (unpadded element counts) of the arena tensors. */
+int ddp_net_param_layout(int64_t* offsets, int64_t* sizes);
+/* Bytes of the saved-activation workspace forward() fills and backward() reads. */
+int64_t ddp_net_workspace_bytes(int64_t batch);
+/* Bytes of scratch (per-CTA partial gradients, inter-kernel gradients, loss partials). */
+int64_t ddp_net_scratch_bytes(int64_t batch);
+
+/* ---- Net.forward  (+ F.nll_loss, + argmax for test()) ----------------------
+ * ref: horovod/mnist_horovod.py:18-25 (forward), :62 (F.nll_loss);
+ *      horovod_mnist_elastic.py:97-99 (torch.max(outputs,1) in test()).
+ * params   [DDP_NET_ARENA_ELEMS] f32 arena
+ * x        [B,1,28,28] f32, 16-byte aligned
+ * target   [B] i64 or NULL (needed for out_loss / out_correct)
+ * mask2d   [B,20] f32 in {0,1} or NULL: Dropout2d keep mask (injected for parity)
+ * mask1d   [B,50] f32 in {0,1} or NULL: F.dropout keep mask
+ *          With training!=0 and a NULL mask the kernel draws the mask from
+ *          Philox4x32-10 keyed (seed, offset, element).  training==0: no dropout.
+ * offset_dev [1] i64 or NULL: added to `offset` on the device, so a captured CUDA graph draws
+ *          fresh masks on every replay (point it at the optimizer's device step counter).
+ * workspace  ddp_net_workspace_bytes(B), always required (activations between kernels)
+ * out_logp [B,10] f32 log-probabilities (the tensor Net.forward returns)
+ * out_loss [1] f32 mean NLL or NULL;  out_argmax [B] i64 or NULL
+ * out_correct [1] i64 or NULL: += number of argmax==target (integer atomics)
+ * scratch  ddp_net_scratch_bytes(B); required when out_loss != NULL           */
+int ddp_net_forward(const float* params, const float* x, const int64_t* target,
+                    const float* mask2d, const float* mask1d,
+                    uint64_t seed, uint64_t offset, const int64_t* offset_dev,
+                    int training, int64_t batch,
+                    void* workspace, float* out_logp, float* out_loss,
+                    int64_t* out_argmax, int64_t* out_correct, void* scratch,
+                    void* stream);
+
+/* ---- loss.backward() through Net ------------------------------------------
+ * ref: horovod/mnist_horovod.py:63 ; horovod_mnist_elastic.py:68.
+ * dlogp [B,10] f32 = dL/d(log-probs) from autograd, or NULL: then the kernel
+ * uses the F.nll_loss(mean) gradient  dlogp[b,c] = -loss_scale/B * [c==target[b]].
+ * Writes all 8 gradients into grad_bucket[DDP_NET_ARENA_ELEMS] (overwrite, so
+ * optimizer.zero_grad() — ref :60 — costs nothing).  Deterministic: per-CTA
+ * partial sums in scratch, reduced in fixed order; no float atomics.           */
+int ddp_net_backward(const float* params, const float* x, const float* logp,
+                     const float* dlogp, const int64_t* target, float loss_scale,
+                     int training, int64_t batch, const void* workspace,
+                     void* scratch, float* grad_bucket, void* stream);
+
+/* ---- flatten-into-bucket (DDP Reducer copy / Horovod fusion buffer) ---------
+ * torch: nn/parallel/distributed.py:1255-1280 (Reducer buckets);
+ * ref: pytorch_elastic/mnist_ddp_elastic.py:58 (DDP wrap), horovod/mnist_horovod.py:53.
+ * A byte-granular gather/scatter: item i copies nbytes[i] between tensor
+ * ptrs[i] and bucket + offsets[i].  The three tables live in DEVICE memory
+ * (built once per bucket layout).  chunk_item/chunk_start map each CTA to a
+ * (item, byte start) so large and small tensors balance.  direction 0 =
+ * tensors -> bucket (flatten), 1 = bucket -> tensors (unflatten).             */
+#define DDP_BUCKET_CHUNK_BYTES 16384
+int ddp_bucket_copy(const uint64_t* ptrs, const int64_t* offsets, const int64_t* nbytes,
+                    const int32_t* chunk_item, const int64_t* chunk_start, int64_t nchunks,
+                    void* bucket, int direction, void* stream);
+
+/* ---- fused (1/N)*g + optimizer update, in place -----------------------------
+ * ref: horovod/mnist_horovod.py:50,64 (SGD lr=.01 + step);
+ *      horovod_mnist_elastic.py:41,69 (AdamW); pytorch_elastic/mnist_ddp_elastic.py:173 (Adam).
+ * torch: optim/sgd.py:343-380, optim/adam.py:414-547, optim/adadelta.py.
+ * One pass over n elements: g = grad[i]*inv_world (+ weight decay), then the
+ * update of kind `opt`.  state1/state2: momentum_buffer | exp_avg,exp_avg_sq |
+ * square_avg,acc_delta (NULL when unused).  grad_dtype 0 = f32, 1 = bf16
+ * (params and state are always f32 master copies).
+ * step: 1-based step count used for Adam bias correction / SGD first-step
+ * momentum; if step_dev != NULL the kernel instead reads *step_dev + 1 from
+ * the device (use ddp_step_increment after it) so a captured CUDA graph can be
+ * replayed without re-baking the step.                                        */
+enum { DDP_OPT_SGD = 0, DDP_OPT_ADAM = 1, DDP_OPT_ADAMW = 2, DDP_OPT_ADADELTA = 3 };
+typedef struct {
+  /* doubles, like the Python floats torch.optim holds; derived constants
+   * (1-beta1, lr/(1-beta1^t), ...) are formed in double and rounded once. */
+  double lr, momentum, dampening, weight_decay;
+  double beta1, beta2, eps, rho;
+  int nesterov;
+  int write_back_grad; /* 1: store the averaged gradient back into grad (f32 only) */
+} ddp_hyper_t;
+int ddp_fused_update(int opt, const void* grad, int grad_dtype, float* params,
+                     float* state1, float* state2, int64_t n, float inv_world,
+                     const ddp_hyper_t* hyper, int64_t step, const int64_t* step_dev,
+                     void* stream);
+int ddp_step_increment(int64_t* step_dev, void* stream);
+/* Scale a bucket in place: buf[i] *= s (the DDP allreduce hook's 1/N). */
+int ddp_scale(void* buf, int dtype, int64_t n, float s, void* stream);
+
+/* ---- DistributedSampler shard indices (bit-exact) ---------------------------
+ * ref: horovod/mnist_horovod.py:41-42 ; pytorch_elastic/mnist_ddp_elastic.py:188,89.
+ * torch: utils/data/distributed.py:102-134 (g=mt19937(seed+epoch); randperm;
+ * pad by wrap-around to ceil(N/W)*W, or truncate when drop_last; take [rank::W]).
+ * perm_scratch: device buffer of n int32 (the whole permutation).
+ * out: [num_samples] i64, num_samples = ddp_sampler_num_samples(...).          */
+int64_t ddp_sampler_num_samples(int64_t n, int world, int drop_last);
+int ddp_sampler_indices(int64_t n, int world, int rank, int shuffle, uint64_t seed,
+                        uint64_t epoch, int drop_last, int32_t* perm_scratch,
+                        int64_t* out, void* stream);
+
+/* ---- on-device synthetic 28x28 batch ----------------------------------------
+ * replaces ref: horovod/mnist_horovod.py:34-38 (datasets.MNIST + ToTensor + Normalize),
+ * which needs a network download.  Sample i of the virtual dataset: pixels u8 ~
+ * Philox4x32-10(key=seed, counter=(i, block)), x=(u8/255-0.1307)/0.3081; label =
+ * philox % 10.  indices [B] i64 (dataset indices from the sampler) or NULL for
+ * base_index + b.                                                             */
+int ddp_synth_batch(uint64_t seed, const int64_t* indices, int64_t base_index,
+                    int64_t batch, float* out_x, int64_t* out_y, void* stream);
+
+/* ---- collectives over NCCL / NVLink -----------------------------------------
+ * ref: pytorch_elastic/mnist_ddp_elastic.py:26,58 (gloo process group + DDP allreduce);
+ *      horovod/mnist_horovod.py:28,53,56 (hvd.init, allreduce, broadcast_parameters).
+ * uid: 128 bytes (ncclUniqueId) created on rank 0 and distributed by the host
+ * layer through the torchrun TCP store.  One communicator per elastic generation. */
+#define DDP_UID_BYTES 128
+int ddp_comm_unique_id(void* uid_out);
+int ddp_comm_init(void** comm_out, const void* uid, int world, int rank);
+int ddp_comm_destroy(void* comm);
+int ddp_comm_abort(void* comm);
+/* dtype 0 = f32, 1 = bf16, 2 = i64, 3 = u8 */
+int ddp_allreduce_sum(void* comm, void* buf, int64_t count, int dtype, void* stream);
+int ddp_allreduce_max(void* comm, void* buf, int64_t count, int dtype, void* stream);
+int ddp_broadcast(void* comm, void* buf, int64_t nbytes, int root, void* stream);
+
+/* ---- elastic state snapshot -------------------------------------------------
+ * ref: horovod_mnist_elastic.py:71-72 (state.commit), :104 (TorchState);
+ *      pytorch_elastic/mnist_ddp_elastic.py:95-104 (snapshot.pt).
+ * Async copies between a device arena and caller-owned pinned host memory.    */
+int ddp_state_snapshot(const void* device_arena, void* pinned_host, int64_t nbytes, void* stream);
+int ddp_state_restore(void* device_arena, const void* pinned_host, int64_t nbytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DDP_STEP_H_ */

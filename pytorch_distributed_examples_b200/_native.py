@@ -1,0 +1,250 @@
+"""ctypes binding of libddp_step.so — the thin C-ABI seam (include/ddp_step.h).
+
+Every method takes torch CUDA tensors, checks them, and passes raw ``data_ptr()``s plus the current
+CUDA stream to the C entry points.  There is NO CPU fallback: a missing library or a CPU tensor raises.
+Host-logic unit tests substitute a test double through ``set_instance`` (tests/fake_native.py).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import POINTER, c_char_p, c_double, c_float, c_int, c_int32, c_int64, c_uint64, c_void_p
+
+import torch
+
+_LIB_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib")
+LIB_PATH = os.path.join(_LIB_DIR, "libddp_step.so")
+
+OPT_SGD, OPT_ADAM, OPT_ADAMW, OPT_ADADELTA = 0, 1, 2, 3
+DT_F32, DT_BF16, DT_I64, DT_U8 = 0, 1, 2, 3
+ARENA_ELEMS = 21848
+PARAM_COUNT = 21840
+UID_BYTES = 128
+BUCKET_CHUNK_BYTES = 16384
+
+
+class Hyper(ctypes.Structure):
+    _fields_ = [("lr", c_double), ("momentum", c_double), ("dampening", c_double), ("weight_decay", c_double),
+                ("beta1", c_double), ("beta2", c_double), ("eps", c_double), ("rho", c_double),
+                ("nesterov", c_int), ("write_back_grad", c_int)]
+
+
+# name -> (restype, argtypes); also the list of symbols the not-gpu test checks against include/ddp_step.h
+SIGNATURES = {
+    "ddp_abi_version": (c_int, []),
+    "ddp_last_error": (c_char_p, []),
+    "ddp_set_device": (c_int, [c_int]),
+    "ddp_net_param_layout": (c_int, [POINTER(c_int64), POINTER(c_int64)]),
+    "ddp_net_workspace_bytes": (c_int64, [c_int64]),
+    "ddp_net_scratch_bytes": (c_int64, [c_int64]),
+    "ddp_net_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_uint64, c_uint64, c_void_p, c_int,
+                                c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "ddp_net_backward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_int, c_int64,
+                                 c_void_p, c_void_p, c_void_p, c_void_p]),
+    "ddp_bucket_copy": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int,
+                                c_void_p]),
+    "ddp_fused_update": (c_int, [c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int64, c_float,
+                                 POINTER(Hyper), c_int64, c_void_p, c_void_p]),
+    "ddp_step_increment": (c_int, [c_void_p, c_void_p]),
+    "ddp_scale": (c_int, [c_void_p, c_int, c_int64, c_float, c_void_p]),
+    "ddp_sampler_num_samples": (c_int64, [c_int64, c_int, c_int]),
+    "ddp_sampler_indices": (c_int, [c_int64, c_int, c_int, c_int, c_uint64, c_uint64, c_int, c_void_p, c_void_p,
+                                    c_void_p]),
+    "ddp_synth_batch": (c_int, [c_uint64, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
+    "ddp_comm_unique_id": (c_int, [c_void_p]),
+    "ddp_comm_init": (c_int, [POINTER(c_void_p), c_void_p, c_int, c_int]),
+    "ddp_comm_destroy": (c_int, [c_void_p]),
+    "ddp_comm_abort": (c_int, [c_void_p]),
+    "ddp_allreduce_sum": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p]),
+    "ddp_allreduce_max": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p]),
+    "ddp_broadcast": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p]),
+    "ddp_state_snapshot": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
+    "ddp_state_restore": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
+}
+
+_DTYPES = {torch.float32: DT_F32, torch.bfloat16: DT_BF16, torch.int64: DT_I64, torch.uint8: DT_U8}
+
+
+def load_library(path: str = LIB_PATH) -> ctypes.CDLL:
+    if not os.path.exists(path):
+        raise RuntimeError(
+            f"libddp_step.so not found at {path}: build it with `python -c 'import __graft_entry__ as g; g.build()'`"
+            " — this package has no CPU or PyTorch fallback for its CUDA path")
+    lib = ctypes.CDLL(path)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    return lib
+
+
+def _ptr(t, name="tensor", dtype=None):
+    if t is None:
+        return None
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor (this path has no CPU fallback)")
+    if not t.is_contiguous():
+        raise RuntimeError(f"{name} must be contiguous")
+    if dtype is not None and t.dtype != dtype:
+        raise RuntimeError(f"{name} must be {dtype}, got {t.dtype}")
+    return t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+class Native:
+    """Tensor-level façade over the C-ABI.  One instance per process."""
+
+    def __init__(self, lib: ctypes.CDLL | None = None):
+        self.lib = lib or load_library()
+        if self.lib.ddp_abi_version() != 1:
+            raise RuntimeError("libddp_step.so ABI version mismatch")
+        self._dev_bound = set()
+
+    # -- plumbing ---------------------------------------------------------------------------------
+    def _check(self, rc: int, what: str):
+        if rc != 0:
+            msg = self.lib.ddp_last_error()
+            raise RuntimeError(f"{what} failed (rc={rc}): {msg.decode() if msg else ''}")
+
+    def bind_device(self, device: int):
+        self._check(self.lib.ddp_set_device(int(device)), "ddp_set_device")
+
+    def param_layout(self):
+        off = (c_int64 * 8)()
+        sz = (c_int64 * 8)()
+        self._check(self.lib.ddp_net_param_layout(off, sz), "ddp_net_param_layout")
+        return list(off), list(sz)
+
+    def workspace_bytes(self, batch: int) -> int:
+        return int(self.lib.ddp_net_workspace_bytes(batch))
+
+    def scratch_bytes(self, batch: int) -> int:
+        return int(self.lib.ddp_net_scratch_bytes(batch))
+
+    # -- Net ----------------------------------------------------------------------------------------
+    def net_forward(self, params, x, target, mask2d, mask1d, seed, offset, training, workspace, out_logp,
+                    out_loss=None, out_argmax=None, out_correct=None, scratch=None, offset_dev=None):
+        batch = x.shape[0]
+        rc = self.lib.ddp_net_forward(
+            _ptr(params, "params", torch.float32), _ptr(x, "x", torch.float32), _ptr(target, "target", torch.int64),
+            _ptr(mask2d, "mask2d", torch.float32), _ptr(mask1d, "mask1d", torch.float32),
+            int(seed) & (2 ** 64 - 1), int(offset) & (2 ** 64 - 1), _ptr(offset_dev, "offset_dev", torch.int64),
+            int(bool(training)), batch, _ptr(workspace, "workspace"), _ptr(out_logp, "out_logp", torch.float32),
+            _ptr(out_loss, "out_loss", torch.float32), _ptr(out_argmax, "out_argmax", torch.int64),
+            _ptr(out_correct, "out_correct", torch.int64), _ptr(scratch, "scratch"), _stream())
+        self._check(rc, "ddp_net_forward")
+
+    def net_backward(self, params, x, logp, dlogp, target, loss_scale, training, workspace, scratch, grad_bucket):
+        rc = self.lib.ddp_net_backward(
+            _ptr(params, "params", torch.float32), _ptr(x, "x", torch.float32), _ptr(logp, "logp", torch.float32),
+            _ptr(dlogp, "dlogp", torch.float32), _ptr(target, "target", torch.int64), float(loss_scale),
+            int(bool(training)), x.shape[0], _ptr(workspace, "workspace"), _ptr(scratch, "scratch"),
+            _ptr(grad_bucket, "grad_bucket", torch.float32), _stream())
+        self._check(rc, "ddp_net_backward")
+
+    # -- bucket -------------------------------------------------------------------------------------
+    def bucket_copy(self, table, bucket, direction: int):
+        """table: BucketTable (device tensors built once per layout, see bucket.py)."""
+        rc = self.lib.ddp_bucket_copy(_ptr(table.ptrs), _ptr(table.offsets), _ptr(table.nbytes),
+                                      _ptr(table.chunk_item), _ptr(table.chunk_start), table.nchunks,
+                                      _ptr(bucket, "bucket"), direction, _stream())
+        self._check(rc, "ddp_bucket_copy")
+
+    # -- optimizer ----------------------------------------------------------------------------------
+    def fused_update(self, opt, grad, params, state1, state2, n, inv_world, hyper: Hyper, step=1, step_dev=None):
+        gd = _DTYPES.get(grad.dtype)
+        if gd not in (DT_F32, DT_BF16):
+            raise RuntimeError(f"unsupported gradient dtype {grad.dtype}")
+        rc = self.lib.ddp_fused_update(opt, _ptr(grad, "grad"), gd, _ptr(params, "params", torch.float32),
+                                       _ptr(state1, "state1", torch.float32), _ptr(state2, "state2", torch.float32),
+                                       int(n), float(inv_world), ctypes.byref(hyper), int(step),
+                                       _ptr(step_dev, "step_dev", torch.int64), _stream())
+        self._check(rc, "ddp_fused_update")
+
+    def step_increment(self, step_dev):
+        self._check(self.lib.ddp_step_increment(_ptr(step_dev, "step_dev", torch.int64), _stream()),
+                    "ddp_step_increment")
+
+    def scale(self, buf, s: float):
+        self._check(self.lib.ddp_scale(_ptr(buf, "buf"), _DTYPES[buf.dtype], buf.numel(), float(s), _stream()),
+                    "ddp_scale")
+
+    # -- sampler / data -----------------------------------------------------------------------------
+    def sampler_num_samples(self, n, world, drop_last) -> int:
+        return int(self.lib.ddp_sampler_num_samples(n, world, int(bool(drop_last))))
+
+    def sampler_indices(self, n, world, rank, shuffle, seed, epoch, drop_last, perm_scratch, out):
+        rc = self.lib.ddp_sampler_indices(n, world, rank, int(bool(shuffle)), int(seed) & (2 ** 64 - 1),
+                                          int(epoch) & (2 ** 64 - 1), int(bool(drop_last)),
+                                          _ptr(perm_scratch, "perm_scratch", torch.int32),
+                                          _ptr(out, "out", torch.int64), _stream())
+        self._check(rc, "ddp_sampler_indices")
+
+    def synth_batch(self, seed, indices, base_index, batch, out_x, out_y):
+        rc = self.lib.ddp_synth_batch(int(seed) & (2 ** 64 - 1), _ptr(indices, "indices", torch.int64),
+                                      int(base_index), int(batch), _ptr(out_x, "out_x", torch.float32),
+                                      _ptr(out_y, "out_y", torch.int64), _stream())
+        self._check(rc, "ddp_synth_batch")
+
+    # -- collectives --------------------------------------------------------------------------------
+    def comm_unique_id(self) -> bytes:
+        buf = ctypes.create_string_buffer(UID_BYTES)
+        self._check(self.lib.ddp_comm_unique_id(buf), "ddp_comm_unique_id")
+        return buf.raw
+
+    def comm_init(self, uid: bytes, world: int, rank: int):
+        handle = c_void_p()
+        buf = ctypes.create_string_buffer(uid, UID_BYTES)
+        self._check(self.lib.ddp_comm_init(ctypes.byref(handle), buf, world, rank), "ddp_comm_init")
+        return handle
+
+    def comm_destroy(self, comm):
+        self._check(self.lib.ddp_comm_destroy(comm), "ddp_comm_destroy")
+
+    def comm_abort(self, comm):
+        self._check(self.lib.ddp_comm_abort(comm), "ddp_comm_abort")
+
+    def allreduce_sum(self, comm, buf):
+        self._check(self.lib.ddp_allreduce_sum(comm, _ptr(buf, "buf"), buf.numel(), _DTYPES[buf.dtype], _stream()),
+                    "ddp_allreduce_sum")
+
+    def allreduce_max(self, comm, buf):
+        self._check(self.lib.ddp_allreduce_max(comm, _ptr(buf, "buf"), buf.numel(), _DTYPES[buf.dtype], _stream()),
+                    "ddp_allreduce_max")
+
+    def broadcast(self, comm, buf, root: int):
+        self._check(self.lib.ddp_broadcast(comm, _ptr(buf, "buf"), buf.numel() * buf.element_size(), root, _stream()),
+                    "ddp_broadcast")
+
+    # -- elastic snapshot ---------------------------------------------------------------------------
+    def state_snapshot(self, device_arena, pinned_host):
+        nbytes = device_arena.numel() * device_arena.element_size()
+        if pinned_host.is_cuda or pinned_host.numel() * pinned_host.element_size() < nbytes:
+            raise RuntimeError("pinned_host must be a host tensor at least as large as the arena")
+        self._check(self.lib.ddp_state_snapshot(_ptr(device_arena, "arena"), pinned_host.data_ptr(), nbytes,
+                                                _stream()), "ddp_state_snapshot")
+
+    def state_restore(self, device_arena, pinned_host):
+        nbytes = device_arena.numel() * device_arena.element_size()
+        self._check(self.lib.ddp_state_restore(_ptr(device_arena, "arena"), pinned_host.data_ptr(), nbytes,
+                                               _stream()), "ddp_state_restore")
+
+
+_INSTANCE = None
+
+
+def get() -> Native:
+    """The process-wide binding.  Raises if the CUDA library has not been built."""
+    global _INSTANCE
+    if _INSTANCE is None:
+        _INSTANCE = Native()
+    return _INSTANCE
+
+
+def set_instance(obj):
+    """Install a test double (host-logic unit tests only)."""
+    global _INSTANCE
+    _INSTANCE = obj

@@ -1,0 +1,92 @@
+"""Process-group plumbing for the native NCCL communicator.
+
+``torch.distributed`` is used only for rendezvous (its TCP store carries the 128-byte ncclUniqueId, small
+pickled objects and the elastic membership plan); every tensor collective on the hot path goes through the
+C-ABI (ddp_allreduce_sum / ddp_broadcast in csrc/comm.cu) on the caller's CUDA stream, so it can be captured
+in a CUDA graph together with the kernels around it.
+Replaces ref: pytorch_elastic/mnist_ddp_elastic.py:22-27 (``init_process_group("gloo")``) and ``hvd.init()``
+(ref: horovod/mnist_horovod.py:28).
+"""
+from __future__ import annotations
+
+import os
+import pickle
+
+import torch
+import torch.distributed as dist
+
+from . import _native
+
+
+def env_world():
+    """(world, rank, local_rank) from torchrun / horovodrun / mpirun environments; (1,0,0) if none."""
+    for w, r, l in (("WORLD_SIZE", "RANK", "LOCAL_RANK"), ("HOROVOD_SIZE", "HOROVOD_RANK", "HOROVOD_LOCAL_RANK"),
+                    ("OMPI_COMM_WORLD_SIZE", "OMPI_COMM_WORLD_RANK", "OMPI_COMM_WORLD_LOCAL_RANK")):
+        if w in os.environ and r in os.environ:
+            return int(os.environ[w]), int(os.environ[r]), int(os.environ.get(l, os.environ[r]))
+    return 1, 0, 0
+
+
+def default_store(world: int):
+    """The rendezvous key-value store.  Initialises torch.distributed (env://) if the script has not."""
+    if world <= 1:
+        return None
+    if not dist.is_initialized():
+        backend = "nccl" if torch.cuda.is_available() else "gloo"
+        dist.init_process_group(backend=backend)
+    return dist.distributed_c10d._get_default_store()
+
+
+class Communicator:
+    """One NCCL communicator over ``ranks`` (global ranks of the job), created through the store."""
+
+    def __init__(self, store, global_rank: int, ranks, generation="0.0"):
+        self.store = store
+        self.global_rank = global_rank
+        self.ranks = list(ranks)
+        self.world = len(self.ranks)
+        self.rank = self.ranks.index(global_rank)
+        self.generation = generation
+        self.handle = None
+        self._obj_seq = 0
+        nat = _native.get()
+        if self.world > 1:
+            key = f"ddp_step/uid/gen{generation}"
+            if self.rank == 0:
+                uid = nat.comm_unique_id()
+                store.set(key, uid)
+            else:
+                uid = bytes(store.get(key))
+            self.handle = nat.comm_init(uid, self.world, self.rank)
+
+    # -- tensor collectives (in place, on the current stream) ---------------------------------------
+    def allreduce_sum_(self, t: torch.Tensor):
+        if self.world > 1:
+            _native.get().allreduce_sum(self.handle, t)
+        return t
+
+    def allreduce_max_(self, t: torch.Tensor):
+        if self.world > 1:
+            _native.get().allreduce_max(self.handle, t)
+        return t
+
+    def broadcast_(self, t: torch.Tensor, root: int = 0):
+        if self.world > 1:
+            _native.get().broadcast(self.handle, t, root)
+        return t
+
+    # -- small host objects through the store --------------------------------------------------------
+    def broadcast_object(self, obj, root: int = 0):
+        if self.world <= 1:
+            return obj
+        self._obj_seq += 1
+        key = f"ddp_step/obj/gen{self.generation}/{self._obj_seq}"
+        if self.rank == root:
+            self.store.set(key, pickle.dumps(obj))
+            return obj
+        return pickle.loads(bytes(self.store.get(key)))
+
+    def destroy(self):
+        if self.handle is not None:
+            _native.get().comm_destroy(self.handle)
+            self.handle = None

@@ -1,0 +1,72 @@
+// Misc entry points of libddp_step.so: versioning, error text, device binding, layout
+// queries and the elastic-state snapshot copies.
+#include <stdarg.h>
+#include <stdio.h>
+#include "common.cuh"
+
+namespace ddp {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int cuda_rc(cudaError_t e, const char* what) {
+  set_error("%s: CUDA error %d: %s", what, int(e), cudaGetErrorString(e));
+  return int(e) > 0 ? int(e) : DDP_EINVAL;
+}
+
+int sm_count() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+}  // namespace ddp
+
+using namespace ddp;
+
+extern "C" int ddp_abi_version(void) { return DDP_ABI_VERSION; }
+extern "C" const char* ddp_last_error(void) { return g_err; }
+
+extern "C" int ddp_set_device(int device) {
+  DDP_CUDA(cudaSetDevice(device));
+  return 0;
+}
+
+extern "C" int ddp_net_param_layout(int64_t* offsets, int64_t* sizes) {
+  DDP_REQUIRE(offsets && sizes, "null output");
+  const int64_t off[DDP_NET_NUM_TENSORS] = {OFF_C1W, OFF_C1B, OFF_C2W, OFF_C2B, OFF_F1W, OFF_F1B, OFF_F2W, OFF_F2B};
+  const int64_t sz[DDP_NET_NUM_TENSORS] = {250, 10, 5000, 20, 16000, 50, 500, 10};
+  for (int i = 0; i < DDP_NET_NUM_TENSORS; ++i) { offsets[i] = off[i]; sizes[i] = sz[i]; }
+  return 0;
+}
+
+extern "C" int64_t ddp_net_workspace_bytes(int64_t batch) { return batch < 1 ? -1 : workspace_bytes(batch); }
+extern "C" int64_t ddp_net_scratch_bytes(int64_t batch) { return batch < 1 ? -1 : scratch_bytes(batch); }
+
+extern "C" int ddp_state_snapshot(const void* device_arena, void* pinned_host, int64_t nbytes, void* stream) {
+  DDP_REQUIRE(nbytes >= 0 && (nbytes == 0 || (device_arena && pinned_host)), "bad arguments");
+  if (nbytes == 0) return 0;
+  DDP_CUDA(cudaMemcpyAsync(pinned_host, device_arena, size_t(nbytes), cudaMemcpyDeviceToHost,
+                           static_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+extern "C" int ddp_state_restore(void* device_arena, const void* pinned_host, int64_t nbytes, void* stream) {
+  DDP_REQUIRE(nbytes >= 0 && (nbytes == 0 || (device_arena && pinned_host)), "bad arguments");
+  if (nbytes == 0) return 0;
+  DDP_CUDA(cudaMemcpyAsync(device_arena, pinned_host, size_t(nbytes), cudaMemcpyHostToDevice,
+                           static_cast<cudaStream_t>(stream)));
+  return 0;
+}

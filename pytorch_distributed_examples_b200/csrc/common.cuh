@@ -1,0 +1,125 @@
+// Shared constants and helpers for libddp_step.so (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/ddp_step.h"
+
+namespace ddp {
+
+// ---- geometry of Net (ref: horovod/mnist_horovod.py:9-25) -------------------
+constexpr int IMG = 28;
+constexpr int IMG_PIX = 784;
+constexpr int C1 = 10;        // conv1 out channels
+constexpr int P1 = 12;        // pooled conv1 side
+constexpr int A1_PER = 1440;  // 10*12*12 pooled+ReLU activations per sample
+constexpr int C2 = 20;        // conv2 out channels
+constexpr int O2 = 8;         // conv2 output side
+constexpr int A2_PER = 320;   // 20*4*4 = fc1 fan-in
+constexpr int F1 = 50;        // fc1 out
+constexpr int NC = 10;        // classes
+
+// ---- arena offsets (floats); every tensor padded to 4 floats ----------------
+constexpr int OFF_C1W = 0;      // 250
+constexpr int OFF_C1B = 252;    // 10
+constexpr int OFF_C2W = 264;    // 5000
+constexpr int OFF_C2B = 5264;   // 20
+constexpr int OFF_F1W = 5284;   // 16000
+constexpr int OFF_F1B = 21284;  // 50
+constexpr int OFF_F2W = 21336;  // 500
+constexpr int OFF_F2B = 21836;  // 10
+constexpr int P_ARENA = DDP_NET_ARENA_ELEMS;
+
+// ---- saved-activation workspace layout (bytes, all 256-aligned) -------------
+struct Workspace {
+  float* a1;      // [B,10,12,12] relu(pool(conv1))
+  uint8_t* idx1;  // [B,10,12,12] argmax in 2x2 window (0..3)
+  float* a2;      // [B,320]      relu(pool(drop2d(conv2)))
+  uint8_t* idx2;  // [B,320]
+  float* h;       // [B,50]       dropout(relu(fc1))  (= fc2 input)
+};
+__host__ __device__ inline int64_t align256(int64_t v) { return (v + 255) & ~int64_t(255); }
+inline int64_t workspace_bytes(int64_t B) {
+  return align256(B * A1_PER * 4) + align256(B * A1_PER) + align256(B * A2_PER * 4) +
+         align256(B * A2_PER) + align256(B * F1 * 4);
+}
+inline Workspace carve_workspace(void* base, int64_t B) {
+  char* p = static_cast<char*>(base);
+  Workspace w;
+  w.a1 = reinterpret_cast<float*>(p);   p += align256(B * A1_PER * 4);
+  w.idx1 = reinterpret_cast<uint8_t*>(p); p += align256(B * A1_PER);
+  w.a2 = reinterpret_cast<float*>(p);   p += align256(B * A2_PER * 4);
+  w.idx2 = reinterpret_cast<uint8_t*>(p); p += align256(B * A2_PER);
+  w.h = reinterpret_cast<float*>(p);
+  return w;
+}
+
+// ---- scratch layout -----------------------------------------------------------
+// [0,256)            : counters (u32 ticket for the loss reduction)
+// loss_part          : MAX_PARTS floats
+// partials           : MAX_PARTS x P_ARENA floats (per-CTA partial weight gradients)
+// da2                : [B,320] f32  dL/d(a2)
+// dp1                : [B,1440] f32 dL/d(pooled conv1, pre-ReLU)
+constexpr int MAX_PARTS = 296;  // 2 CTAs per SM on 148 SMs
+struct Scratch {
+  unsigned int* counters;
+  float* loss_part;
+  float* partials;
+  float* da2;
+  float* dp1;
+};
+inline int64_t scratch_bytes(int64_t B) {
+  return 256 + align256(MAX_PARTS * 4) + align256(int64_t(MAX_PARTS) * P_ARENA * 4) +
+         align256(B * A2_PER * 4) + align256(B * A1_PER * 4);
+}
+inline Scratch carve_scratch(void* base, int64_t B) {
+  char* p = static_cast<char*>(base);
+  Scratch s;
+  s.counters = reinterpret_cast<unsigned int*>(p); p += 256;
+  s.loss_part = reinterpret_cast<float*>(p); p += align256(MAX_PARTS * 4);
+  s.partials = reinterpret_cast<float*>(p);  p += align256(int64_t(MAX_PARTS) * P_ARENA * 4);
+  s.da2 = reinterpret_cast<float*>(p);       p += align256(B * A2_PER * 4);
+  s.dp1 = reinterpret_cast<float*>(p);
+  return s;
+}
+
+// ---- error plumbing -----------------------------------------------------------
+void set_error(const char* fmt, ...);
+int cuda_rc(cudaError_t e, const char* what);
+#define DDP_CUDA(call)                                   \
+  do {                                                   \
+    cudaError_t e__ = (call);                            \
+    if (e__ != cudaSuccess) return ::ddp::cuda_rc(e__, #call); \
+  } while (0)
+#define DDP_REQUIRE(cond, msg)                           \
+  do {                                                   \
+    if (!(cond)) { ::ddp::set_error("%s: %s", __func__, msg); return DDP_EINVAL; } \
+  } while (0)
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+int sm_count();
+
+// ---- Philox4x32-10 (counter-based; same constants as Random123 / curand) ------
+struct Philox4 { uint32_t x, y, z, w; };
+__host__ __device__ inline Philox4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                                 uint32_t k0, uint32_t k1) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint64_t p0 = uint64_t(M0) * c0;
+    uint64_t p1 = uint64_t(M1) * c2;
+    uint32_t hi0 = uint32_t(p0 >> 32), lo0 = uint32_t(p0);
+    uint32_t hi1 = uint32_t(p1 >> 32), lo1 = uint32_t(p1);
+    uint32_t n0 = hi1 ^ c1 ^ k0;
+    uint32_t n2 = hi0 ^ c3 ^ k1;
+    c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+    k0 += W0; k1 += W1;
+  }
+  return Philox4{c0, c1, c2, c3};
+}
+// Bernoulli(0.5) keep decision for dropout element `elem` of stream `which`.
+__device__ inline float philox_keep(uint64_t seed, uint64_t offset, uint32_t which, uint64_t elem) {
+  Philox4 r = philox4x32_10(uint32_t(elem), uint32_t(elem >> 32), uint32_t(offset), which ^ (uint32_t(offset >> 32) << 8),
+                            uint32_t(seed), uint32_t(seed >> 32));
+  return (r.x & 0x80000000u) ? 0.f : 1.f;
+}
+
+}  // namespace ddp

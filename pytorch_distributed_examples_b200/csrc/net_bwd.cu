@@ -1,0 +1,584 @@
+// Backward kernels of `Net` (autograd of ref: horovod/mnist_horovod.py:18-25,62-63):
+//   K_B3  head: log_softmax/NLL -> fc2 -> dropout/ReLU -> fc1      -> partial dW/db, da2
+//   K_B2d conv2 dgrad (through ReLU/pool/Dropout2d)                 da2 -> dp1
+//   K_B2w conv2 wgrad + bgrad                                       da2,a1 -> partials
+//   K_B1  conv1 wgrad + bgrad (through ReLU/pool)                   dp1,x -> partials
+//   K_R   fixed-order reduction of the per-CTA partials into the gradient bucket
+// Weight gradients are accumulated in registers across all samples a CTA sees and
+// written once per CTA; there are no floating-point atomics anywhere.
+#include "common.cuh"
+
+namespace ddp {
+
+// ---------------------------------------------------------------------------
+// K_B3 head backward. Tile of 32 samples per iteration, 320 threads.
+// ---------------------------------------------------------------------------
+constexpr int HT = 32;
+constexpr int HB_THREADS = 320;
+constexpr int HB_A2S = 324;   // a2 tile row stride
+constexpr int HB_DPS = 36;    // dpT row stride ([j][s])
+constexpr int HB_HS = 53;     // h tile row stride
+constexpr int HB_SMEM =
+    (F1 * A2_PER + HT * HB_A2S + F1 * HB_DPS + HT * 12 + HT * HB_HS + NC * 52) * 4;
+__global__ void __launch_bounds__(HB_THREADS, 1)
+head_bwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
+                const float* __restrict__ h, const float* __restrict__ logp,
+                const float* __restrict__ dlogp, const int64_t* __restrict__ target,
+                float nll_coef, float drop_scale, float* __restrict__ da2,
+                float* __restrict__ partials, int B) {
+  extern __shared__ __align__(16) float smem[];
+  float* w1_s = smem;                     // [50][320] natural layout
+  float* a2_s = w1_s + F1 * A2_PER;       // [32][324]
+  float* dp_s = a2_s + HT * HB_A2S;       // [50][36]  dL/d(fc1 pre-activation), transposed
+  float* dz_s = dp_s + F1 * HB_DPS;       // [32][12]
+  float* h_s = dz_s + HT * 12;            // [32][53]
+  float* w2_s = h_s + HT * HB_HS;         // [10][52]
+  const int tid = threadIdx.x;
+  for (int i = tid; i < F1 * A2_PER / 4; i += HB_THREADS)
+    reinterpret_cast<float4*>(w1_s)[i] = *reinterpret_cast<const float4*>(params + OFF_F1W + i * 4);
+  for (int i = tid; i < NC * 52; i += HB_THREADS) {
+    int c = i / 52, j = i % 52;
+    w2_s[i] = j < F1 ? params[OFF_F2W + c * F1 + j] : 0.f;
+  }
+  // persistent accumulators
+  float accW1[5][10];                      // fc1.weight rows jg*5.., cols ig*10..
+#pragma unroll
+  for (int a = 0; a < 5; ++a)
+#pragma unroll
+    for (int c = 0; c < 10; ++c) accW1[a][c] = 0.f;
+  float accW2[2] = {0.f, 0.f};             // fc2.weight element tid, tid+320
+  float accB = 0.f;                        // tid<50: fc1.bias[tid]; 64<=tid<74: fc2.bias[tid-64]
+  const int jgW = tid >> 5, igW = tid & 31;  // fc1 wgrad mapping
+  const int sgD = tid / 40, igD = tid % 40;  // fc1 dgrad mapping
+  const int ntiles = (B + HT - 1) / HT;
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int b0 = tile * HT;
+    const int nvalid = min(HT, B - b0);
+    __syncthreads();
+    for (int i = tid; i < HT * (A2_PER / 4); i += HB_THREADS) {
+      int s = i / (A2_PER / 4), k4 = i % (A2_PER / 4);
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (s < nvalid) v = *reinterpret_cast<const float4*>(a2 + size_t(b0 + s) * A2_PER + k4 * 4);
+      *reinterpret_cast<float4*>(a2_s + s * HB_A2S + k4 * 4) = v;
+    }
+    for (int i = tid; i < HT * F1; i += HB_THREADS) {
+      int s = i / F1, j = i % F1;
+      h_s[s * HB_HS + j] = s < nvalid ? h[size_t(b0) * F1 + i] : 0.f;
+    }
+    // dz = dlogp - exp(logp) * sum_c dlogp   (log_softmax backward)
+    if (tid < HT) {
+      const int s = tid;
+      float g[NC], lp[NC];
+      float sum = 0.f;
+#pragma unroll
+      for (int c = 0; c < NC; ++c) { g[c] = 0.f; lp[c] = 0.f; }
+      if (s < nvalid) {
+        const size_t o = size_t(b0 + s) * NC;
+        if (dlogp) {
+#pragma unroll
+          for (int c = 0; c < NC; ++c) g[c] = dlogp[o + c];
+        } else {
+          const int t = int(target[b0 + s]);
+#pragma unroll
+          for (int c = 0; c < NC; ++c) g[c] = (c == t) ? nll_coef : 0.f;
+        }
+#pragma unroll
+        for (int c = 0; c < NC; ++c) { lp[c] = logp[o + c]; sum += g[c]; }
+      }
+#pragma unroll
+      for (int c = 0; c < NC; ++c)
+        dz_s[s * 12 + c] = (s < nvalid) ? g[c] - expf(lp[c]) * sum : 0.f;
+    }
+    __syncthreads();
+    // dp[s][j] = relu'/dropout' * sum_c dz[s][c] * W2[c][j]
+    for (int e = tid; e < HT * F1; e += HB_THREADS) {
+      const int s = e / F1, j = e % F1;
+      float dh = 0.f;
+#pragma unroll
+      for (int c = 0; c < NC; ++c) dh = fmaf(dz_s[s * 12 + c], w2_s[c * 52 + j], dh);
+      dp_s[j * HB_DPS + s] = h_s[s * HB_HS + j] > 0.f ? dh * drop_scale : 0.f;
+    }
+    __syncthreads();
+    // fc2 weight / bias gradients and fc1 bias gradient
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const int e = tid + q * HB_THREADS;
+      if (e < NC * F1) {
+        const int c = e / F1, j = e % F1;
+        float a = accW2[q];
+        for (int s = 0; s < HT; ++s) a = fmaf(dz_s[s * 12 + c], h_s[s * HB_HS + j], a);
+        accW2[q] = a;
+      }
+    }
+    if (tid < F1) {
+      float a = accB;
+      for (int s = 0; s < HT; ++s) a += dp_s[tid * HB_DPS + s];
+      accB = a;
+    } else if (tid >= 64 && tid < 64 + NC) {
+      float a = accB;
+      for (int s = 0; s < HT; ++s) a += dz_s[s * 12 + (tid - 64)];
+      accB = a;
+    }
+    // fc1 weight gradient: dW1[j][i] += dp[s][j] * a2[s][i]
+    {
+      const float* ar = a2_s + igW * 10;
+      const float* dr = dp_s + (jgW * 5) * HB_DPS;
+#pragma unroll 2
+      for (int s = 0; s < HT; ++s) {
+        float av[10];
+#pragma unroll
+        for (int q = 0; q < 5; ++q) {
+          float2 v = *reinterpret_cast<const float2*>(ar + s * HB_A2S + 2 * q);
+          av[2 * q] = v.x; av[2 * q + 1] = v.y;
+        }
+#pragma unroll
+        for (int a = 0; a < 5; ++a) {
+          const float d = dr[a * HB_DPS + s];
+#pragma unroll
+          for (int c = 0; c < 10; ++c) accW1[a][c] = fmaf(d, av[c], accW1[a][c]);
+        }
+      }
+    }
+    // fc1 data gradient: da2[s][i] = sum_j dp[s][j] * W1[j][i]
+    {
+      float acc[4][8];
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[a][c] = 0.f;
+#pragma unroll 2
+      for (int j = 0; j < F1; ++j) {
+        float4 d = *reinterpret_cast<const float4*>(dp_s + j * HB_DPS + sgD * 4);
+        float4 wa = *reinterpret_cast<const float4*>(w1_s + j * A2_PER + igD * 4);
+        float4 wb = *reinterpret_cast<const float4*>(w1_s + j * A2_PER + 160 + igD * 4);
+        float dv[4] = {d.x, d.y, d.z, d.w};
+        float wv[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int c = 0; c < 8; ++c) acc[a][c] = fmaf(dv[a], wv[c], acc[a][c]);
+      }
+#pragma unroll
+      for (int a = 0; a < 4; ++a) {
+        const int s = sgD * 4 + a;
+        if (s < nvalid) {
+          float* o = da2 + size_t(b0 + s) * A2_PER + igD * 4;
+          *reinterpret_cast<float4*>(o) = make_float4(acc[a][0], acc[a][1], acc[a][2], acc[a][3]);
+          *reinterpret_cast<float4*>(o + 160) = make_float4(acc[a][4], acc[a][5], acc[a][6], acc[a][7]);
+        }
+      }
+    }
+  }
+  // one partial per CTA
+  float* part = partials + size_t(blockIdx.x) * P_ARENA;
+#pragma unroll
+  for (int a = 0; a < 5; ++a)
+#pragma unroll
+    for (int c = 0; c < 10; ++c)
+      part[OFF_F1W + (jgW * 5 + a) * A2_PER + igW * 10 + c] = accW1[a][c];
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int e = tid + q * HB_THREADS;
+    if (e < NC * F1) part[OFF_F2W + e] = accW2[q];
+  }
+  if (tid < F1) part[OFF_F1B + tid] = accB;
+  else if (tid >= 64 && tid < 64 + NC) part[OFF_F2B + tid - 64] = accB;
+}
+
+// ---------------------------------------------------------------------------
+// K_B2d conv2 data gradient.  One warp per sample; lane = g*16 + tile, tile =
+// 3x3 block of the 12x12 input plane, g = half of the 10 input channels.
+//   da1[ci][y][x] = sum_co sum_kh,kw dy2[co][y-kh][x-kw] * W[co][ci][kh][kw]
+// dy2 (8x8 per co, one non-zero per 2x2 pool window) is rebuilt in smem from
+// da2/a2/idx2; out-of-range taps are predicated to zero.
+// Output dp1 = da1 * (a1 > 0): gradient w.r.t. the pooled conv1 map before ReLU.
+// ---------------------------------------------------------------------------
+constexpr int D2_WARPS = 16;
+constexpr int D2_THREADS = D2_WARPS * 32;
+constexpr int D2_WS = C2 * 25 * 2 * 8;              // [co][tap][g][8]
+constexpr int D2_PER_WARP = C2 * 64 + A1_PER;       // dy2 + staged output
+constexpr int D2_SMEM = (D2_WS + D2_WARPS * D2_PER_WARP) * 4;
+__global__ void __launch_bounds__(D2_THREADS, 1)
+conv2_dgrad_kernel(const float* __restrict__ params, const float* __restrict__ da2,
+                   const float* __restrict__ a2, const uint8_t* __restrict__ idx2,
+                   const float* __restrict__ a1, float drop_scale, float* __restrict__ dp1, int B) {
+  extern __shared__ __align__(16) float smem[];
+  float* w_s = smem;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  float* dy_s = smem + D2_WS + warp * D2_PER_WARP;  // [20][8][8]
+  float* out_s = dy_s + C2 * 64;                    // [10][144]
+  for (int i = tid; i < D2_WS; i += D2_THREADS) {
+    int cc = i & 7, g = (i >> 3) & 1, ct = i >> 4;  // ct = co*25 + tap
+    int co = ct / 25, tap = ct % 25;
+    w_s[i] = cc < 5 ? params[OFF_C2W + co * 250 + (g * 5 + cc) * 25 + tap] : 0.f;
+  }
+  __syncthreads();
+  const int g = lane >> 4, tile = lane & 15, ty = tile >> 2, tx = tile & 3;
+  // validity of patch rows/cols: dy2 row = 3*ty + r - 4 must be in [0,8)
+  bool rok[7], cok[7];
+#pragma unroll
+  for (int r = 0; r < 7; ++r) {
+    int rr = 3 * ty + r - 4, cc = 3 * tx + r - 4;
+    rok[r] = rr >= 0 && rr < O2;
+    cok[r] = cc >= 0 && cc < O2;
+  }
+  const int pbase = (3 * ty - 4) * O2 + (3 * tx - 4);
+  const int total_warps = gridDim.x * D2_WARPS;
+  for (int b = blockIdx.x * D2_WARPS + warp; b < B; b += total_warps) {
+    // rebuild dy2: 320 (co,pp) entries, 10 per lane, each a 2x2 block with one non-zero
+#pragma unroll
+    for (int q = 0; q < 10; ++q) {
+      const int e = lane + 32 * q;               // = co*16 + pp
+      const size_t o = size_t(b) * A2_PER + e;
+      const float gv = a2[o] > 0.f ? da2[o] * drop_scale : 0.f;
+      const int id = idx2[o];
+      const int co = e >> 4, pp = e & 15, py = pp >> 2, px = pp & 3;
+      float* d = dy_s + co * 64 + (2 * py) * O2 + 2 * px;
+      *reinterpret_cast<float2*>(d) = make_float2(id == 0 ? gv : 0.f, id == 1 ? gv : 0.f);
+      *reinterpret_cast<float2*>(d + O2) = make_float2(id == 2 ? gv : 0.f, id == 3 ? gv : 0.f);
+    }
+    __syncwarp();
+    float acc[3][3][5];
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+#pragma unroll
+        for (int k = 0; k < 5; ++k) acc[a][c][k] = 0.f;
+#pragma unroll 1
+    for (int co = 0; co < C2; ++co) {
+      float patch[7][7];
+      const float* dp = dy_s + co * 64 + pbase;
+#pragma unroll
+      for (int r = 0; r < 7; ++r)
+#pragma unroll
+        for (int c = 0; c < 7; ++c) patch[r][c] = (rok[r] && cok[c]) ? dp[r * O2 + c] : 0.f;
+      const float* wb = w_s + (co * 25) * 16 + g * 8;
+#pragma unroll
+      for (int kh = 0; kh < 5; ++kh)
+#pragma unroll
+        for (int kw = 0; kw < 5; ++kw) {
+          float4 w0 = *reinterpret_cast<const float4*>(wb + (kh * 5 + kw) * 16);
+          float w4 = wb[(kh * 5 + kw) * 16 + 4];
+          float w[5] = {w0.x, w0.y, w0.z, w0.w, w4};
+#pragma unroll
+          for (int oy = 0; oy < 3; ++oy)
+#pragma unroll
+            for (int ox = 0; ox < 3; ++ox) {
+              float v = patch[oy - kh + 4][ox - kw + 4];
+#pragma unroll
+              for (int k = 0; k < 5; ++k) acc[oy][ox][k] = fmaf(v, w[k], acc[oy][ox][k]);
+            }
+        }
+    }
+    // stage through smem so the global store (and the a1 mask read) is coalesced
+#pragma unroll
+    for (int k = 0; k < 5; ++k)
+#pragma unroll
+      for (int oy = 0; oy < 3; ++oy)
+#pragma unroll
+        for (int ox = 0; ox < 3; ++ox)
+          out_s[(g * 5 + k) * 144 + (3 * ty + oy) * P1 + 3 * tx + ox] = acc[oy][ox][k];
+    __syncwarp();
+    const float4* a4 = reinterpret_cast<const float4*>(a1 + size_t(b) * A1_PER);
+    float4* o4 = reinterpret_cast<float4*>(dp1 + size_t(b) * A1_PER);
+    for (int i = lane; i < A1_PER / 4; i += 32) {
+      float4 v = reinterpret_cast<const float4*>(out_s)[i];
+      float4 a = a4[i];
+      v.x = a.x > 0.f ? v.x : 0.f; v.y = a.y > 0.f ? v.y : 0.f;
+      v.z = a.z > 0.f ? v.z : 0.f; v.w = a.w > 0.f ? v.w : 0.f;
+      o4[i] = v;
+    }
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------------------
+// K_B2w conv2 weight/bias gradient.  thread <-> (ci, kh, cq): accumulators for
+// co in {cq, cq+5, cq+10, cq+15} x kw 0..4; slides over the 8 output columns.
+//   dW[co][ci][kh][kw] = sum_b sum_oy,ox dy2[b][co][oy][ox] * a1[b][ci][oy+kh][ox+kw]
+// ---------------------------------------------------------------------------
+constexpr int W2_THREADS = 256;
+constexpr int W2_NS = 2;                              // samples per stage
+constexpr int W2_DYS = O2 * C2 * O2;                  // [oy][co][ox] = 1280
+__global__ void __launch_bounds__(W2_THREADS, 3)
+conv2_wgrad_kernel(const float* __restrict__ da2, const float* __restrict__ a2,
+                   const uint8_t* __restrict__ idx2, const float* __restrict__ a1,
+                   float drop_scale, float* __restrict__ partials, int B) {
+  __shared__ __align__(16) float a1_s[W2_NS * A1_PER];
+  __shared__ __align__(16) float dy_s[W2_NS * W2_DYS];
+  __shared__ float bsum_s[A2_PER];
+  const int tid = threadIdx.x;
+  const int cq = tid % 5, kh = (tid / 5) % 5, ci = tid / 25;  // ci < 10 for tid < 250
+  const bool active = tid < 250;
+  float acc[4][5];
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int k = 0; k < 5; ++k) acc[j][k] = 0.f;
+  float bacc[2] = {0.f, 0.f};  // bias-gradient share of entries tid and tid+256
+  const int nstages = (B + W2_NS - 1) / W2_NS;
+  for (int st = blockIdx.x; st < nstages; st += gridDim.x) {
+    const int b0 = st * W2_NS;
+    const int nvalid = min(W2_NS, B - b0);
+    __syncthreads();
+    const float4* src = reinterpret_cast<const float4*>(a1 + size_t(b0) * A1_PER);
+    for (int i = tid; i < nvalid * (A1_PER / 4); i += W2_THREADS)
+      reinterpret_cast<float4*>(a1_s)[i] = src[i];
+    for (int s = 0; s < nvalid; ++s) {
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const int e = tid + q * W2_THREADS;
+        if (e < A2_PER) {
+          const size_t o = size_t(b0 + s) * A2_PER + e;
+          const float gv = a2[o] > 0.f ? da2[o] * drop_scale : 0.f;
+          const int id = idx2[o];
+          const int co = e >> 4, pp = e & 15, py = pp >> 2, px = pp & 3;
+          bacc[q] += gv;
+          float* d = dy_s + s * W2_DYS + (2 * py) * (C2 * O2) + co * O2 + 2 * px;
+          *reinterpret_cast<float2*>(d) = make_float2(id == 0 ? gv : 0.f, id == 1 ? gv : 0.f);
+          *reinterpret_cast<float2*>(d + C2 * O2) = make_float2(id == 2 ? gv : 0.f, id == 3 ? gv : 0.f);
+        }
+      }
+    }
+    __syncthreads();
+    if (active) {
+      for (int s = 0; s < nvalid; ++s) {
+        const float* ab = a1_s + s * A1_PER + ci * 144 + kh * P1;
+        const float* db = dy_s + s * W2_DYS + cq * O2;
+#pragma unroll 2
+        for (int oy = 0; oy < O2; ++oy) {
+          float a[12];
+#pragma unroll
+          for (int q = 0; q < 3; ++q) {
+            float4 v = *reinterpret_cast<const float4*>(ab + oy * P1 + 4 * q);
+            a[4 * q] = v.x; a[4 * q + 1] = v.y; a[4 * q + 2] = v.z; a[4 * q + 3] = v.w;
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float* dr = db + oy * (C2 * O2) + j * 5 * O2;
+            float4 d0 = *reinterpret_cast<const float4*>(dr);
+            float4 d1 = *reinterpret_cast<const float4*>(dr + 4);
+            float d[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+#pragma unroll
+            for (int ox = 0; ox < 8; ++ox)
+#pragma unroll
+              for (int k = 0; k < 5; ++k) acc[j][k] = fmaf(d[ox], a[ox + k], acc[j][k]);
+          }
+        }
+      }
+    }
+  }
+  float* part = partials + size_t(blockIdx.x) * P_ARENA;
+  if (active) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int k = 0; k < 5; ++k)
+        part[OFF_C2W + (cq + 5 * j) * 250 + ci * 25 + kh * 5 + k] = acc[j][k];
+  }
+  __syncthreads();
+  bsum_s[tid] = bacc[0];
+  if (tid + W2_THREADS < A2_PER) bsum_s[tid + W2_THREADS] = bacc[1];
+  __syncthreads();
+  if (tid < C2) {
+    float s = 0.f;
+#pragma unroll
+    for (int p = 0; p < 16; ++p) s += bsum_s[tid * 16 + p];
+    part[OFF_C2B + tid] = s;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// K_B1 conv1 weight/bias gradient.  One sample per stage; dy1 (24x24 per channel,
+// one non-zero per pool window) rebuilt dense in smem from dp1/idx1.
+// thread <-> (c, kh, chunk of output rows); 5 accumulators (kw), sliding over ox.
+//   dW[c][kh][kw] = sum_b sum_oy,ox dy1[b][c][oy][ox] * x[b][oy+kh][ox+kw]
+// ---------------------------------------------------------------------------
+constexpr int W1_THREADS = 256;
+constexpr int W1_DYS = C1 * 576;
+__global__ void __launch_bounds__(W1_THREADS, 3)
+conv1_wgrad_kernel(const float* __restrict__ dp1, const uint8_t* __restrict__ idx1,
+                   const float* __restrict__ x, float* __restrict__ partials, int B) {
+  __shared__ __align__(16) float dy_s[W1_DYS];
+  __shared__ __align__(16) float x_s[IMG_PIX];
+  __shared__ float red_s[256 * 5];
+  const int tid = threadIdx.x;
+  const int kh = tid % 5, chunk = (tid / 5) % 5, c = tid / 25;  // c < 10 for tid < 250
+  const bool active = tid < 250;
+  const int oy0 = chunk * 5, oy1 = min(24, oy0 + 5);
+  float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+  float bacc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // entries tid + 256*q of the 1440 (c,p) cells
+  for (int b = blockIdx.x; b < B; b += gridDim.x) {
+    __syncthreads();
+    if (tid < IMG_PIX / 4)
+      reinterpret_cast<float4*>(x_s)[tid] = __ldg(reinterpret_cast<const float4*>(x + size_t(b) * IMG_PIX) + tid);
+#pragma unroll
+    for (int q = 0; q < 6; ++q) {
+      const int e = tid + q * W1_THREADS;   // = cc*144 + p
+      if (e < A1_PER) {
+        const size_t o = size_t(b) * A1_PER + e;
+        const float gv = dp1[o];
+        const int id = idx1[o];
+        const int cc = e / 144, p = e % 144, py = p / 12, px = p % 12;
+        bacc[q] += gv;
+        float* d = dy_s + cc * 576 + (2 * py) * 24 + 2 * px;
+        *reinterpret_cast<float2*>(d) = make_float2(id == 0 ? gv : 0.f, id == 1 ? gv : 0.f);
+        *reinterpret_cast<float2*>(d + 24) = make_float2(id == 2 ? gv : 0.f, id == 3 ? gv : 0.f);
+      }
+    }
+    __syncthreads();
+    if (active) {
+      for (int oy = oy0; oy < oy1; ++oy) {
+        float xr[28], d[24];
+        const float* xp = x_s + (oy + kh) * IMG;
+        const float* dp = dy_s + c * 576 + oy * 24;
+#pragma unroll
+        for (int q = 0; q < 7; ++q) {
+          float4 v = *reinterpret_cast<const float4*>(xp + 4 * q);
+          xr[4 * q] = v.x; xr[4 * q + 1] = v.y; xr[4 * q + 2] = v.z; xr[4 * q + 3] = v.w;
+        }
+#pragma unroll
+        for (int q = 0; q < 6; ++q) {
+          float4 v = *reinterpret_cast<const float4*>(dp + 4 * q);
+          d[4 * q] = v.x; d[4 * q + 1] = v.y; d[4 * q + 2] = v.z; d[4 * q + 3] = v.w;
+        }
+#pragma unroll
+        for (int ox = 0; ox < 24; ++ox)
+#pragma unroll
+          for (int k = 0; k < 5; ++k) acc[k] = fmaf(d[ox], xr[ox + k], acc[k]);
+      }
+    }
+  }
+  // combine the 5 row-chunks in fixed order
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < 5; ++k) red_s[tid * 5 + k] = acc[k];
+  __syncthreads();
+  float* part = partials + size_t(blockIdx.x) * P_ARENA;
+  if (active && chunk == 0) {
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      float s = 0.f;
+#pragma unroll
+      for (int ch = 0; ch < 5; ++ch) s += red_s[((c * 5 + ch) * 5 + kh) * 5 + k];
+      part[OFF_C1W + c * 25 + kh * 5 + k] = s;
+    }
+  }
+  // bias gradient: sum of the 144 cells of each channel (reuse dy_s as staging)
+  __syncthreads();
+#pragma unroll
+  for (int q = 0; q < 6; ++q) {
+    const int e = tid + q * W1_THREADS;
+    if (e < A1_PER) dy_s[e] = bacc[q];
+  }
+  __syncthreads();
+  if (tid < C1 * 16) {           // 16 threads per channel, 9 cells each, then fixed-order combine
+    const int cc = tid >> 4, l = tid & 15;
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) s += dy_s[cc * 144 + l * 9 + i];
+    red_s[tid] = s;
+  }
+  __syncthreads();
+  if (tid < C1) {
+    float s = 0.f;
+#pragma unroll
+    for (int l = 0; l < 16; ++l) s += red_s[tid * 16 + l];
+    part[OFF_C1B + tid] = s;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// K_R reduce per-CTA partials into the gradient bucket, fixed order.
+// 256 threads = 8 warps x 32 consecutive elements; warp w sums parts w, w+8, ...
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ bool arena_is_pad(int e) {
+  return (e >= 250 && e < OFF_C1B) || (e >= OFF_C1B + 10 && e < OFF_C2W) ||
+         (e >= OFF_F1B + 50 && e < OFF_F2W) || (e >= OFF_F2B + 10);
+}
+__global__ void __launch_bounds__(256)
+reduce_partials_kernel(const float* __restrict__ partials, int parts_c1, int parts_c2,
+                       int parts_head, float* __restrict__ bucket) {
+  __shared__ float red[8][33];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int e = blockIdx.x * 32 + lane;
+  float s = 0.f;
+  if (e < P_ARENA && !arena_is_pad(e)) {
+    const int parts = e < OFF_C2W ? parts_c1 : (e < OFF_F1W ? parts_c2 : parts_head);
+    const float* p = partials + e;
+    int i = warp;
+    for (; i + 24 < parts; i += 32) {
+      float v0 = p[size_t(i) * P_ARENA], v1 = p[size_t(i + 8) * P_ARENA];
+      float v2 = p[size_t(i + 16) * P_ARENA], v3 = p[size_t(i + 24) * P_ARENA];
+      s += v0; s += v1; s += v2; s += v3;
+    }
+    for (; i < parts; i += 8) s += p[size_t(i) * P_ARENA];
+  }
+  red[warp][lane] = s;
+  __syncthreads();
+  if (warp == 0 && e < P_ARENA) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += red[w][lane];
+    bucket[e] = t;
+  }
+}
+
+}  // namespace ddp
+
+using namespace ddp;
+
+extern "C" int ddp_net_backward(const float* params, const float* x, const float* logp,
+                                const float* dlogp, const int64_t* target, float loss_scale,
+                                int training, int64_t batch, const void* workspace, void* scratch,
+                                float* grad_bucket, void* stream_) {
+  DDP_REQUIRE(params && x && logp && workspace && scratch && grad_bucket, "null required pointer");
+  DDP_REQUIRE(dlogp || target, "either dlogp or target must be given");
+  DDP_REQUIRE(batch >= 1 && batch <= (int64_t(1) << 24), "batch out of range");
+  DDP_REQUIRE(aligned16(params) && aligned16(x) && aligned16(workspace) && aligned16(scratch),
+              "params/x/workspace/scratch must be 16-byte aligned");
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int B = int(batch);
+  const int sms = sm_count();
+  Workspace ws = carve_workspace(const_cast<void*>(workspace), batch);
+  Scratch sc = carve_scratch(scratch, batch);
+  const float drop_scale = training ? 2.f : 1.f;
+  const float nll_coef = -loss_scale / float(B);
+
+  static bool attr_done = false;
+  if (!attr_done) {
+    DDP_CUDA(cudaFuncSetAttribute(head_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HB_SMEM));
+    DDP_CUDA(cudaFuncSetAttribute(conv2_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, D2_SMEM));
+    attr_done = true;
+  }
+  int parts_head, parts_c2, parts_c1;
+  {
+    int ntiles = (B + HT - 1) / HT;
+    parts_head = ntiles < sms ? ntiles : sms;
+    head_bwd_kernel<<<parts_head, HB_THREADS, HB_SMEM, stream>>>(params, ws.a2, ws.h, logp, dlogp, target,
+                                                                 nll_coef, drop_scale, sc.da2, sc.partials, B);
+  }
+  {
+    int nblk = (B + D2_WARPS - 1) / D2_WARPS;
+    int grid = nblk < sms ? nblk : sms;
+    conv2_dgrad_kernel<<<grid, D2_THREADS, D2_SMEM, stream>>>(params, sc.da2, ws.a2, ws.idx2, ws.a1,
+                                                             drop_scale, sc.dp1, B);
+  }
+  {
+    int nstages = (B + W2_NS - 1) / W2_NS;
+    parts_c2 = nstages < MAX_PARTS ? nstages : MAX_PARTS;
+    if (parts_c2 > sms * 2) parts_c2 = sms * 2;
+    conv2_wgrad_kernel<<<parts_c2, W2_THREADS, 0, stream>>>(sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale,
+                                                           sc.partials, B);
+  }
+  {
+    parts_c1 = B < sms * 2 ? B : sms * 2;
+    if (parts_c1 > MAX_PARTS) parts_c1 = MAX_PARTS;
+    conv1_wgrad_kernel<<<parts_c1, W1_THREADS, 0, stream>>>(sc.dp1, ws.idx1, x, sc.partials, B);
+  }
+  reduce_partials_kernel<<<(P_ARENA + 31) / 32, 256, 0, stream>>>(sc.partials, parts_c1, parts_c2,
+                                                                  parts_head, grad_bucket);
+  DDP_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,409 @@
+// Forward kernels of the MNIST CNN `Net` (ref: horovod/mnist_horovod.py:18-25):
+//   K_F1  conv1(1->10,5x5)+bias -> maxpool2 -> ReLU                     x  -> a1,idx1
+//   K_F2  conv2(10->20,5x5)+bias -> Dropout2d -> maxpool2 -> ReLU       a1 -> a2,idx2
+//   K_F3  fc1+bias -> ReLU -> dropout -> fc2+bias -> log_softmax (-> NLL mean, argmax)
+// fp32 FFMA with register tiling; conv outputs before pooling never leave registers.
+#include "common.cuh"
+
+namespace ddp {
+
+// first-max over the 2x2 window in scan order (0,0),(0,1),(1,0),(1,1); matches
+// torch max_pool2d's `val > maxval` update rule, so ties keep the earliest index.
+__device__ __forceinline__ void pool4(float v0, float v1, float v2, float v3, float& best, int& bi) {
+  best = v0; bi = 0;
+  if (v1 > best) { best = v1; bi = 1; }
+  if (v2 > best) { best = v2; bi = 2; }
+  if (v3 > best) { best = v3; bi = 3; }
+}
+
+// ---------------------------------------------------------------------------
+// K_F1: one thread per pooled output position (144 per sample), all 10 channels:
+// 6x6 input patch in registers, 40 accumulators, weights broadcast from smem.
+// 288 threads = 2 samples per pass.
+// ---------------------------------------------------------------------------
+constexpr int F1_THREADS = 288;
+__global__ void __launch_bounds__(F1_THREADS, 2)
+conv1_fwd_kernel(const float* __restrict__ params, const float* __restrict__ x,
+                 float* __restrict__ a1, uint8_t* __restrict__ idx1, int B) {
+  __shared__ __align__(16) float w_s[25 * 12];   // [tap][c padded to 12]
+  __shared__ float b_s[12];
+  __shared__ __align__(16) float img[2 * IMG_PIX];
+  const int tid = threadIdx.x;
+  for (int i = tid; i < 25 * 12; i += F1_THREADS) {
+    int tap = i / 12, c = i % 12;
+    w_s[i] = c < C1 ? params[OFF_C1W + c * 25 + tap] : 0.f;
+  }
+  if (tid < 12) b_s[tid] = tid < C1 ? params[OFF_C1B + tid] : 0.f;
+  const int s = tid / 144, p = tid % 144, py = p / 12, px = p % 12;
+  const int npairs = (B + 1) >> 1;
+  for (int pair = blockIdx.x; pair < npairs; pair += gridDim.x) {
+    const int b0 = pair * 2;
+    const int nvalid = min(2, B - b0);
+    __syncthreads();
+    const float4* src = reinterpret_cast<const float4*>(x + size_t(b0) * IMG_PIX);
+    float4* dst = reinterpret_cast<float4*>(img);
+    for (int i = tid; i < nvalid * (IMG_PIX / 4); i += F1_THREADS) dst[i] = __ldg(src + i);
+    __syncthreads();
+    if (s >= nvalid) continue;
+
+    float patch[6][6];
+    const float* ip = img + s * IMG_PIX + (2 * py) * IMG + 2 * px;
+#pragma unroll
+    for (int r = 0; r < 6; ++r)
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        float2 v = *reinterpret_cast<const float2*>(ip + r * IMG + 2 * j);
+        patch[r][2 * j] = v.x; patch[r][2 * j + 1] = v.y;
+      }
+    float acc[4][C1];
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+      for (int c = 0; c < C1; ++c) acc[q][c] = b_s[c];
+#pragma unroll
+    for (int kh = 0; kh < 5; ++kh)
+#pragma unroll
+      for (int kw = 0; kw < 5; ++kw) {
+        const float4* wp = reinterpret_cast<const float4*>(w_s + (kh * 5 + kw) * 12);
+        float4 w0 = wp[0], w1 = wp[1], w2 = wp[2];
+        float w[C1] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w, w2.x, w2.y};
+#pragma unroll
+        for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+          for (int dx = 0; dx < 2; ++dx) {
+            float v = patch[dy + kh][dx + kw];
+#pragma unroll
+            for (int c = 0; c < C1; ++c) acc[dy * 2 + dx][c] = fmaf(v, w[c], acc[dy * 2 + dx][c]);
+          }
+      }
+    const size_t ob = size_t(b0 + s) * A1_PER + p;
+#pragma unroll
+    for (int c = 0; c < C1; ++c) {
+      float best; int bi;
+      pool4(acc[0][c], acc[1][c], acc[2][c], acc[3][c], best, bi);
+      a1[ob + c * 144] = fmaxf(best, 0.f);
+      idx1[ob + c * 144] = uint8_t(bi);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// K_F2: one warp per sample.  lane = g*16 + pp: pp = pooled position (4x4),
+// g = half of the 20 output channels.  Per input channel: 6x6 patch in registers,
+// 40 accumulators (4 conv positions x 10 channels), weights via LDS.128 broadcast.
+// ---------------------------------------------------------------------------
+constexpr int F2_WARPS = 8;
+constexpr int F2_THREADS = F2_WARPS * 32;
+constexpr int F2_WS = 250 * 24;  // [ci*25+tap][g][12]
+constexpr int F2_SMEM = (F2_WS + 24 + F2_WARPS * A1_PER) * 4;
+__global__ void __launch_bounds__(F2_THREADS, 2)
+conv2_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a1,
+                 const float* __restrict__ mask2d, uint64_t seed, uint64_t offset,
+                 const int64_t* __restrict__ offset_dev, int training,
+                 float* __restrict__ a2, uint8_t* __restrict__ idx2, int B) {
+  if (offset_dev) offset += uint64_t(*offset_dev);
+  extern __shared__ __align__(16) float smem[];
+  float* w_s = smem;
+  float* b_s = w_s + F2_WS;
+  float* in_s = b_s + 24;
+  const int tid = threadIdx.x;
+  for (int i = tid; i < F2_WS; i += F2_THREADS) {
+    int j = i % 12, g = (i / 12) & 1, ct = i / 24;
+    w_s[i] = j < 10 ? params[OFF_C2W + (g * 10 + j) * 250 + ct] : 0.f;
+  }
+  if (tid < 24) { int j = tid % 12, g = tid / 12; b_s[tid] = j < 10 ? params[OFF_C2B + g * 10 + j] : 0.f; }
+  const int warp = tid >> 5, lane = tid & 31;
+  const int g = lane >> 4, pp = lane & 15, py = pp >> 2, px = pp & 3;
+  const int ngroups = (B + F2_WARPS - 1) / F2_WARPS;
+  for (int grp = blockIdx.x; grp < ngroups; grp += gridDim.x) {
+    const int b0 = grp * F2_WARPS;
+    const int nvalid = min(F2_WARPS, B - b0);
+    __syncthreads();
+    const float4* src = reinterpret_cast<const float4*>(a1 + size_t(b0) * A1_PER);
+    float4* dst = reinterpret_cast<float4*>(in_s);
+    for (int i = tid; i < nvalid * (A1_PER / 4); i += F2_THREADS) dst[i] = src[i];
+    __syncthreads();
+    if (warp >= nvalid) continue;
+    const int b = b0 + warp;
+    const float* sample = in_s + warp * A1_PER + (2 * py) * P1 + 2 * px;
+
+    float acc[4][10];
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+      for (int j = 0; j < 10; ++j) acc[q][j] = 0.f;
+
+#pragma unroll 1
+    for (int ci = 0; ci < C1; ++ci) {
+      float patch[6][6];
+      const float* ip = sample + ci * 144;
+#pragma unroll
+      for (int r = 0; r < 6; ++r)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+          float2 v = *reinterpret_cast<const float2*>(ip + r * P1 + 2 * j);
+          patch[r][2 * j] = v.x; patch[r][2 * j + 1] = v.y;
+        }
+      const float* wbase = w_s + (ci * 25) * 24 + g * 12;
+#pragma unroll
+      for (int kh = 0; kh < 5; ++kh)
+#pragma unroll
+        for (int kw = 0; kw < 5; ++kw) {
+          const float4* wp = reinterpret_cast<const float4*>(wbase + (kh * 5 + kw) * 24);
+          float4 w0 = wp[0], w1 = wp[1], w2 = wp[2];
+          float w[10] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w, w2.x, w2.y};
+#pragma unroll
+          for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+            for (int dx = 0; dx < 2; ++dx) {
+              float v = patch[dy + kh][dx + kw];
+#pragma unroll
+              for (int j = 0; j < 10; ++j) acc[dy * 2 + dx][j] = fmaf(v, w[j], acc[dy * 2 + dx][j]);
+            }
+        }
+    }
+    // epilogue: bias, channel dropout (x * noise, noise in {0,2}), pool, ReLU
+#pragma unroll
+    for (int j = 0; j < 10; ++j) {
+      const int co = g * 10 + j;
+      float noise = 1.f;
+      if (training) {
+        float keep = mask2d ? mask2d[size_t(b) * C2 + co]
+                            : philox_keep(seed, offset, 1u, uint64_t(b) * C2 + co);
+        noise = keep * 2.f;
+      }
+      const float bias = b_s[g * 12 + j];
+      float best; int bi;
+      pool4((acc[0][j] + bias) * noise, (acc[1][j] + bias) * noise, (acc[2][j] + bias) * noise,
+            (acc[3][j] + bias) * noise, best, bi);
+      const size_t o = size_t(b) * A2_PER + co * 16 + pp;
+      a2[o] = fmaxf(best, 0.f);
+      idx2[o] = uint8_t(bi);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// K_F3: head.  Tile of 32 samples per CTA iteration; thread (sg,jg) computes
+// 2 samples x 4 fc1 outputs; W1 transposed in smem [k][52].
+// ---------------------------------------------------------------------------
+constexpr int HT = 32;              // samples per tile
+constexpr int HF_THREADS = 224;     // 16 sample-pairs x 13 output-quads = 208 active
+constexpr int HF_A2S = 324;         // a2 row stride (floats)
+constexpr int HF_HS = 53;           // h row stride
+constexpr int HF_SMEM = (320 * 52 + HT * HF_A2S + 52 + HT * HF_HS + 50 * 12 + 12 + HT * 12 + HT) * 4;
+__global__ void __launch_bounds__(HF_THREADS, 1)
+head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
+                const int64_t* __restrict__ target, const float* __restrict__ mask1d,
+                uint64_t seed, uint64_t offset, const int64_t* __restrict__ offset_dev, int training,
+                float* __restrict__ h_out,
+                float* __restrict__ logp_out, float* __restrict__ loss_out,
+                int64_t* __restrict__ argmax_out, unsigned long long* __restrict__ correct_out,
+                float* __restrict__ loss_part, unsigned int* __restrict__ counters, int B) {
+  extern __shared__ __align__(16) float smem[];
+  float* w1_s = smem;                    // [320][52]
+  float* a2_s = w1_s + 320 * 52;         // [32][324]
+  float* b1_s = a2_s + HT * HF_A2S;      // [52]
+  float* h_s = b1_s + 52;                // [32][53]
+  float* w2_s = h_s + HT * HF_HS;        // [50][12]
+  float* b2_s = w2_s + 50 * 12;          // [12]
+  float* z_s = b2_s + 12;                // [32][12]
+  float* nll_s = z_s + HT * 12;          // [32]
+  if (offset_dev) offset += uint64_t(*offset_dev);
+  const int tid = threadIdx.x;
+  for (int i = tid; i < F1 * A2_PER; i += HF_THREADS) {
+    int j = i / A2_PER, k = i % A2_PER;
+    w1_s[k * 52 + j] = params[OFF_F1W + i];
+  }
+  for (int i = tid; i < 320 * 2; i += HF_THREADS) w1_s[(i >> 1) * 52 + 50 + (i & 1)] = 0.f;
+  if (tid < 52) b1_s[tid] = tid < F1 ? params[OFF_F1B + tid] : 0.f;
+  for (int i = tid; i < 50 * 12; i += HF_THREADS) {
+    int k = i / 12, c = i % 12;
+    w2_s[i] = c < NC ? params[OFF_F2W + c * F1 + k] : 0.f;
+  }
+  if (tid < 12) b2_s[tid] = tid < NC ? params[OFF_F2B + tid] : 0.f;
+
+  const int sg = tid & 15, jg = tid >> 4;  // jg < 13 active
+  const int ntiles = (B + HT - 1) / HT;
+  float loss_acc = 0.f;                    // thread 0 only
+  int corr_acc = 0;
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int b0 = tile * HT;
+    const int nvalid = min(HT, B - b0);
+    __syncthreads();
+    // stage a2 tile (zero-fill rows past the batch)
+    for (int i = tid; i < HT * (A2_PER / 4); i += HF_THREADS) {
+      int s = i / (A2_PER / 4), k4 = i % (A2_PER / 4);
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (s < nvalid) v = *reinterpret_cast<const float4*>(a2 + size_t(b0 + s) * A2_PER + k4 * 4);
+      *reinterpret_cast<float4*>(a2_s + s * HF_A2S + k4 * 4) = v;
+    }
+    __syncthreads();
+    if (jg < 13) {
+      float acc[2][4];
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+      const float* ar0 = a2_s + sg * HF_A2S;
+      const float* ar1 = a2_s + (sg + 16) * HF_A2S;
+      const float* wr = w1_s + jg * 4;
+#pragma unroll 4
+      for (int k = 0; k < A2_PER; k += 4) {
+        float4 x0 = *reinterpret_cast<const float4*>(ar0 + k);
+        float4 x1 = *reinterpret_cast<const float4*>(ar1 + k);
+        float xa[4] = {x0.x, x0.y, x0.z, x0.w};
+        float xb[4] = {x1.x, x1.y, x1.z, x1.w};
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+          float4 w = *reinterpret_cast<const float4*>(wr + (k + kk) * 52);
+          acc[0][0] = fmaf(xa[kk], w.x, acc[0][0]); acc[0][1] = fmaf(xa[kk], w.y, acc[0][1]);
+          acc[0][2] = fmaf(xa[kk], w.z, acc[0][2]); acc[0][3] = fmaf(xa[kk], w.w, acc[0][3]);
+          acc[1][0] = fmaf(xb[kk], w.x, acc[1][0]); acc[1][1] = fmaf(xb[kk], w.y, acc[1][1]);
+          acc[1][2] = fmaf(xb[kk], w.z, acc[1][2]); acc[1][3] = fmaf(xb[kk], w.w, acc[1][3]);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int s = sg + 16 * i;
+        const int b = b0 + s;
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) {
+          const int j = jg * 4 + jj;
+          if (j < F1) {
+            float v = fmaxf(acc[i][jj] + b1_s[j], 0.f);
+            if (training && s < nvalid) {
+              float keep = mask1d ? mask1d[size_t(b) * F1 + j]
+                                  : philox_keep(seed, offset, 2u, uint64_t(b) * F1 + j);
+              v = v * (keep * 2.f);
+            }
+            h_s[s * HF_HS + j] = v;
+            if (s < nvalid) h_out[size_t(b) * F1 + j] = v;
+          }
+        }
+      }
+    }
+    __syncthreads();
+    // fc2: thread (s, class pair)
+    if (tid < HT * 5) {
+      const int s = tid / 5, c2 = (tid % 5) * 2;
+      float z0 = b2_s[c2], z1 = b2_s[c2 + 1];
+      const float* hr = h_s + s * HF_HS;
+#pragma unroll 10
+      for (int k = 0; k < F1; ++k) {
+        float hv = hr[k];
+        float2 w = *reinterpret_cast<const float2*>(w2_s + k * 12 + c2);
+        z0 = fmaf(hv, w.x, z0); z1 = fmaf(hv, w.y, z1);
+      }
+      z_s[s * 12 + c2] = z0; z_s[s * 12 + c2 + 1] = z1;
+    }
+    __syncthreads();
+    if (tid < HT) {
+      const int s = tid;
+      float nll = 0.f; int ok = 0;
+      if (s < nvalid) {
+        float z[NC];
+#pragma unroll
+        for (int c = 0; c < NC; ++c) z[c] = z_s[s * 12 + c];
+        float m = z[0];
+#pragma unroll
+        for (int c = 1; c < NC; ++c) m = fmaxf(m, z[c]);
+        float sum = 0.f;
+#pragma unroll
+        for (int c = 0; c < NC; ++c) sum += expf(z[c] - m);
+        const float lse = logf(sum);
+        float lp[NC];
+        int am = 0;
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+          lp[c] = z[c] - m - lse;
+          logp_out[size_t(b0 + s) * NC + c] = lp[c];
+        }
+        float best = lp[0];
+#pragma unroll
+        for (int c = 1; c < NC; ++c) if (lp[c] > best) { best = lp[c]; am = c; }
+        if (argmax_out) argmax_out[b0 + s] = am;
+        if (target) {
+          const int t = int(target[b0 + s]);
+          float picked = 0.f;
+#pragma unroll
+          for (int c = 0; c < NC; ++c) if (c == t) picked = lp[c];
+          nll = -picked;
+          ok = (am == t);
+        }
+      }
+      nll_s[s] = nll;
+      // warp 0 holds all 32 samples of the tile: fixed-order shuffle tree
+      float v = nll;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      int okc = __popc(__ballot_sync(0xffffffffu, ok));
+      if (tid == 0) { loss_acc += v; corr_acc += okc; }
+    }
+  }
+  if (tid == 0) {
+    if (correct_out && corr_acc) atomicAdd(correct_out, (unsigned long long)corr_acc);
+    if (loss_out) {
+      loss_part[blockIdx.x] = loss_acc;
+      __threadfence();
+      unsigned int ticket = atomicAdd(&counters[0], 1u);
+      if (ticket == gridDim.x - 1) {
+        __threadfence();
+        float total = 0.f;
+        for (unsigned int i = 0; i < gridDim.x; ++i) total += *((volatile float*)(loss_part + i));
+        loss_out[0] = total / float(B);
+        counters[0] = 0u;  // self-reset for the next launch
+      }
+    }
+  }
+}
+
+}  // namespace ddp
+
+using namespace ddp;
+
+extern "C" int ddp_net_forward(const float* params, const float* x, const int64_t* target,
+                               const float* mask2d, const float* mask1d, uint64_t seed,
+                               uint64_t offset, const int64_t* offset_dev, int training, int64_t batch,
+                               void* workspace,
+                               float* out_logp, float* out_loss, int64_t* out_argmax,
+                               int64_t* out_correct, void* scratch, void* stream_) {
+  DDP_REQUIRE(params && x && workspace && out_logp, "params, x, workspace and out_logp are required");
+  DDP_REQUIRE(batch >= 1 && batch <= (int64_t(1) << 24), "batch out of range");
+  DDP_REQUIRE(aligned16(params) && aligned16(x) && aligned16(workspace), "params/x/workspace must be 16-byte aligned");
+  DDP_REQUIRE(!(out_loss || out_correct) || target, "target is required for out_loss/out_correct");
+  DDP_REQUIRE(!out_loss || scratch, "scratch is required for out_loss");
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int B = int(batch);
+  const int sms = sm_count();
+  Workspace ws = carve_workspace(workspace, batch);
+
+  static bool attr_done = false;
+  if (!attr_done) {
+    DDP_CUDA(cudaFuncSetAttribute(conv2_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, F2_SMEM));
+    DDP_CUDA(cudaFuncSetAttribute(head_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HF_SMEM));
+    attr_done = true;
+  }
+  {
+    int npairs = (B + 1) / 2;
+    int grid = npairs < sms * 2 ? npairs : sms * 2;
+    conv1_fwd_kernel<<<grid, F1_THREADS, 0, stream>>>(params, x, ws.a1, ws.idx1, B);
+  }
+  {
+    int ngroups = (B + F2_WARPS - 1) / F2_WARPS;
+    int grid = ngroups < sms * 2 ? ngroups : sms * 2;
+    conv2_fwd_kernel<<<grid, F2_THREADS, F2_SMEM, stream>>>(params, ws.a1, mask2d, seed, offset, offset_dev, training,
+                                                          ws.a2, ws.idx2, B);
+  }
+  {
+    int ntiles = (B + HT - 1) / HT;
+    int grid = ntiles < sms ? ntiles : sms;
+    Scratch sc{};
+    if (scratch) sc = carve_scratch(scratch, batch);
+    head_fwd_kernel<<<grid, HF_THREADS, HF_SMEM, stream>>>(
+        params, ws.a2, target, mask1d, seed, offset, offset_dev, training, ws.h, out_logp, out_loss, out_argmax,
+        reinterpret_cast<unsigned long long*>(out_correct), sc.loss_part, sc.counters, B);
+  }
+  DDP_CUDA(cudaGetLastError());
+  return 0;
+}

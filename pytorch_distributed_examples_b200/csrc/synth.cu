@@ -1,0 +1,54 @@
+// On-device synthetic 28x28 data (replaces ref: horovod/mnist_horovod.py:34-38, the
+// torchvision MNIST download + ToTensor + Normalize((0.1307,), (0.3081,)) pipeline, which
+// needs a network).  Sample `i` of the virtual dataset is a pure function of (seed, i):
+//   pixels  u8[784]: bytes of Philox4x32-10(counter=(i_lo, i_hi, blk, 0), key=seed), blk=0..48
+//   x = (float(u8) / 255 - 0.1307) / 0.3081      (IEEE fp32, same op order as torchvision)
+//   label   Philox(counter=(i_lo, i_hi, 49, 0)).x % 10
+// HBM-bound writer: 3,136 + 8 bytes per sample, 64 contiguous bytes per thread.
+#include "common.cuh"
+
+namespace ddp {
+
+__global__ void __launch_bounds__(256)
+synth_batch_kernel(uint64_t seed, const int64_t* __restrict__ indices, int64_t base_index, int64_t batch,
+                   float* __restrict__ out_x, int64_t* __restrict__ out_y) {
+  const int64_t t = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int64_t b = t / 50;
+  const int blk = int(t % 50);
+  if (b >= batch) return;
+  const uint64_t idx = uint64_t(indices ? indices[b] : base_index + b);
+  Philox4 r = philox4x32_10(uint32_t(idx), uint32_t(idx >> 32), uint32_t(blk), 0u,
+                            uint32_t(seed), uint32_t(seed >> 32));
+  if (blk == 49) {
+    if (out_y) out_y[b] = int64_t(r.x % 10u);
+    return;
+  }
+  const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+  float4* o = reinterpret_cast<float4*>(out_x + b * IMG_PIX + blk * 16);
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    float v[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      float u = float((w[q] >> (8 * k)) & 0xffu);
+      v[k] = (u / 255.0f - 0.1307f) / 0.3081f;
+    }
+    o[q] = make_float4(v[0], v[1], v[2], v[3]);
+  }
+}
+
+}  // namespace ddp
+
+using namespace ddp;
+
+extern "C" int ddp_synth_batch(uint64_t seed, const int64_t* indices, int64_t base_index, int64_t batch,
+                               float* out_x, int64_t* out_y, void* stream_) {
+  DDP_REQUIRE(batch >= 0, "negative batch");
+  if (batch == 0) return 0;
+  DDP_REQUIRE(out_x && aligned16(out_x), "out_x must be non-null and 16-byte aligned");
+  const int64_t threads = batch * 50;
+  synth_batch_kernel<<<int((threads + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      seed, indices, base_index, batch, out_x, out_y);
+  DDP_CUDA(cudaGetLastError());
+  return 0;
+}

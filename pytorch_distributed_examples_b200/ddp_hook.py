@@ -1,0 +1,114 @@
+"""DDP communication hook: stock ``torch.nn.parallel.DistributedDataParallel`` + our NCCL path.
+
+The reference wraps its model in DDP (ref: pytorch_elastic/mnist_ddp_elastic.py:58) and relies on DDP's
+built-in bucket allreduce.  ``allreduce_hook`` is the drop-in seam: registered with
+``ddp.register_comm_hook(state, allreduce_hook)`` it must leave results equal to hook-less DDP, whose
+contract is torch: distributed/algorithms/ddp_comm_hooks/default_hooks.py:35-54 — the hook receives the
+bucket NOT pre-divided and returns a Future of a tensor shaped like ``bucket.buffer()`` holding the mean.
+Here: ncclAllReduce(sum) of the flat bucket through the C-ABI on a dedicated comm stream, then the 1/N scale
+kernel, completed as a CUDA-aware Future so DDP's finalize_backward stream-syncs correctly.
+``FusedUpdateHook`` goes one step further (optimizer-in-backward, same idea as torch:
+distributed/algorithms/ddp_comm_hooks/optimizer_overlap_hooks.py:50-128): after the allreduce it runs the
+fused (1/N)*g + optimizer update straight from the bucket, so ``optimizer.step()`` becomes a no-op.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+from . import _native
+from .optim import optimizer_kind
+
+
+class HookState:
+    def __init__(self, communicator=None, device=None):
+        if communicator is None:
+            from . import hvd
+            communicator = hvd._require()
+        self.comm = communicator
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.stream = torch.cuda.Stream(device=self.device, priority=-1)
+        self.calls = 0
+
+
+def _run_on_comm_stream(state: HookState, buf: torch.Tensor, body):
+    nat = _native.get()
+    nat.bind_device(state.device.index)        # hooks run on autograd's engine thread
+    cur = torch.cuda.current_stream(state.device)
+    state.stream.wait_stream(cur)
+    with torch.cuda.stream(state.stream):
+        body()
+        fut = torch.futures.Future(devices=[state.device])
+        fut.set_result(buf)                    # records an event on the comm stream
+    buf.record_stream(state.stream)
+    state.calls += 1
+    return fut
+
+
+def allreduce_hook(state: HookState, bucket: dist.GradBucket) -> torch.futures.Future[torch.Tensor]:
+    buf = bucket.buffer()
+    world = state.comm.world
+
+    def body():
+        state.comm.allreduce_sum_(buf)
+        if world > 1:
+            _native.get().scale(buf, 1.0 / world)
+
+    return _run_on_comm_stream(state, buf, body)
+
+
+class FusedUpdateHook:
+    """``ddp.register_comm_hook(FusedUpdateHook.State(comm, optimizer), FusedUpdateHook.hook)``.
+    Parameters of each bucket are re-homed (once) into a flat arena packed exactly like DDP packs the
+    bucket, so the update kernel walks bucket and parameters with the same index."""
+
+    class State(HookState):
+        def __init__(self, optimizer: torch.optim.Optimizer, communicator=None, device=None):
+            super().__init__(communicator, device)
+            self.optimizer = optimizer
+            self.kind = optimizer_kind(optimizer)
+            self.buckets = {}   # bucket index -> dict(arena, state1, state2, steps, group)
+
+    @staticmethod
+    def _prepare(state, bucket):
+        params = bucket.parameters()
+        total = bucket.buffer().numel()
+        arena = torch.zeros(total, dtype=torch.float32, device=state.device)
+        off = 0
+        group = None
+        with torch.no_grad():
+            for p in params:
+                n = p.numel()
+                arena[off:off + n].copy_(p.data.reshape(-1))
+                p.data = arena[off:off + n].view(p.shape)
+                off += n
+                for g in state.optimizer.param_groups:
+                    if any(p is q for q in g["params"]):
+                        if group is not None and g is not group:
+                            raise RuntimeError("a DDP bucket spans several optimizer param groups")
+                        group = g
+        from .optim import _Group
+        shell = _Group.__new__(_Group)      # reuse hyper()/needs_state() on a bare group
+        shell.group, shell.kind = group, state.kind
+        n1, n2 = shell.needs_state()
+        return dict(arena=arena, shell=shell, steps=0,
+                    state1=torch.zeros_like(arena) if n1 else None,
+                    state2=torch.zeros_like(arena) if n2 else None)
+
+    @staticmethod
+    def hook(state, bucket: dist.GradBucket) -> torch.futures.Future[torch.Tensor]:
+        buf = bucket.buffer()
+        idx = bucket.index()
+        if idx not in state.buckets or state.buckets[idx]["arena"].numel() != buf.numel():
+            state.buckets[idx] = FusedUpdateHook._prepare(state, bucket)
+        b = state.buckets[idx]
+        world = state.comm.world
+
+        def body():
+            state.comm.allreduce_sum_(buf)
+            b["steps"] += 1
+            hyper = b["shell"].hyper(write_back=True)   # leave the averaged gradient in the bucket for DDP
+            _native.get().fused_update(state.kind, buf, b["arena"], b["state1"], b["state2"], buf.numel(),
+                                       1.0 / world, hyper, step=b["steps"])
+
+        return _run_on_comm_stream(state, buf, body)

@@ -1,0 +1,112 @@
+"""``TrainStep`` — the whole data-parallel training step of the reference loop as ONE replayable CUDA graph.
+
+The reference's hot loop (ref: horovod/mnist_horovod.py:59-64; Trainer._run_batch,
+ref: pytorch_elastic/mnist_ddp_elastic.py:71-79) is
+    optimizer.zero_grad(); output = model(data); loss = F.nll_loss(output, target); loss.backward(); optimizer.step()
+At 2.6 MFLOP/sample the GPU work of a step is tens of microseconds, so Python dispatch, autograd and launch
+latency dominate unless the step is fused and replayed.  TrainStep enqueues, on one stream,
+    K_F1..K_F3 (+NLL mean)  ->  K_B3,K_B2d,K_B2w,K_B1,K_R (grads born in the bucket)
+    ->  ncclAllReduce(sum) of the bucket (world > 1)  ->  fused (1/N)*g + optimizer update  ->  step++
+captures it once, and replays it per batch.  zero_grad() is free (the bucket is overwritten).  Dropout masks
+come from Philox keyed by the device step counter, so replays draw fresh masks.
+Same arithmetic as the module path (`Net` + `hvd.DistributedOptimizer`), which stays the drop-in API.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _native
+from .net import Net
+from .optim import FusedUpdater
+
+
+class TrainStep:
+    def __init__(self, model: Net, optimizer, batch_size: int, communicator=None, use_graph: bool = True):
+        model._check_arena()
+        self.model = model
+        self.optimizer = optimizer
+        self.updater = getattr(optimizer, "_fused", None) or FusedUpdater(optimizer)
+        if len(self.updater.groups) != 1 or self.updater.groups[0].param_arena.data_ptr() != model.flat_params.data_ptr():
+            raise RuntimeError("TrainStep expects one param group covering exactly the Net's parameters")
+        self.group = self.updater.groups[0]
+        self.comm = communicator
+        self.world = communicator.world if communicator is not None else 1
+        self.batch = int(batch_size)
+        dev = model.flat_params.device
+        nat = _native.get()
+        self.x = torch.zeros(self.batch, 1, 28, 28, dtype=torch.float32, device=dev)
+        self.y = torch.zeros(self.batch, dtype=torch.int64, device=dev)
+        self.logp = torch.empty(self.batch, 10, dtype=torch.float32, device=dev)
+        self.loss = torch.zeros(1, dtype=torch.float32, device=dev)
+        self.ws = torch.empty(nat.workspace_bytes(self.batch), dtype=torch.uint8, device=dev)
+        self.scratch = torch.zeros(nat.scratch_bytes(self.batch), dtype=torch.uint8, device=dev)
+        self.use_graph = use_graph
+        self.graph = None
+        self._fingerprint = None
+        self.kernel_launches_per_step = 0
+
+    # -- one step's stream work ----------------------------------------------------------------------
+    def _enqueue(self):
+        nat = _native.get()
+        m, g = self.model, self.group
+        nat.net_forward(m._arena, self.x, self.y, None, None, m.dropout_seed, 0, True, self.ws, self.logp,
+                        out_loss=self.loss, scratch=self.scratch, offset_dev=g.step_dev)
+        nat.net_backward(m._arena, self.x, self.logp, None, self.y, 1.0, True, self.ws, self.scratch, m._grad_arena)
+        launches = 3 + 5
+        if self.world > 1:
+            self.comm.allreduce_sum_(m._grad_arena)
+        g.bucket = m._grad_arena
+        g.adopted = True
+        g.update(1.0 / self.world, use_step_dev=True)
+        launches += 2
+        self.kernel_launches_per_step = launches
+
+    def _hyper_fingerprint(self):
+        return tuple(sorted((k, str(v)) for k, v in self.group.group.items() if k != "params"))
+
+    def _capture(self):
+        g = self.group
+        g.ensure_state()
+        g.sync_step_to_device()
+        keep = [t.clone() for t in (g.param_arena, g.step_dev, self.loss)]
+        keep_s = [s.clone() if s is not None else None for s in (g.state1, g.state2)]
+        host_steps = g.steps
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):            # warm-up outside capture (sets func attributes, loads modules)
+                self._enqueue()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        with torch.no_grad():             # undo the warm-up steps
+            g.param_arena.copy_(keep[0]); g.step_dev.copy_(keep[1]); self.loss.copy_(keep[2])
+            for s, k in zip((g.state1, g.state2), keep_s):
+                if s is not None:
+                    s.copy_(k)
+        g.steps = host_steps
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            self._enqueue()
+        g.steps = host_steps
+        self.graph = graph
+        self._fingerprint = self._hyper_fingerprint()
+
+    # -- public --------------------------------------------------------------------------------------
+    def __call__(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        """Runs one step on (data [B,1,28,28], target [B]); returns the device loss tensor (no host sync).
+        Host tensors are accepted (pinned memory makes the copy asynchronous)."""
+        if data.shape[0] != self.batch:
+            raise RuntimeError(f"TrainStep was built for batch {self.batch}, got {data.shape[0]}")
+        if data.data_ptr() != self.x.data_ptr():
+            self.x.copy_(data.reshape(self.batch, 1, 28, 28), non_blocking=True)
+        if target.data_ptr() != self.y.data_ptr():
+            self.y.copy_(target, non_blocking=True)
+        if not self.use_graph:
+            self._enqueue()
+            return self.loss
+        if self.graph is None or self._fingerprint != self._hyper_fingerprint():
+            self._capture()
+        self.graph.replay()
+        self.group.steps += 1
+        self.group.graph_mode = True
+        return self.loss

@@ -1,0 +1,169 @@
+"""GPU parity of the Net kernels, called through the C-ABI, against the reference golden vectors and the oracle."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from helpers import RTOL, arena_from_state_dict, assert_close_scaled, load_golden, split_arena
+from oracle import net_oracle, synth_oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _run_fwd_bwd(nat, sd, x, y, m2, m1, training=True, use_dlogp=False):
+    dev = "cuda"
+    B = x.shape[0]
+    arena = arena_from_state_dict(nat, sd)
+    xg, yg = x.to(dev).contiguous(), y.to(dev)
+    ws = torch.empty(nat.workspace_bytes(B), dtype=torch.uint8, device=dev)
+    sc = torch.zeros(nat.scratch_bytes(B), dtype=torch.uint8, device=dev)
+    logp = torch.empty(B, 10, device=dev)
+    loss = torch.zeros(1, device=dev)
+    am = torch.empty(B, dtype=torch.int64, device=dev)
+    nat.net_forward(arena, xg, yg, None if m2 is None else m2.to(dev).contiguous(),
+                    None if m1 is None else m1.to(dev).contiguous(), 0, 0, training, ws, logp,
+                    out_loss=loss, out_argmax=am, scratch=sc)
+    bucket = torch.full((21848,), float("nan"), device=dev)
+    if use_dlogp:
+        dlogp = torch.zeros(B, 10, device=dev)
+        dlogp[torch.arange(B), yg] = -1.0 / B
+        nat.net_backward(arena, xg, logp, dlogp, None, 1.0, training, ws, sc, bucket)
+    else:
+        nat.net_backward(arena, xg, logp, None, yg, 1.0, training, ws, sc, bucket)
+    torch.cuda.synchronize()
+    return logp, loss, am, bucket
+
+
+@pytest.mark.parametrize("name", ["fwdbwd_b1.pt", "fwdbwd_b8.pt", "fwdbwd_b48.pt", "fwdbwd_b64.pt"])
+@pytest.mark.parametrize("use_dlogp", [False, True])
+def test_forward_backward_vs_reference_golden(native, name, use_dlogp):
+    fx = load_golden(name)
+    logp, loss, am, bucket = _run_fwd_bwd(native, fx["state_dict"], fx["x"], fx["y"], fx["mask2d"], fx["mask1d"],
+                                          use_dlogp=use_dlogp)
+    assert_close_scaled(logp, fx["logp"], name="logp")
+    assert abs(loss.item() - fx["loss"].item()) <= RTOL * abs(fx["loss"].item())
+    grads = split_arena(native, bucket)
+    for k, g in fx["grads"].items():
+        assert_close_scaled(grads[k], g, name=k)
+    assert torch.isfinite(bucket).all(), "padding slots of the bucket must be written (zeros)"
+    # argmax of the training-mode output must agree with the reference's bit-for-bit
+    assert torch.equal(am.cpu(), fx["logp"].argmax(1))
+
+
+@pytest.mark.parametrize("name", ["fwdbwd_b8.pt", "fwdbwd_b48.pt", "fwdbwd_b64.pt"])
+def test_eval_forward_argmax_bit_exact(native, name):
+    fx = load_golden(name)
+    B = fx["x"].shape[0]
+    arena = arena_from_state_dict(native, fx["state_dict"])
+    ws = torch.empty(native.workspace_bytes(B), dtype=torch.uint8, device="cuda")
+    logp = torch.empty(B, 10, device="cuda")
+    am = torch.empty(B, dtype=torch.int64, device="cuda")
+    correct = torch.zeros(1, dtype=torch.int64, device="cuda")
+    native.net_forward(arena, fx["x"].cuda(), fx["y"].cuda(), None, None, 0, 0, False, ws, logp, out_argmax=am,
+                       out_correct=correct)
+    assert_close_scaled(logp, fx["logp_eval"], name="logp_eval")
+    assert torch.equal(am.cpu(), fx["argmax_eval"])
+    assert correct.item() == int((fx["argmax_eval"] == fx["y"]).sum())
+
+
+@pytest.mark.parametrize("B", [2, 3, 31, 33, 100, 257, 512, 1024])
+def test_forward_backward_vs_oracle_ragged_sizes(native, B):
+    torch.manual_seed(100 + B)
+    sd = {k: v.detach().clone() for k, v in net_oracle.OracleNet().state_dict().items()}
+    xn, yn = synth_oracle.synth_batch(77, np.arange(B) + 31 * B)
+    x, y = torch.from_numpy(xn), torch.from_numpy(yn)
+    g = torch.Generator().manual_seed(B)
+    m2 = torch.empty(B, 20).bernoulli_(0.5, generator=g)
+    m1 = torch.empty(B, 50).bernoulli_(0.5, generator=g)
+    logp_o, loss_o, grads_o = net_oracle.forward_backward(sd, x, y, m2, m1)
+    logp, loss, am, bucket = _run_fwd_bwd(native, sd, x, y, m2, m1)
+    assert_close_scaled(logp, logp_o, name="logp")
+    assert abs(loss.item() - loss_o.item()) <= RTOL * abs(loss_o.item())
+    grads = split_arena(native, bucket)
+    for k, gref in grads_o.items():
+        assert_close_scaled(grads[k], gref, name=f"B={B} {k}")
+
+
+def test_full_size_batch_4096_properties(native):
+    """BASELINE config size: linearity of the batch-mean gradient (size-independent property) + oracle check
+    on a slice.  grad(B=4096) == mean of the grads of its 4 contiguous quarters (same masks)."""
+    B = 4096
+    torch.manual_seed(5)
+    sd = {k: v.detach().clone() for k, v in net_oracle.OracleNet().state_dict().items()}
+    xn, yn = synth_oracle.synth_batch(1234, np.arange(B))
+    x, y = torch.from_numpy(xn), torch.from_numpy(yn)
+    g = torch.Generator().manual_seed(9)
+    m2 = torch.empty(B, 20).bernoulli_(0.5, generator=g)
+    m1 = torch.empty(B, 50).bernoulli_(0.5, generator=g)
+    logp, loss, am, bucket = _run_fwd_bwd(native, sd, x, y, m2, m1)
+    parts, losses = [], []
+    for q in range(4):
+        s = slice(q * 1024, (q + 1) * 1024)
+        lq, lossq, _, bq = _run_fwd_bwd(native, sd, x[s], y[s], m2[s], m1[s])
+        assert torch.equal(lq, logp[s]), "per-sample outputs must not depend on the batch they are in"
+        parts.append(bq); losses.append(lossq)
+    assert_close_scaled(bucket, torch.stack(parts).mean(0), name="grad linearity")
+    assert abs(loss.item() - torch.stack(losses).mean().item()) <= RTOL * abs(loss.item())
+    # determinism: same launch twice -> identical bits (fixed-order reductions, no float atomics)
+    _, loss2, _, bucket2 = _run_fwd_bwd(native, sd, x, y, m2, m1)
+    assert torch.equal(bucket, bucket2) and torch.equal(loss, loss2)
+    # oracle on the full batch (CPU takes ~1 s)
+    logp_o, loss_o, grads_o = net_oracle.forward_backward(sd, x, y, m2, m1)
+    assert_close_scaled(logp, logp_o, name="logp 4096")
+    grads = split_arena(native, bucket)
+    for k, gref in grads_o.items():
+        assert_close_scaled(grads[k], gref, name=f"4096 {k}")
+
+
+def test_philox_dropout_statistics_and_determinism(native):
+    B = 2048
+    torch.manual_seed(1)
+    sd = {k: v.detach().clone() for k, v in net_oracle.OracleNet().state_dict().items()}
+    arena = arena_from_state_dict(native, sd)
+    x = torch.from_numpy(synth_oracle.synth_batch(5, np.arange(B))[0]).cuda()
+    ws = torch.empty(native.workspace_bytes(B), dtype=torch.uint8, device="cuda")
+    outs = []
+    for seed, off in [(11, 0), (11, 0), (11, 1), (12, 0)]:
+        logp = torch.empty(B, 10, device="cuda")
+        native.net_forward(arena, x, None, None, None, seed, off, True, ws, logp)
+        # h (fc2 input) sits last in the workspace; recover the keep rate from zeros of relu*mask
+        outs.append(logp.clone())
+    assert torch.equal(outs[0], outs[1]), "same (seed, offset) -> same masks"
+    assert not torch.equal(outs[0], outs[2]) and not torch.equal(outs[0], outs[3])
+    # keep-rate: a2 is exactly 0 for dropped channels; count all-zero (b,co) rows
+    a2_off = ((B * 1440 * 4 + 255) // 256 * 256) + ((B * 1440 + 255) // 256 * 256)
+    a2 = ws[a2_off:a2_off + B * 320 * 4].view(torch.float32).view(B, 20, 16)
+    dropped = (a2.abs().sum(-1) == 0).float().mean().item()
+    assert 0.45 < dropped < 0.60, dropped      # ~0.5 (+ a few channels that are all-negative before ReLU)
+
+
+def test_module_api_matches_reference_loop(native):
+    """The drop-in surface: Net().cuda(), F.nll_loss, loss.backward(), torch.max — ref: mnist_horovod.py:58-64."""
+    import pytorch_distributed_examples_b200 as pkg
+    fx = load_golden("fwdbwd_b8.pt")
+    model = pkg.Net()
+    model.load_state_dict(fx["state_dict"])
+    model = model.cuda()
+    assert list(model.state_dict().keys()) == list(fx["state_dict"].keys())
+    model.train()
+    out = model(fx["x"].cuda(), fx["mask2d"].cuda(), fx["mask1d"].cuda())
+    loss = F.nll_loss(out, fx["y"].cuda())
+    loss.backward()
+    assert abs(loss.item() - fx["loss"].item()) <= RTOL * abs(fx["loss"].item())
+    for k, p in model.named_parameters():
+        assert_close_scaled(p.grad, fx["grads"][k], name=k)
+        # gradients are views of the flat bucket (born there, no copy)
+    assert model.conv1.weight.grad.data_ptr() == model.flat_grads.data_ptr()
+    model.eval()
+    with torch.no_grad():
+        outputs = model(fx["x"].cuda())
+    _, predicted = torch.max(outputs, 1)
+    assert torch.equal(predicted.cpu(), fx["argmax_eval"])
+    # gradient accumulation (two backwards without zero_grad) must add, not overwrite
+    model.train()
+    model.zero_grad(set_to_none=True)
+    for _ in range(2):
+        F.nll_loss(model(fx["x"].cuda(), fx["mask2d"].cuda(), fx["mask1d"].cuda()), fx["y"].cuda()).backward()
+    assert_close_scaled(model.fc1.weight.grad, 2 * fx["grads"]["fc1.weight"], name="accumulated")
+    with pytest.raises(RuntimeError):
+        pkg.Net()(fx["x"])            # CPU call must fail loudly

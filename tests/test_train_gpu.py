@@ -1,0 +1,155 @@
+"""Multi-step training parity against the reference loops (golden), W=2 data-parallel semantics, the
+graph-captured TrainStep, elastic commit/restore and snapshot interchange — all on one GPU."""
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from helpers import RTOL, assert_close_scaled, load_golden
+from oracle import net_oracle, synth_oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _make(pkg, sd, opt_kind, opt_kw, wrap):
+    model = pkg.Net(); model.load_state_dict(sd); model = model.cuda(); model.train()
+    topt = net_oracle.make_optimizer(opt_kind, model.parameters(), **opt_kw)
+    return model, wrap(topt)
+
+
+@pytest.mark.parametrize("name", ["train_sgd.pt", "train_adamw.pt", "train_adam.pt", "train_sgdm.pt", "train_adadelta.pt"])
+def test_training_loop_matches_reference_golden(native, name):
+    """ref loop: horovod/mnist_horovod.py:58-64 with hvd.DistributedOptimizer at size 1."""
+    import pytorch_distributed_examples_b200 as pkg
+    hvd = pkg.hvd
+    hvd.init()
+    fx = load_golden(name)
+    model, opt = _make(pkg, fx["state_dict0"], fx["opt_kind"], fx["opt_kw"],
+                       lambda o: hvd.DistributedOptimizer(o, named_parameters=None))
+    assert isinstance(opt, torch.optim.Optimizer)
+    hvd.broadcast_parameters(model.state_dict(), root_rank=0)
+    for k in range(fx["xs"].shape[0]):
+        opt.zero_grad()
+        out = model(fx["xs"][k].cuda(), fx["masks2d"][k].cuda(), fx["masks1d"][k].cuda())
+        loss = F.nll_loss(out, fx["ys"][k].cuda())
+        loss.backward()
+        opt.step()
+        assert abs(loss.item() - fx["losses"][k].item()) <= RTOL * abs(fx["losses"][k].item()), (k, loss.item())
+    for key, v in model.state_dict().items():
+        assert_close_scaled(v, fx["state_dict"][key], rtol=3e-5 if "adadelta" in name else RTOL, name=key)
+
+
+def test_two_rank_semantics_match_real_gloo_ddp(native):
+    """Both shards of every step run on this GPU; the 'allreduce' is the sum of the two buckets; then the fused
+    (1/2)*g + SGD update.  Must equal the parameters real 2-process gloo DDP produced (golden)."""
+    from pytorch_distributed_examples_b200 import _native
+    import pytorch_distributed_examples_b200 as pkg
+    fx = load_golden("ddp_gloo_w2.pt")
+    W = fx["world"]
+    models = []
+    for r in range(W):
+        m = pkg.Net(); m.load_state_dict(fx["state_dict0"]); models.append(m.cuda().train())
+    h = _native.Hyper(); h.lr = 0.01
+    Bt = fx["xs"].shape[1] // W
+    for k in range(fx["xs"].shape[0]):
+        for r, m in enumerate(models):
+            sl = slice(r * Bt, (r + 1) * Bt)
+            m.zero_grad(set_to_none=True)
+            F.nll_loss(m(fx["xs"][k, sl].cuda(), fx["masks2d"][k, sl].cuda(), fx["masks1d"][k, sl].cuda()),
+                       fx["ys"][k, sl].cuda()).backward()
+        total = models[0].flat_grads + models[1].flat_grads          # what ncclAllReduce(sum) leaves on every rank
+        for m in models:
+            native.fused_update(_native.OPT_SGD, total, m.flat_params, None, None, total.numel(), 1.0 / W, h, step=k + 1)
+    assert torch.equal(models[0].flat_params, models[1].flat_params), "replicas must stay bit-identical"
+    for key, v in models[0].state_dict().items():
+        assert_close_scaled(v, fx["state_dict"][key], name=key)
+
+
+@pytest.mark.parametrize("opt_kind,kw", [("sgd", dict(lr=0.01, momentum=0.9)), ("adamw", dict(lr=0.005))])
+def test_trainstep_graph_equals_module_path(native, opt_kind, kw):
+    import pytorch_distributed_examples_b200 as pkg
+    torch.manual_seed(11)
+    sd = {k: v.detach().clone() for k, v in net_oracle.OracleNet().state_dict().items()}
+    B, steps = 64, 5
+    xn, yn = synth_oracle.synth_batch(1234, np.arange(B * steps))
+    xs = torch.from_numpy(xn).view(steps, B, 1, 28, 28).cuda(); ys = torch.from_numpy(yn).view(steps, B).cuda()
+    results = []
+    for mode in ("module", "eager", "graph"):
+        model = pkg.Net(); model.load_state_dict(sd); model = model.cuda().train(); model.dropout_seed = 99
+        topt = net_oracle.make_optimizer(opt_kind, model.parameters(), **kw)
+        losses = []
+        if mode == "module":
+            opt = pkg.FusedOptimizer(topt)
+            for k in range(steps):
+                opt.zero_grad()
+                loss = F.nll_loss(model(xs[k]), ys[k]); loss.backward(); opt.step()
+                losses.append(loss.item())
+        else:
+            step = pkg.TrainStep(model, topt, B, use_graph=(mode == "graph"))
+            for k in range(steps):
+                losses.append(step(xs[k], ys[k]).item())
+        results.append((losses, model.flat_params.clone()))
+    for losses, params in results[1:]:
+        np.testing.assert_allclose(losses, results[0][0], rtol=1e-6)
+        assert_close_scaled(params, results[0][1], rtol=1e-6, name="TrainStep vs module path")
+    assert torch.equal(results[1][1], results[2][1]), "graph replay must equal eager enqueue bit-for-bit"
+
+
+def test_elastic_commit_restore_and_snapshot(native, tmp_path):
+    """ref: horovod_mnist_elastic.py:71-72,104 (commit / TorchState) and mnist_ddp_elastic.py:95-104 (snapshot.pt)."""
+    import pytorch_distributed_examples_b200 as pkg
+    hvd = pkg.hvd
+    hvd.init()
+    torch.manual_seed(2)
+    model = pkg.Net().cuda().train()
+    opt = hvd.DistributedOptimizer(torch.optim.AdamW(model.parameters(), lr=0.01), named_parameters=model.named_parameters())
+    ds = pkg.SyntheticMNIST(length=4096)
+
+    def step(i):
+        x, y = ds.batch(base_index=64 * i, count=64)
+        opt.zero_grad(); F.nll_loss(model(x), y).backward(); opt.step()
+
+    state = hvd.elastic.TorchState(model, opt, batch=0, epoch=0)
+    calls = []
+    state.register_reset_callbacks([lambda: calls.append(1)])
+    for i in range(3):
+        step(i)
+    state.batch = 3; state.epoch = 1
+    state.commit()
+    committed = [a.clone() for a in opt._fused.arenas()]
+    for i in range(3, 6):
+        step(i)
+    state.batch = 6
+    assert not torch.equal(opt._fused.arenas()[0], committed[0])
+    state.restore()
+    torch.cuda.synchronize()
+    for a, c in zip(opt._fused.arenas(), committed):
+        assert torch.equal(a, c), "restore must be bit-exact"
+    assert state.batch == 3 and state.epoch == 1 and opt._fused.groups[0].steps == 3
+    state.sync(); state.on_reset()
+    assert calls == [1]
+    # LR rescale callback semantics (ref :80-82): param_groups are the live hyper-parameters
+    for g in opt.param_groups:
+        g["lr"] = 0.01 / 2 ** 0.5
+    step(7)
+    # snapshot.pt: same keys/format as the reference; loads into the oracle (= reference) Net on CPU
+    path = os.path.join(tmp_path, "snapshot.pt")
+    pkg.save_snapshot(model, 4, path)
+    snap = torch.load(path)
+    assert set(snap) == {"MODEL_STATE", "EPOCHS_RUN"} and snap["EPOCHS_RUN"] == 4
+    ref = net_oracle.OracleNet(); ref.load_state_dict(snap["MODEL_STATE"])
+    m2 = pkg.Net().cuda()
+    assert pkg.load_snapshot(m2, path) == 4
+    assert torch.equal(m2.flat_params, model.flat_params)
+
+
+def test_device_loader_epoch_matches_reference_batching(native):
+    """DataLoader(batch_size=128, sampler=DistributedSampler) at world 2: 234 full batches + one of 48."""
+    import pytorch_distributed_examples_b200 as pkg
+    ds = pkg.SyntheticMNIST(length=60000)
+    sampler = pkg.DistributedSampler(ds, num_replicas=2, rank=1)
+    loader = pkg.DeviceLoader(ds, batch_size=128, sampler=sampler)
+    sizes = [d.shape[0] for d, _ in loader]
+    assert len(loader) == 235 and sizes == [128] * 234 + [48]
