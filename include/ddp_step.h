@@ -175,6 +175,16 @@ int ddp_broadcast(void* comm, void* buf, int64_t nbytes, int root, void* stream)
 int ddp_state_snapshot(const void* device_arena, void* pinned_host, int64_t nbytes, void* stream);
 int ddp_state_restore(void* device_arena, const void* pinned_host, int64_t nbytes, void* stream);
 
+/* ---- per-kernel timing aid (no counterpart in the reference; used by bench.py's roofline leg) ----
+ * When enabled, ddp_net_forward/backward bracket every kernel they launch with CUDA events on the
+ * launch stream.  ddp_prof_read synchronises on the last event and returns the duration in ms of
+ * the kernels of the most recent forward and backward call, in this order:
+ *   conv1_fwd, conv2_fwd, head_fwd, head_bwd, conv2_dgrad, conv2_wgrad, conv1_wgrad, reduce_partials
+ * Do not enable during CUDA-graph capture.                                                        */
+#define DDP_PROF_KERNELS 8
+int ddp_prof_enable(int on);
+int ddp_prof_read(float* ms_out /* [DDP_PROF_KERNELS] */);
+
 #ifdef __cplusplus
 }
 #endif

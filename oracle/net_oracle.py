@@ -61,12 +61,16 @@ def draw_masks(batch: int, generator=None):
     return m2, m1
 
 
-def forward_backward(state_dict, x, target, mask2d=None, mask1d=None, training=True):
+def forward_backward(state_dict, x, target, mask2d=None, mask1d=None, training=True, dtype=torch.float32):
     """One forward + F.nll_loss + backward (ref: horovod/mnist_horovod.py:61-63).
-    Returns (logp, loss, grads dict)."""
-    net = OracleNet()
-    net.load_state_dict(state_dict)
+    Returns (logp, loss, grads dict).  dtype=float64 gives the exact-arithmetic yardstick: at B=4096 torch's
+    own fp32 CPU conv1 weight gradient (a 2.4M-term fp32 reduction) is ~1e-4 relative off it."""
+    net = OracleNet().to(dtype)
+    net.load_state_dict({k: v.to(dtype) for k, v in state_dict.items()})
     net.train(training)
+    x = x.to(dtype)
+    mask2d = None if mask2d is None else mask2d.to(dtype)
+    mask1d = None if mask1d is None else mask1d.to(dtype)
     logp = net(x, mask2d, mask1d)
     loss = F.nll_loss(logp, target)
     loss.backward()

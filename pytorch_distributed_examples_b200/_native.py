@@ -60,7 +60,11 @@ SIGNATURES = {
     "ddp_broadcast": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "ddp_state_snapshot": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "ddp_state_restore": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
+    "ddp_prof_enable": (c_int, [c_int]),
+    "ddp_prof_read": (c_int, [POINTER(c_float)]),
 }
+PROF_KERNELS = ("conv1_fwd", "conv2_fwd", "head_fwd", "head_bwd", "conv2_dgrad", "conv2_wgrad", "conv1_wgrad",
+                "reduce_partials")
 
 _DTYPES = {torch.float32: DT_F32, torch.bfloat16: DT_BF16, torch.int64: DT_I64, torch.uint8: DT_U8}
 
@@ -231,6 +235,16 @@ class Native:
         nbytes = device_arena.numel() * device_arena.element_size()
         self._check(self.lib.ddp_state_restore(_ptr(device_arena, "arena"), pinned_host.data_ptr(), nbytes,
                                                _stream()), "ddp_state_restore")
+
+
+    # -- per-kernel timing aid ----------------------------------------------------------------------
+    def prof_enable(self, on: bool):
+        self._check(self.lib.ddp_prof_enable(int(bool(on))), "ddp_prof_enable")
+
+    def prof_read(self):
+        ms = (c_float * len(PROF_KERNELS))()
+        self._check(self.lib.ddp_prof_read(ms), "ddp_prof_read")
+        return dict(zip(PROF_KERNELS, [float(v) for v in ms]))
 
 
 _INSTANCE = None

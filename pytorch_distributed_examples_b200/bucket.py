@@ -89,6 +89,8 @@ class BucketTable:
         self.chunk_start = torch.tensor(cstart, dtype=torch.int64, device=dev)
         self.nchunks = len(citem)
         self._key = key
+        self._tensors = list(tensors)                 # host-side mirror (kept alive; used by test doubles)
+        self._offsets_elems = list(layout.offsets)
         return self
 
 

@@ -32,9 +32,33 @@ int sm_count() {
   return cached[dev];
 }
 
+// events: 0 fwd start, 1 conv1_fwd, 2 conv2_fwd, 3 head_fwd, 4 bwd start, 5 head_bwd, 6 dgrad, 7 wgrad2, 8 wgrad1, 9 reduce
+static bool g_prof_on = false;
+static cudaEvent_t g_prof_ev[10];
+static bool g_prof_made = false;
+void prof_mark(int idx, cudaStream_t stream) {
+  if (!g_prof_on) return;
+  if (!g_prof_made) {
+    for (auto& e : g_prof_ev) cudaEventCreate(&e);
+    g_prof_made = true;
+  }
+  cudaEventRecord(g_prof_ev[idx], stream);
+}
+
 }  // namespace ddp
 
 using namespace ddp;
+
+extern "C" int ddp_prof_enable(int on) { g_prof_on = on != 0; return 0; }
+extern "C" int ddp_prof_read(float* ms_out) {
+  DDP_REQUIRE(ms_out, "ms_out is NULL");
+  DDP_REQUIRE(g_prof_made, "no profiled launch yet");
+  DDP_CUDA(cudaEventSynchronize(g_prof_ev[9]));
+  const int pairs[DDP_PROF_KERNELS][2] = {{0, 1}, {1, 2}, {2, 3}, {4, 5}, {5, 6}, {6, 7}, {7, 8}, {8, 9}};
+  for (int i = 0; i < DDP_PROF_KERNELS; ++i)
+    DDP_CUDA(cudaEventElapsedTime(&ms_out[i], g_prof_ev[pairs[i][0]], g_prof_ev[pairs[i][1]]));
+  return 0;
+}
 
 extern "C" int ddp_abi_version(void) { return DDP_ABI_VERSION; }
 extern "C" const char* ddp_last_error(void) { return g_err; }

@@ -96,6 +96,8 @@ int cuda_rc(cudaError_t e, const char* what);
   } while (0)
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 int sm_count();
+// per-kernel event timing (api.cu); mark(i) records event i on `stream` when profiling is on
+void prof_mark(int idx, cudaStream_t stream);
 
 // ---- Philox4x32-10 (counter-based; same constants as Random123 / curand) ------
 struct Philox4 { uint32_t x, y, z, w; };

@@ -553,18 +553,21 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
     attr_done = true;
   }
   int parts_head, parts_c2, parts_c1;
+  prof_mark(4, stream);
   {
     int ntiles = (B + HT - 1) / HT;
     parts_head = ntiles < sms ? ntiles : sms;
     head_bwd_kernel<<<parts_head, HB_THREADS, HB_SMEM, stream>>>(params, ws.a2, ws.h, logp, dlogp, target,
                                                                  nll_coef, drop_scale, sc.da2, sc.partials, B);
   }
+  prof_mark(5, stream);
   {
     int nblk = (B + D2_WARPS - 1) / D2_WARPS;
     int grid = nblk < sms ? nblk : sms;
     conv2_dgrad_kernel<<<grid, D2_THREADS, D2_SMEM, stream>>>(params, sc.da2, ws.a2, ws.idx2, ws.a1,
                                                              drop_scale, sc.dp1, B);
   }
+  prof_mark(6, stream);
   {
     int nstages = (B + W2_NS - 1) / W2_NS;
     parts_c2 = nstages < MAX_PARTS ? nstages : MAX_PARTS;
@@ -572,13 +575,16 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
     conv2_wgrad_kernel<<<parts_c2, W2_THREADS, 0, stream>>>(sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale,
                                                            sc.partials, B);
   }
+  prof_mark(7, stream);
   {
     parts_c1 = B < sms * 2 ? B : sms * 2;
     if (parts_c1 > MAX_PARTS) parts_c1 = MAX_PARTS;
     conv1_wgrad_kernel<<<parts_c1, W1_THREADS, 0, stream>>>(sc.dp1, ws.idx1, x, sc.partials, B);
   }
+  prof_mark(8, stream);
   reduce_partials_kernel<<<(P_ARENA + 31) / 32, 256, 0, stream>>>(sc.partials, parts_c1, parts_c2,
                                                                   parts_head, grad_bucket);
+  prof_mark(9, stream);
   DDP_CUDA(cudaGetLastError());
   return 0;
 }

@@ -384,17 +384,20 @@ extern "C" int ddp_net_forward(const float* params, const float* x, const int64_
     DDP_CUDA(cudaFuncSetAttribute(head_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HF_SMEM));
     attr_done = true;
   }
+  prof_mark(0, stream);
   {
     int npairs = (B + 1) / 2;
     int grid = npairs < sms * 2 ? npairs : sms * 2;
     conv1_fwd_kernel<<<grid, F1_THREADS, 0, stream>>>(params, x, ws.a1, ws.idx1, B);
   }
+  prof_mark(1, stream);
   {
     int ngroups = (B + F2_WARPS - 1) / F2_WARPS;
     int grid = ngroups < sms * 2 ? ngroups : sms * 2;
     conv2_fwd_kernel<<<grid, F2_THREADS, F2_SMEM, stream>>>(params, ws.a1, mask2d, seed, offset, offset_dev, training,
                                                           ws.a2, ws.idx2, B);
   }
+  prof_mark(2, stream);
   {
     int ntiles = (B + HT - 1) / HT;
     int grid = ntiles < sms ? ntiles : sms;
@@ -404,6 +407,7 @@ extern "C" int ddp_net_forward(const float* params, const float* x, const int64_
         params, ws.a2, target, mask1d, seed, offset, offset_dev, training, ws.h, out_logp, out_loss, out_argmax,
         reinterpret_cast<unsigned long long*>(out_correct), sc.loss_part, sc.counters, B);
   }
+  prof_mark(3, stream);
   DDP_CUDA(cudaGetLastError());
   return 0;
 }

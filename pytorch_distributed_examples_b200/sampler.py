@@ -51,12 +51,11 @@ class DistributedSampler(torch.utils.data.Sampler):
         """This rank's shard for the current epoch as an int64 CUDA tensor (no host round trip)."""
         n = len(self.dataset)
         nat = _native.get()
-        with torch.cuda.device(self.device):
-            if self._perm is None or self._perm.numel() < n:
-                self._perm = torch.empty(max(n, 1), dtype=torch.int32, device=self.device)
-            out = torch.empty(self.num_samples, dtype=torch.int64, device=self.device)
-            nat.sampler_indices(n, self.num_replicas, self.rank, self.shuffle, self.seed, self.epoch,
-                                self.drop_last, self._perm, out)
+        if self._perm is None or self._perm.numel() < n:
+            self._perm = torch.empty(max(n, 1), dtype=torch.int32, device=self.device)
+        out = torch.empty(self.num_samples, dtype=torch.int64, device=self.device)
+        nat.sampler_indices(n, self.num_replicas, self.rank, self.shuffle, self.seed, self.epoch,
+                            self.drop_last, self._perm, out)
         return out
 
     def __iter__(self):

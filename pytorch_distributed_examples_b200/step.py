@@ -10,6 +10,9 @@ latency dominate unless the step is fused and replayed.  Train
 captures it once, and replays it per batch.  zero_grad() is free (the bucket is overwritten).  Dropout masks
 come from Philox keyed by the device step counter, so replays draw fresh masks.
 Same arithmetic as the module path (`Net` + `hvd.DistributedOptimizer`), which stays the drop-in API.
+
+``slots`` > 1 keeps several resident input batches (one captured graph each) so a benchmark can rotate through
+more input bytes than the L2 holds.
 """
 from __future__ import annotations
 
@@ -19,9 +22,12 @@ from . import _native
 from .net import Net
 from .optim import FusedUpdater
 
+KERNELS_PER_STEP = 3 + 5 + 2   # forward, backward(+reduce), fused update + step counter
+
 
 class TrainStep:
-    def __init__(self, model: Net, optimizer, batch_size: int, communicator=None, use_graph: bool = True):
+    def __init__(self, model: Net, optimizer, batch_size: int, communicator=None, use_graph: bool = True,
+                 slots: int = 1):
         model._check_arena()
         self.model = model
         self.optimizer = optimizer
@@ -34,32 +40,38 @@ class TrainStep:
         self.batch = int(batch_size)
         dev = model.flat_params.device
         nat = _native.get()
-        self.x = torch.zeros(self.batch, 1, 28, 28, dtype=torch.float32, device=dev)
-        self.y = torch.zeros(self.batch, dtype=torch.int64, device=dev)
+        self.xs = [torch.zeros(self.batch, 1, 28, 28, dtype=torch.float32, device=dev) for _ in range(slots)]
+        self.ys = [torch.zeros(self.batch, dtype=torch.int64, device=dev) for _ in range(slots)]
         self.logp = torch.empty(self.batch, 10, dtype=torch.float32, device=dev)
         self.loss = torch.zeros(1, dtype=torch.float32, device=dev)
         self.ws = torch.empty(nat.workspace_bytes(self.batch), dtype=torch.uint8, device=dev)
         self.scratch = torch.zeros(nat.scratch_bytes(self.batch), dtype=torch.uint8, device=dev)
         self.use_graph = use_graph
-        self.graph = None
+        self.graphs = None
         self._fingerprint = None
-        self.kernel_launches_per_step = 0
+        self.kernel_launches_per_step = KERNELS_PER_STEP
+
+    @property
+    def x(self):
+        return self.xs[0]
+
+    @property
+    def y(self):
+        return self.ys[0]
 
     # -- one step's stream work ----------------------------------------------------------------------
-    def _enqueue(self):
+    def _enqueue(self, slot: int = 0):
         nat = _native.get()
         m, g = self.model, self.group
-        nat.net_forward(m._arena, self.x, self.y, None, None, m.dropout_seed, 0, True, self.ws, self.logp,
+        x, y = self.xs[slot], self.ys[slot]
+        nat.net_forward(m._arena, x, y, None, None, m.dropout_seed, 0, True, self.ws, self.logp,
                         out_loss=self.loss, scratch=self.scratch, offset_dev=g.step_dev)
-        nat.net_backward(m._arena, self.x, self.logp, None, self.y, 1.0, True, self.ws, self.scratch, m._grad_arena)
-        launches = 3 + 5
+        nat.net_backward(m._arena, x, self.logp, None, y, 1.0, True, self.ws, self.scratch, m._grad_arena)
         if self.world > 1:
             self.comm.allreduce_sum_(m._grad_arena)
         g.bucket = m._grad_arena
         g.adopted = True
         g.update(1.0 / self.world, use_step_dev=True)
-        launches += 2
-        self.kernel_launches_per_step = launches
 
     def _hyper_fingerprint(self):
         return tuple(sorted((k, str(v)) for k, v in self.group.group.items() if k != "params"))
@@ -75,7 +87,7 @@ class TrainStep:
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
             for _ in range(2):            # warm-up outside capture (sets func attributes, loads modules)
-                self._enqueue()
+                self._enqueue(0)
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         with torch.no_grad():             # undo the warm-up steps
@@ -83,30 +95,36 @@ class TrainStep:
             for s, k in zip((g.state1, g.state2), keep_s):
                 if s is not None:
                     s.copy_(k)
+        graphs = []
+        for slot in range(len(self.xs)):
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                self._enqueue(slot)
+            graphs.append(graph)
         g.steps = host_steps
-        graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(graph):
-            self._enqueue()
-        g.steps = host_steps
-        self.graph = graph
+        self.graphs = graphs
         self._fingerprint = self._hyper_fingerprint()
 
     # -- public --------------------------------------------------------------------------------------
-    def __call__(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
-        """Runs one step on (data [B,1,28,28], target [B]); returns the device loss tensor (no host sync).
-        Host tensors are accepted (pinned memory makes the copy asynchronous)."""
-        if data.shape[0] != self.batch:
-            raise RuntimeError(f"TrainStep was built for batch {self.batch}, got {data.shape[0]}")
-        if data.data_ptr() != self.x.data_ptr():
-            self.x.copy_(data.reshape(self.batch, 1, 28, 28), non_blocking=True)
-        if target.data_ptr() != self.y.data_ptr():
-            self.y.copy_(target, non_blocking=True)
+    def run_slot(self, slot: int = 0) -> torch.Tensor:
+        """One step on the batch already resident in ``xs[slot]`` / ``ys[slot]``."""
         if not self.use_graph:
-            self._enqueue()
+            self._enqueue(slot)
             return self.loss
-        if self.graph is None or self._fingerprint != self._hyper_fingerprint():
+        if self.graphs is None or self._fingerprint != self._hyper_fingerprint():
             self._capture()
-        self.graph.replay()
+        self.graphs[slot].replay()
         self.group.steps += 1
         self.group.graph_mode = True
         return self.loss
+
+    def __call__(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        """One step on (data [B,1,28,28], target [B]); returns the device loss tensor (no host sync).
+        Host tensors are accepted (pinned memory makes the copies asynchronous)."""
+        if data.shape[0] != self.batch:
+            raise RuntimeError(f"TrainStep was built for batch {self.batch}, got {data.shape[0]}")
+        if data.data_ptr() != self.xs[0].data_ptr():
+            self.xs[0].copy_(data.reshape(self.batch, 1, 28, 28), non_blocking=True)
+        if target.data_ptr() != self.ys[0].data_ptr():
+            self.ys[0].copy_(target, non_blocking=True)
+        return self.run_slot(0)

@@ -99,6 +99,8 @@ def test_fused_optimizer_wrapper_on_foreign_module(native):
         ropt.zero_grad(); crit(ref(x), y).backward(); ropt.step()
         fopt.zero_grad(); crit(mlp(x.cuda()), y.cuda()).backward(); fopt.step()
     for a, b in zip(mlp.parameters(), ref.parameters()):
-        assert_close_scaled(a, b.detach(), rtol=2e-5, name="mlp param")
+        # gradients here come from cuBLAS vs MKL; Adam amplifies their last-bit differences (see test_train_gpu)
+        err = (a.detach().cpu() - b.detach()).abs().max().item()
+        assert err <= 1e-5 * b.abs().max().item() + 1e-2 * 1e-3, err
     sd = fopt.state_dict()
     assert "exp_avg" in sd["state"][0] and float(sd["state"][0]["step"]) == 3.0
