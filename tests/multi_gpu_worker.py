@@ -1,0 +1,199 @@
+"""Multi-GPU checks, one rank per GPU (run under torchrun by tests/test_multi_gpu.py or by hand):
+    torchrun --nproc-per-node=2 --master-addr 127.0.0.1 --master-port 29541 tests/multi_gpu_worker.py
+Checks: native NCCL ring bootstrap; hvd.DistributedOptimizer on Net == real gloo DDP golden (W=2);
+stock DDP + allreduce_hook == hook-less DDP; FusedUpdateHook; TrainStep with the allreduce in the graph;
+elastic shrink/regrow with resharding; replicas bit-identical throughout."""
+import math
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE); sys.path.insert(0, os.path.dirname(HERE))
+
+from helpers import RTOL, load_golden  # noqa: E402
+
+
+def same_on_all_ranks(t, name):
+    lo, hi = t.clone(), t.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    assert torch.equal(lo, hi), f"{name}: replicas diverged"
+
+
+def main():
+    import pytorch_distributed_examples_b200 as pkg
+    from oracle import net_oracle
+    hvd = pkg.hvd
+    local = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    hvd.init()
+    W, R = hvd.size(), hvd.rank()
+    assert W == dist.get_world_size() and R == dist.get_rank()
+    log = lambda *a: print(f"[rank {R}]", *a, flush=True) if R == 0 else None
+
+    # 1. collectives through the C-ABI
+    t = torch.full((1000,), float(R + 1), device="cuda")
+    hvd.allreduce_(t, average=False)
+    assert torch.all(t == W * (W + 1) / 2)
+    b = torch.arange(10, device="cuda", dtype=torch.float32) * (R + 1)
+    hvd.broadcast_(b, root_rank=W - 1)
+    assert torch.equal(b, torch.arange(10, device="cuda", dtype=torch.float32) * W)
+    assert hvd.broadcast_object({"r": R}, root_rank=0) == {"r": 0}
+    log("collectives ok")
+
+    # 2. reference loop with hvd.DistributedOptimizer == real 2-process gloo DDP (golden), when W == 2
+    if W == 2:
+        fx = load_golden("ddp_gloo_w2.pt")
+        torch.manual_seed(100 + R)
+        model = pkg.Net().cuda().train()                       # ranks start different ...
+        if R == 0:
+            model.load_state_dict(fx["state_dict0"])
+        opt = hvd.DistributedOptimizer(torch.optim.SGD(model.parameters(), lr=0.01), named_parameters=model.named_parameters())
+        hvd.broadcast_parameters(model.state_dict(), root_rank=0)          # ... broadcast makes them equal
+        Bt = fx["xs"].shape[1] // W
+        sl = slice(R * Bt, (R + 1) * Bt)
+        for k in range(fx["xs"].shape[0]):
+            opt.zero_grad()
+            F.nll_loss(model(fx["xs"][k, sl].cuda(), fx["masks2d"][k, sl].cuda(), fx["masks1d"][k, sl].cuda()),
+                       fx["ys"][k, sl].cuda()).backward()
+            opt.step()
+        for key, v in model.state_dict().items():
+            ref = fx["state_dict"][key]
+            err = (v.cpu() - ref).abs().max().item()
+            assert err <= RTOL * ref.abs().max().item(), (key, err)
+        same_on_all_ranks(model.flat_params, "hvd path")
+        log("DistributedOptimizer == gloo DDP golden ok")
+
+    # 3. stock DDP + our hook == hook-less DDP (same seeds, same data)
+    from torch.nn.parallel import DistributedDataParallel as DDP
+
+    def ddp_run(hook):
+        torch.manual_seed(7)
+        m = pkg.Net().cuda().train(); m.dropout_seed = 5
+        d = DDP(m, device_ids=[local], gradient_as_bucket_view=True)
+        o = torch.optim.SGD(d.parameters(), lr=0.05)
+        if hook == "allreduce":
+            d.register_comm_hook(pkg.HookState(), pkg.allreduce_hook)
+        ds = pkg.SyntheticMNIST(length=4096, seed=3)
+        for k in range(4):
+            x, y = ds.batch(base_index=(k * W + R) * 32, count=32)
+            o.zero_grad()
+            F.nll_loss(d(x), y).backward()
+            o.step()
+        torch.cuda.synchronize()
+        return torch.cat([p.detach().reshape(-1) for p in m.parameters()]).clone()
+
+    base = ddp_run(None)
+    hooked = ddp_run("allreduce")
+    assert (hooked - base).abs().max().item() <= 1e-6 * base.abs().max().item(), "allreduce_hook != stock DDP"
+    same_on_all_ranks(hooked, "ddp hook")
+
+    # FusedUpdateHook on the DDP script's own model family (MLP of ref: mnist_ddp_elastic.py:133-159, Adam :173);
+    # (Net keeps its parameters in its own C-layout arena, so the optimizer-in-hook variant targets foreign modules)
+    def mlp_run(fused):
+        torch.manual_seed(8)
+        m = torch.nn.Sequential(torch.nn.Flatten(), torch.nn.Linear(784, 96), torch.nn.ReLU(), torch.nn.Linear(96, 96),
+                                torch.nn.ReLU(), torch.nn.Linear(96, 10)).cuda()
+        d = DDP(m, device_ids=[local], gradient_as_bucket_view=True)
+        o = torch.optim.Adam(d.parameters(), lr=1e-3)
+        if fused:
+            d.register_comm_hook(pkg.FusedUpdateHook.State(o), pkg.FusedUpdateHook.hook)
+        crit = torch.nn.CrossEntropyLoss()
+        ds = pkg.SyntheticMNIST(length=4096, seed=4)
+        for k in range(4):
+            x, y = ds.batch(base_index=(k * W + R) * 32, count=32)
+            o.zero_grad()
+            crit(d(x), y).backward()
+            if not fused:
+                o.step()
+        torch.cuda.synchronize()
+        return torch.cat([p.detach().reshape(-1) for p in m.parameters()]).clone()
+
+    mb, mf = mlp_run(False), mlp_run(True)
+    assert (mf - mb).abs().max().item() <= 1e-5 * mb.abs().max().item() + 1e-2 * 1e-3, "FusedUpdateHook != DDP + Adam"
+    same_on_all_ranks(mf, "fused hook")
+    log("DDP comm hooks ok")
+
+    # 4. TrainStep (allreduce captured in the CUDA graph) == module path
+    def run_steps(mode):
+        torch.manual_seed(21)
+        m = pkg.Net().cuda().train(); m.dropout_seed = 77
+        o = hvd.DistributedOptimizer(torch.optim.SGD(m.parameters(), lr=0.01, momentum=0.9))
+        ds = pkg.SyntheticMNIST(length=1 << 20, seed=9)
+        B = 256
+        step = pkg.TrainStep(m, o, B, communicator=hvd._require(), use_graph=True) if mode == "graph" else None
+        losses = []
+        for k in range(6):
+            x, y = ds.batch(base_index=(k * W + R) * B, count=B)
+            if step is not None:
+                losses.append(step(x, y).item())
+            else:
+                o.zero_grad(); loss = F.nll_loss(m(x), y); loss.backward(); o.step(); losses.append(loss.item())
+        return losses, m.flat_params.clone()
+
+    l_mod, p_mod = run_steps("module")
+    l_gr, p_gr = run_steps("graph")
+    assert max(abs(a - b) for a, b in zip(l_mod, l_gr)) <= 1e-5, (l_mod, l_gr)
+    assert (p_mod - p_gr).abs().max().item() <= 1e-6 * p_mod.abs().max().item()
+    same_on_all_ranks(p_gr, "TrainStep")
+    log("TrainStep with in-graph allreduce ok")
+
+    # 5. elastic: W -> W/2 -> W with commit/sync/LR-rescale and resharding (ref: horovod_mnist_elastic.py)
+    lr = 0.01
+    torch.manual_seed(5 + R)
+    model = pkg.Net().cuda().train()
+    opt = hvd.DistributedOptimizer(torch.optim.AdamW(model.parameters(), lr=lr / math.sqrt(hvd.size())),
+                                   named_parameters=model.named_parameters())
+    ds = pkg.SyntheticMNIST(length=60000, seed=1)
+    events = []
+    half = list(range(max(1, W // 2)))
+
+    def on_state_reset():
+        for g in opt.param_groups:
+            g["lr"] = lr / math.sqrt(hvd.size())
+        events.append(hvd.size())
+
+    @hvd.elastic.run
+    def train(state):
+        sampler = pkg.DistributedSampler(ds, num_replicas=hvd.size(), rank=hvd.rank())      # re-created after every reset
+        ref = torch.utils.data.distributed.DistributedSampler(range(60000), num_replicas=hvd.size(), rank=hvd.rank())
+        assert list(sampler)[:64] == list(ref)[:64]
+        loader = pkg.DeviceLoader(ds, 128, sampler)
+        for batch_idx, (x, y) in enumerate(loader):
+            if batch_idx >= 40:
+                break
+            if batch_idx < state.batch:
+                continue
+            opt.zero_grad(); F.nll_loss(model(x), y).backward(); opt.step()
+            if batch_idx == 9 and hvd.size() == W and state.phase == 0 and hvd.rank() == 0:
+                hvd.elastic.request_resize(half)
+            if batch_idx == 19 and hvd.size() == len(half) and hvd.rank() == 0 and W > 1:
+                hvd.elastic.request_resize(list(range(W)))
+            if batch_idx % 5 == 0:
+                state.phase = 1 if hvd.size() < W else state.phase
+                state.commit()
+            state.batch = batch_idx
+
+    state = hvd.elastic.TorchState(model, opt, batch=0, phase=0)
+    state.register_reset_callbacks([on_state_reset])
+    train(state)
+    if W > 1:
+        assert hvd.size() == W and events[-1] == W, events
+        assert abs(opt.param_groups[0]["lr"] - lr / math.sqrt(W)) < 1e-12
+        torch.cuda.synchronize()
+        same_on_all_ranks(model.flat_params, "elastic params")
+        for a in opt._fused.arenas():
+            same_on_all_ranks(a.float(), "elastic optimizer state")
+    log(f"elastic {W}->{len(half)}->{W} ok, reset sizes seen by rank 0: {events}")
+    dist.barrier()
+    dist.destroy_process_group()
+    if R == 0:
+        print("MULTI_GPU_OK", flush=True)
+
+
+if __name__ == "__main__":
+    main()
