@@ -143,6 +143,17 @@ int64_t ddp_sampler_num_samples(int64_t n, int world, int drop_last);
 int ddp_sampler_indices(int64_t n, int world, int rank, int shuffle, uint64_t seed,
                         uint64_t epoch, int drop_last, int32_t* perm_scratch,
                         int64_t* out, void* stream);
+/* Same result as ddp_sampler_indices, for hosts that have no device allocator to take perm_scratch
+ * from (all device memory already handed to a fixed pool, a plain-C caller, or a loop that cannot
+ * afford cudaMalloc's device-wide synchronisation).  It has no counterpart in the reference: it
+ * exists only because of that constraint.  The permutation scratch is a 256 KiB array built into
+ * the library (resident on every GPU that loads it, until exit), so n is limited to
+ * DDP_SAMPLER_STATIC_MAX_N; larger n is rejected with DDP_EINVAL and a message.  It allocates and
+ * frees nothing.  The first call on each device resolves the array's device address — issue it
+ * before any stream capture.  All calls share the array: do not let two calls overlap on the GPU. */
+#define DDP_SAMPLER_STATIC_MAX_N 65536
+int ddp_sampler_indices_static(int64_t n, int world, int rank, int shuffle, uint64_t seed,
+                               uint64_t epoch, int drop_last, int64_t* out, void* stream);
 
 /* ---- on-device synthetic 28x28 batch ----------------------------------------
  * replaces ref: horovod/mnist_horovod.py:34-38 (datasets.MNIST + ToTensor + Normalize),

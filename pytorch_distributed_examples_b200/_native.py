@@ -50,6 +50,7 @@ SIGNATURES = {
     "ddp_sampler_num_samples": (c_int64, [c_int64, c_int, c_int]),
     "ddp_sampler_indices": (c_int, [c_int64, c_int, c_int, c_int, c_uint64, c_uint64, c_int, c_void_p, c_void_p,
                                     c_void_p]),
+    "ddp_sampler_indices_static": (c_int, [c_int64, c_int, c_int, c_int, c_uint64, c_uint64, c_int, c_void_p, c_void_p]),
     "ddp_synth_batch": (c_int, [c_uint64, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
     "ddp_comm_unique_id": (c_int, [c_void_p]),
     "ddp_comm_init": (c_int, [POINTER(c_void_p), c_void_p, c_int, c_int]),
@@ -186,6 +187,14 @@ class Native:
                                           _ptr(perm_scratch, "perm_scratch", torch.int32),
                                           _ptr(out, "out", torch.int64), _stream())
         self._check(rc, "ddp_sampler_indices")
+
+    def sampler_indices_static(self, n, world, rank, shuffle, seed, epoch, drop_last, out):
+        """Shard indices without a caller-provided permutation buffer: for callers that cannot allocate device
+        memory.  Uses the 256 KiB scratch array built into the library (n <= 65536); calls must not overlap."""
+        rc = self.lib.ddp_sampler_indices_static(n, world, rank, int(bool(shuffle)), int(seed) & (2 ** 64 - 1),
+                                                 int(epoch) & (2 ** 64 - 1), int(bool(drop_last)),
+                                                 _ptr(out, "out", torch.int64), _stream())
+        self._check(rc, "ddp_sampler_indices_static")
 
     def synth_batch(self, seed, indices, base_index, batch, out_x, out_y):
         rc = self.lib.ddp_synth_batch(int(seed) & (2 ** 64 - 1), _ptr(indices, "indices", torch.int64),

@@ -153,3 +153,64 @@ extern "C" int ddp_sampler_indices(int64_t n, int world, int rank, int shuffle, 
   DDP_CUDA(cudaGetLastError());
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------------
+// ddp_sampler_indices_static: the same shard-index computation for callers that cannot allocate.
+//
+// ddp_sampler_indices needs a caller-provided permutation buffer of n int32.  Some hosts have no way to
+// give it one: a data-feeding thread that runs after the application has handed every byte of device
+// memory to its own fixed pool, a plain-C program that links this library without bringing an allocator,
+// or a loop that must not pay the device-wide synchronisation cudaMalloc/cudaFree imply.  For them the
+// permutation lives in the array below, which is part of the library image: every GPU that loads the
+// library carries these 256 KiB until the process exits, and nothing is allocated or freed here or in
+// anything this function calls.
+//
+// The array name is only a host-side handle.  Its device address is looked up once per device with
+// cudaGetSymbolAddress while that device is current (the first call on each device does this, so make
+// that first call before starting any stream capture) and the kernels are handed that address.
+// All calls share the one array and it keeps whatever the previous call left in it; the permutation
+// kernel rewrites all n entries before reading any, so nothing needs clearing — but two calls whose GPU
+// work overlaps (different streams, or different host threads) race on it: serialise them.
+// ---------------------------------------------------------------------------------------------------
+static __device__ __align__(256) int32_t g_static_perm[DDP_SAMPLER_STATIC_MAX_N];
+
+extern "C" int ddp_sampler_indices_static(int64_t n, int world, int rank, int shuffle, uint64_t seed,
+                                          uint64_t epoch, int drop_last, int64_t* out, void* stream_) {
+  DDP_REQUIRE(n >= 1, "dataset length must be >= 1");
+  if (n > DDP_SAMPLER_STATIC_MAX_N) {
+    set_error("ddp_sampler_indices_static: dataset length %lld exceeds the built-in scratch of %d entries; "
+              "use ddp_sampler_indices with a caller-provided perm_scratch",
+              (long long)n, DDP_SAMPLER_STATIC_MAX_N);
+    return DDP_EINVAL;
+  }
+  DDP_REQUIRE(world >= 1 && rank >= 0 && rank < world, "bad world/rank");
+  DDP_REQUIRE(out, "null output");
+  static_assert(DDP_SAMPLER_STATIC_MAX_N <= RP_SMEM_MAX_N, "static scratch must fit the shared-memory path");
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+
+  // per-device set-up: resolve the device address of the scratch array, opt the kernel into large smem
+  static int32_t* dev_ptr[64] = {nullptr};
+  int dev = -1;
+  DDP_CUDA(cudaGetDevice(&dev));
+  DDP_REQUIRE(dev >= 0 && dev < 64, "device ordinal out of range");
+  if (dev_ptr[dev] == nullptr) {
+    int32_t* p = nullptr;
+    DDP_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_static_perm));
+    DDP_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null address");
+    DDP_CUDA(cudaFuncSetAttribute(randperm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  int(3 * MT_N * 4 + RP_SMEM_MAX_N * 2)));
+    dev_ptr[dev] = p;
+  }
+  int32_t* perm = dev_ptr[dev];
+
+  const int64_t num_samples = ddp_sampler_num_samples(n, world, drop_last);
+  if (shuffle) {
+    const uint32_t seed32 = uint32_t((seed + epoch) & 0xffffffffu);
+    const int smem = int(3 * MT_N * 4 + ((n * 2 + 15) & ~int64_t(15)));
+    randperm_kernel<true><<<1, RP_THREADS, smem, stream>>>(n, seed32, perm);
+  }
+  if (num_samples > 0)
+    shard_kernel<<<int((num_samples + 255) / 256), 256, 0, stream>>>(perm, n, world, rank, num_samples, shuffle, out);
+  DDP_CUDA(cudaGetLastError());
+  return 0;
+}
