@@ -18,8 +18,7 @@ constexpr int HB_THREADS = 320;
 constexpr int HB_A2S = 324;   // a2 tile row stride
 constexpr int HB_DPS = 36;    // dpT row stride ([j][s])
 constexpr int HB_HS = 53;     // h tile row stride
-constexpr int HB_SMEM =
-    (F1 * A2_PER + HT * HB_A2S + F1 * HB_DPS + HT * 12 + HT * HB_HS + NC * 52) * 4;
+constexpr int HB_SMEM = (HT * HB_A2S + F1 * HB_DPS + HT * 12 + HT * HB_HS + NC * 52) * 4;
 __global__ void __launch_bounds__(HB_THREADS, 1)
 head_bwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
                 const float* __restrict__ h, const float* __restrict__ logp,
@@ -27,15 +26,13 @@ head_bwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
                 float nll_coef, float drop_scale, float* __restrict__ da2,
                 float* __restrict__ partials, int B) {
   extern __shared__ __align__(16) float smem[];
-  float* w1_s = smem;                     // [50][320] natural layout
-  float* a2_s = w1_s + F1 * A2_PER;       // [32][324]
+  const float* w1g = params + OFF_F1W;    // [50][320], read through L1 (ld.global.nc), not staged
+  float* a2_s = smem;                     // [32][324]
   float* dp_s = a2_s + HT * HB_A2S;       // [50][36]  dL/d(fc1 pre-activation), transposed
   float* dz_s = dp_s + F1 * HB_DPS;       // [32][12]
   float* h_s = dz_s + HT * 12;            // [32][53]
   float* w2_s = h_s + HT * HB_HS;         // [10][52]
   const int tid = threadIdx.x;
-  for (int i = tid; i < F1 * A2_PER / 4; i += HB_THREADS)
-    reinterpret_cast<float4*>(w1_s)[i] = *reinterpret_cast<const float4*>(params + OFF_F1W + i * 4);
   for (int i = tid; i < NC * 52; i += HB_THREADS) {
     int c = i / 52, j = i % 52;
     w2_s[i] = j < F1 ? params[OFF_F2W + c * F1 + j] : 0.f;
@@ -149,8 +146,8 @@ head_bwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
 #pragma unroll 2
       for (int j = 0; j < F1; ++j) {
         float4 d = *reinterpret_cast<const float4*>(dp_s + j * HB_DPS + sgD * 4);
-        float4 wa = *reinterpret_cast<const float4*>(w1_s + j * A2_PER + igD * 4);
-        float4 wb = *reinterpret_cast<const float4*>(w1_s + j * A2_PER + 160 + igD * 4);
+        float4 wa = __ldg(reinterpret_cast<const float4*>(w1g + j * A2_PER + igD * 4));
+        float4 wb = __ldg(reinterpret_cast<const float4*>(w1g + j * A2_PER + 160 + igD * 4));
         float dv[4] = {d.x, d.y, d.z, d.w};
         float wv[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
 #pragma unroll
@@ -225,13 +222,19 @@ conv2_dgrad_kernel(const float* __restrict__ params, const float* __restrict__ d
   const int pbase = (3 * ty - 4) * O2 + (3 * tx - 4);
   const int total_warps = gridDim.x * D2_WARPS;
   for (int b = blockIdx.x * D2_WARPS + warp; b < B; b += total_warps) {
-    // rebuild dy2: 320 (co,pp) entries, 10 per lane, each a 2x2 block with one non-zero
+    // rebuild dy2: 320 (co,pp) entries, 10 per lane, each a 2x2 block with one non-zero.
+    // live_mask bit co: the channel has any gradient for this sample (Dropout2d zeroes ~half of the
+    // channels, ReLU some more) -- dead channels are skipped, a warp-uniform branch.
+    unsigned live_mask = 0u;
 #pragma unroll
     for (int q = 0; q < 10; ++q) {
       const int e = lane + 32 * q;               // = co*16 + pp
       const size_t o = size_t(b) * A2_PER + e;
       const float gv = a2[o] > 0.f ? da2[o] * drop_scale : 0.f;
       const int id = idx2[o];
+      const unsigned bal = __ballot_sync(0xffffffffu, gv != 0.f);
+      live_mask |= ((bal & 0xffffu) ? 1u : 0u) << (2 * q);
+      live_mask |= ((bal >> 16) ? 1u : 0u) << (2 * q + 1);
       const int co = e >> 4, pp = e & 15, py = pp >> 2, px = pp & 3;
       float* d = dy_s + co * 64 + (2 * py) * O2 + 2 * px;
       *reinterpret_cast<float2*>(d) = make_float2(id == 0 ? gv : 0.f, id == 1 ? gv : 0.f);
@@ -247,6 +250,7 @@ conv2_dgrad_kernel(const float* __restrict__ params, const float* __restrict__ d
         for (int k = 0; k < 5; ++k) acc[a][c][k] = 0.f;
 #pragma unroll 1
     for (int co = 0; co < C2; ++co) {
+      if (!((live_mask >> co) & 1u)) continue;
       float patch[7][7];
       const float* dp = dy_s + co * 64 + pbase;
 #pragma unroll
@@ -308,8 +312,11 @@ conv2_wgrad_kernel(const float* __restrict__ da2, const float* __restrict__ a2,
   __shared__ __align__(16) float a1_s[W2_NS * A1_PER];
   __shared__ __align__(16) float dy_s[W2_NS * W2_DYS];
   __shared__ float bsum_s[A2_PER];
+  __shared__ int live_s[W2_NS * C2];   // (sample, co) has any gradient: dead channels are skipped
   const int tid = threadIdx.x;
-  const int cq = tid % 5, kh = (tid / 5) % 5, ci = tid / 25;  // ci < 10 for tid < 250
+  // cq (output-channel residue mod 5) is the SLOWEST index so that a warp is (almost) uniform in co
+  // and the dead-channel skip below is (almost) divergence-free
+  const int cq = tid / 50, kh = tid % 5, ci = (tid % 50) / 5;   // cq < 5 for tid < 250
   const bool active = tid < 250;
   float acc[4][5];
 #pragma unroll
@@ -335,6 +342,8 @@ conv2_wgrad_kernel(const float* __restrict__ da2, const float* __restrict__ a2,
           const int id = idx2[o];
           const int co = e >> 4, pp = e & 15, py = pp >> 2, px = pp & 3;
           bacc[q] += gv;
+          const unsigned bal = __ballot_sync(0xffffffffu, gv != 0.f);   // e < 320 is warp-uniform here
+          if ((tid & 15) == 0) live_s[s * C2 + co] = ((bal >> (tid & 16)) & 0xffffu) != 0u;
           float* d = dy_s + s * W2_DYS + (2 * py) * (C2 * O2) + co * O2 + 2 * px;
           *reinterpret_cast<float2*>(d) = make_float2(id == 0 ? gv : 0.f, id == 1 ? gv : 0.f);
           *reinterpret_cast<float2*>(d + C2 * O2) = make_float2(id == 2 ? gv : 0.f, id == 3 ? gv : 0.f);
@@ -346,6 +355,10 @@ conv2_wgrad_kernel(const float* __restrict__ da2, const float* __restrict__ a2,
       for (int s = 0; s < nvalid; ++s) {
         const float* ab = a1_s + s * A1_PER + ci * 144 + kh * P1;
         const float* db = dy_s + s * W2_DYS + cq * O2;
+        bool lv[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) lv[j] = live_s[s * C2 + cq + 5 * j] != 0;
+        if (!(lv[0] || lv[1] || lv[2] || lv[3])) continue;
 #pragma unroll 2
         for (int oy = 0; oy < O2; ++oy) {
           float a[12];
@@ -356,6 +369,7 @@ conv2_wgrad_kernel(const float* __restrict__ da2, const float* __restrict__ a2,
           }
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
+            if (!lv[j]) continue;
             const float* dr = db + oy * (C2 * O2) + j * 5 * O2;
             float4 d0 = *reinterpret_cast<const float4*>(dr);
             float4 d1 = *reinterpret_cast<const float4*>(dr + 4);

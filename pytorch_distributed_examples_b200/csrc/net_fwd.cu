@@ -184,15 +184,16 @@ conv2_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a1,
 }
 
 // ---------------------------------------------------------------------------
-// K_F3: head.  Tile of 32 samples per CTA iteration; thread (sg,jg) computes
-// 2 samples x 4 fc1 outputs; W1 transposed in smem [k][52].
+// K_F3: head.  Tile of 16 samples per CTA iteration (several CTAs per SM); thread (sg,jg)
+// computes 2 samples x 4 fc1 outputs.  fc1.weight (64 KB) is read through L1 with ld.global.nc
+// (2-4 distinct 16-byte addresses per warp instruction, shared by every CTA on the SM) instead
+// of being staged per CTA; only the a2 tile and the small fc2 operands live in shared memory.
 // ---------------------------------------------------------------------------
-constexpr int HT = 32;              // samples per tile
-constexpr int HF_THREADS = 224;     // 16 sample-pairs x 13 output-quads = 208 active
+constexpr int HT = 16;              // samples per tile
+constexpr int HF_THREADS = 128;     // 8 sample-pairs x 13 output-quads = 104 active
 constexpr int HF_A2S = 324;         // a2 row stride (floats)
 constexpr int HF_HS = 53;           // h row stride
-constexpr int HF_SMEM = (320 * 52 + HT * HF_A2S + 52 + HT * HF_HS + 50 * 12 + 12 + HT * 12 + HT) * 4;
-__global__ void __launch_bounds__(HF_THREADS, 1)
+__global__ void __launch_bounds__(HF_THREADS, 4)
 head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
                 const int64_t* __restrict__ target, const float* __restrict__ mask1d,
                 uint64_t seed, uint64_t offset, const int64_t* __restrict__ offset_dev, int training,
@@ -200,22 +201,14 @@ head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
                 float* __restrict__ logp_out, float* __restrict__ loss_out,
                 int64_t* __restrict__ argmax_out, unsigned long long* __restrict__ correct_out,
                 float* __restrict__ loss_part, unsigned int* __restrict__ counters, int B) {
-  extern __shared__ __align__(16) float smem[];
-  float* w1_s = smem;                    // [320][52]
-  float* a2_s = w1_s + 320 * 52;         // [32][324]
-  float* b1_s = a2_s + HT * HF_A2S;      // [52]
-  float* h_s = b1_s + 52;                // [32][53]
-  float* w2_s = h_s + HT * HF_HS;        // [50][12]
-  float* b2_s = w2_s + 50 * 12;          // [12]
-  float* z_s = b2_s + 12;                // [32][12]
-  float* nll_s = z_s + HT * 12;          // [32]
+  __shared__ __align__(16) float a2_s[HT * HF_A2S];   // [16][324]
+  __shared__ float b1_s[52];
+  __shared__ float h_s[HT * HF_HS];                   // [16][53]
+  __shared__ __align__(16) float w2_s[50 * 12];       // [k][c padded to 12]
+  __shared__ float b2_s[12];
+  __shared__ float z_s[HT * 12];
   if (offset_dev) offset += uint64_t(*offset_dev);
   const int tid = threadIdx.x;
-  for (int i = tid; i < F1 * A2_PER; i += HF_THREADS) {
-    int j = i / A2_PER, k = i % A2_PER;
-    w1_s[k * 52 + j] = params[OFF_F1W + i];
-  }
-  for (int i = tid; i < 320 * 2; i += HF_THREADS) w1_s[(i >> 1) * 52 + 50 + (i & 1)] = 0.f;
   if (tid < 52) b1_s[tid] = tid < F1 ? params[OFF_F1B + tid] : 0.f;
   for (int i = tid; i < 50 * 12; i += HF_THREADS) {
     int k = i / 12, c = i % 12;
@@ -223,7 +216,11 @@ head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
   }
   if (tid < 12) b2_s[tid] = tid < NC ? params[OFF_F2B + tid] : 0.f;
 
-  const int sg = tid & 15, jg = tid >> 4;  // jg < 13 active
+  const int sg = tid & 7, jg = tid >> 3;   // jg < 13 active
+  const float* w1g = params + OFF_F1W;
+  int jrow[4];
+#pragma unroll
+  for (int jj = 0; jj < 4; ++jj) jrow[jj] = min(jg * 4 + jj, F1 - 1) * A2_PER;   // clamp: cols 50,51 are discarded
   const int ntiles = (B + HT - 1) / HT;
   float loss_acc = 0.f;                    // thread 0 only
   int corr_acc = 0;
@@ -231,7 +228,6 @@ head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
     const int b0 = tile * HT;
     const int nvalid = min(HT, B - b0);
     __syncthreads();
-    // stage a2 tile (zero-fill rows past the batch)
     for (int i = tid; i < HT * (A2_PER / 4); i += HF_THREADS) {
       int s = i / (A2_PER / 4), k4 = i % (A2_PER / 4);
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -244,28 +240,25 @@ head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
 #pragma unroll
       for (int i = 0; i < 2; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+        for (int jj = 0; jj < 4; ++jj) acc[i][jj] = 0.f;
       const float* ar0 = a2_s + sg * HF_A2S;
-      const float* ar1 = a2_s + (sg + 16) * HF_A2S;
-      const float* wr = w1_s + jg * 4;
+      const float* ar1 = a2_s + (sg + 8) * HF_A2S;
 #pragma unroll 4
       for (int k = 0; k < A2_PER; k += 4) {
         float4 x0 = *reinterpret_cast<const float4*>(ar0 + k);
         float4 x1 = *reinterpret_cast<const float4*>(ar1 + k);
-        float xa[4] = {x0.x, x0.y, x0.z, x0.w};
-        float xb[4] = {x1.x, x1.y, x1.z, x1.w};
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk) {
-          float4 w = *reinterpret_cast<const float4*>(wr + (k + kk) * 52);
-          acc[0][0] = fmaf(xa[kk], w.x, acc[0][0]); acc[0][1] = fmaf(xa[kk], w.y, acc[0][1]);
-          acc[0][2] = fmaf(xa[kk], w.z, acc[0][2]); acc[0][3] = fmaf(xa[kk], w.w, acc[0][3]);
-          acc[1][0] = fmaf(xb[kk], w.x, acc[1][0]); acc[1][1] = fmaf(xb[kk], w.y, acc[1][1]);
-          acc[1][2] = fmaf(xb[kk], w.z, acc[1][2]); acc[1][3] = fmaf(xb[kk], w.w, acc[1][3]);
+        for (int jj = 0; jj < 4; ++jj) {
+          float4 w = __ldg(reinterpret_cast<const float4*>(w1g + jrow[jj] + k));
+          acc[0][jj] = fmaf(x0.x, w.x, acc[0][jj]); acc[0][jj] = fmaf(x0.y, w.y, acc[0][jj]);
+          acc[0][jj] = fmaf(x0.z, w.z, acc[0][jj]); acc[0][jj] = fmaf(x0.w, w.w, acc[0][jj]);
+          acc[1][jj] = fmaf(x1.x, w.x, acc[1][jj]); acc[1][jj] = fmaf(x1.y, w.y, acc[1][jj]);
+          acc[1][jj] = fmaf(x1.z, w.z, acc[1][jj]); acc[1][jj] = fmaf(x1.w, w.w, acc[1][jj]);
         }
       }
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
-        const int s = sg + 16 * i;
+        const int s = sg + 8 * i;
         const int b = b0 + s;
 #pragma unroll
         for (int jj = 0; jj < 4; ++jj) {
@@ -298,7 +291,7 @@ head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
       z_s[s * 12 + c2] = z0; z_s[s * 12 + c2 + 1] = z1;
     }
     __syncthreads();
-    if (tid < HT) {
+    if (tid < 32) {                        // warp 0: lanes 0..15 hold the tile's samples
       const int s = tid;
       float nll = 0.f; int ok = 0;
       if (s < nvalid) {
@@ -332,9 +325,7 @@ head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
           ok = (am == t);
         }
       }
-      nll_s[s] = nll;
-      // warp 0 holds all 32 samples of the tile: fixed-order shuffle tree
-      float v = nll;
+      float v = nll;                       // fixed-order shuffle tree
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
       int okc = __popc(__ballot_sync(0xffffffffu, ok));
@@ -381,7 +372,6 @@ extern "C" int ddp_net_forward(const float* params, const float* x, const int64_
   static bool attr_done = false;
   if (!attr_done) {
     DDP_CUDA(cudaFuncSetAttribute(conv2_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, F2_SMEM));
-    DDP_CUDA(cudaFuncSetAttribute(head_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HF_SMEM));
     attr_done = true;
   }
   prof_mark(0, stream);
@@ -400,10 +390,10 @@ extern "C" int ddp_net_forward(const float* params, const float* x, const int64_
   prof_mark(2, stream);
   {
     int ntiles = (B + HT - 1) / HT;
-    int grid = ntiles < sms ? ntiles : sms;
+    int grid = ntiles < MAX_PARTS ? ntiles : MAX_PARTS;   // one loss partial per CTA
     Scratch sc{};
     if (scratch) sc = carve_scratch(scratch, batch);
-    head_fwd_kernel<<<grid, HF_THREADS, HF_SMEM, stream>>>(
+    head_fwd_kernel<<<grid, HF_THREADS, 0, stream>>>(
         params, ws.a2, target, mask1d, seed, offset, offset_dev, training, ws.h, out_logp, out_loss, out_argmax,
         reinterpret_cast<unsigned long long*>(out_correct), sc.loss_part, sc.counters, B);
   }

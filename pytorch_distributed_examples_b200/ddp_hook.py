@@ -11,7 +11,6 @@ kernel, completed as a CUDA-aware Future so DDP's finalize_backward stream-syncs
 distributed/algorithms/ddp_comm_hooks/optimizer_overlap_hooks.py:50-128): after the allreduce it runs the
 fused (1/N)*g + optimizer update straight from the bucket, so ``optimizer.step()`` becomes a no-op.
 """
-from __future__ import annotations
 
 import torch
 import torch.distributed as dist
@@ -58,57 +57,73 @@ def allreduce_hook(state: HookState, bucket: dist.GradBucket) -> torch.futures.F
 
 
 class FusedUpdateHook:
-    """``ddp.register_comm_hook(FusedUpdateHook.State(comm, optimizer), FusedUpdateHook.hook)``.
-    Parameters of each bucket are re-homed (once) into a flat arena packed exactly like DDP packs the
-    bucket, so the update kernel walks bucket and parameters with the same index."""
+    """``ddp.register_comm_hook(FusedUpdateHook.State(optimizer), FusedUpdateHook.hook)``.
+    Parameters of each bucket are re-homed into a flat arena packed exactly like DDP packs the bucket, so
+    the update kernel walks bucket and parameters with the same index.  DDP rebuilds its buckets after the
+    first iteration (backward order); optimizer state is therefore tracked per PARAMETER and carried into
+    the new packing when a bucket's composition changes."""
 
     class State(HookState):
         def __init__(self, optimizer: torch.optim.Optimizer, communicator=None, device=None):
             super().__init__(communicator, device)
             self.optimizer = optimizer
             self.kind = optimizer_kind(optimizer)
-            self.buckets = {}   # bucket index -> dict(arena, state1, state2, steps, group)
+            self.buckets = {}       # bucket index -> dict(key, arena, state1, state2, shell)
+            self.param_state = {}   # id(param) -> (state1 view, state2 view)
+            self.iteration = 0      # completed backward passes == optimizer steps taken
 
     @staticmethod
     def _prepare(state, bucket):
+        from .optim import _Group
         params = bucket.parameters()
         total = bucket.buffer().numel()
-        arena = torch.zeros(total, dtype=torch.float32, device=state.device)
-        off = 0
         group = None
+        for p in params:
+            for g in state.optimizer.param_groups:
+                if any(p is q for q in g["params"]):
+                    if group is not None and g is not group:
+                        raise RuntimeError("a DDP bucket spans several optimizer param groups")
+                    group = g
+        shell = _Group.__new__(_Group)      # reuse hyper()/needs_state() on a bare group
+        shell.group, shell.kind = group, state.kind
+        n1, n2 = shell.needs_state()
+        arena = torch.zeros(total, dtype=torch.float32, device=state.device)
+        s1 = torch.zeros_like(arena) if n1 else None
+        s2 = torch.zeros_like(arena) if n2 else None
+        off = 0
         with torch.no_grad():
             for p in params:
                 n = p.numel()
                 arena[off:off + n].copy_(p.data.reshape(-1))
                 p.data = arena[off:off + n].view(p.shape)
+                old = state.param_state.get(id(p))
+                if old is not None:             # carry optimizer state across DDP's bucket rebuild
+                    if s1 is not None and old[0] is not None:
+                        s1[off:off + n].copy_(old[0])
+                    if s2 is not None and old[1] is not None:
+                        s2[off:off + n].copy_(old[1])
+                state.param_state[id(p)] = (s1[off:off + n] if s1 is not None else None,
+                                            s2[off:off + n] if s2 is not None else None)
                 off += n
-                for g in state.optimizer.param_groups:
-                    if any(p is q for q in g["params"]):
-                        if group is not None and g is not group:
-                            raise RuntimeError("a DDP bucket spans several optimizer param groups")
-                        group = g
-        from .optim import _Group
-        shell = _Group.__new__(_Group)      # reuse hyper()/needs_state() on a bare group
-        shell.group, shell.kind = group, state.kind
-        n1, n2 = shell.needs_state()
-        return dict(arena=arena, shell=shell, steps=0,
-                    state1=torch.zeros_like(arena) if n1 else None,
-                    state2=torch.zeros_like(arena) if n2 else None)
+        return dict(key=tuple(id(p) for p in params), arena=arena, shell=shell, state1=s1, state2=s2)
 
     @staticmethod
     def hook(state, bucket: dist.GradBucket) -> torch.futures.Future[torch.Tensor]:
         buf = bucket.buffer()
         idx = bucket.index()
-        if idx not in state.buckets or state.buckets[idx]["arena"].numel() != buf.numel():
+        key = tuple(id(p) for p in bucket.parameters())
+        if idx not in state.buckets or state.buckets[idx]["key"] != key:
             state.buckets[idx] = FusedUpdateHook._prepare(state, bucket)
         b = state.buckets[idx]
         world = state.comm.world
+        step = state.iteration + 1
+        if bucket.is_last():
+            state.iteration += 1
 
         def body():
             state.comm.allreduce_sum_(buf)
-            b["steps"] += 1
             hyper = b["shell"].hyper(write_back=True)   # leave the averaged gradient in the bucket for DDP
             _native.get().fused_update(state.kind, buf, b["arena"], b["state1"], b["state2"], buf.numel(),
-                                       1.0 / world, hyper, step=b["steps"])
+                                       1.0 / world, hyper, step=step)
 
         return _run_on_comm_stream(state, buf, body)

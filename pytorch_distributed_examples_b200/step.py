@@ -46,6 +46,9 @@ class TrainStep:
         self.loss = torch.zeros(1, dtype=torch.float32, device=dev)
         self.ws = torch.empty(nat.workspace_bytes(self.batch), dtype=torch.uint8, device=dev)
         self.scratch = torch.zeros(nat.scratch_bytes(self.batch), dtype=torch.uint8, device=dev)
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self._staged = [None] * slots      # event: H2D copy into the slot finished
+        self._consumed = [None] * slots    # event: last step that read the slot finished
         self.use_graph = use_graph
         self.graphs = None
         self._fingerprint = None
@@ -106,16 +109,36 @@ class TrainStep:
         self._fingerprint = self._hyper_fingerprint()
 
     # -- public --------------------------------------------------------------------------------------
+    def stage(self, slot: int, data: torch.Tensor, target: torch.Tensor):
+        """Prefetch a (pinned) host batch into ``slot`` on the copy stream while earlier steps compute —
+        what DataLoader(pin_memory=True) + non_blocking copies do in the reference-style loop."""
+        cs = self.copy_stream
+        if self._consumed[slot] is not None:
+            cs.wait_event(self._consumed[slot])
+        with torch.cuda.stream(cs):
+            self.xs[slot].copy_(data.reshape(self.batch, 1, 28, 28), non_blocking=True)
+            self.ys[slot].copy_(target, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(cs)
+        self._staged[slot] = ev
+
     def run_slot(self, slot: int = 0) -> torch.Tensor:
-        """One step on the batch already resident in ``xs[slot]`` / ``ys[slot]``."""
+        """One step on the batch resident (or being staged) in ``xs[slot]`` / ``ys[slot]``."""
+        if self.use_graph and (self.graphs is None or self._fingerprint != self._hyper_fingerprint()):
+            self._capture()
+        if self._staged[slot] is not None:
+            torch.cuda.current_stream().wait_event(self._staged[slot])
+            self._staged[slot] = None
         if not self.use_graph:
             self._enqueue(slot)
-            return self.loss
-        if self.graphs is None or self._fingerprint != self._hyper_fingerprint():
-            self._capture()
-        self.graphs[slot].replay()
-        self.group.steps += 1
-        self.group.graph_mode = True
+        else:
+            self.graphs[slot].replay()
+            self.group.steps += 1
+            self.group.graph_mode = True
+        if len(self.xs) > 1:
+            ev = torch.cuda.Event()
+            ev.record()
+            self._consumed[slot] = ev
         return self.loss
 
     def __call__(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
