@@ -163,6 +163,15 @@ int ddp_sampler_indices_static(int64_t n, int world, int rank, int shuffle, uint
  * base_index + b.                                                             */
 int ddp_synth_batch(uint64_t seed, const int64_t* indices, int64_t base_index,
                     int64_t batch, float* out_x, int64_t* out_y, void* stream);
+/* The same samples as raw uint8 pixels [B,784] (MNIST's on-disk format, what datasets.MNIST holds
+ * before its transform runs; ref: horovod/mnist_horovod.py:38).                                   */
+int ddp_synth_batch_u8(uint64_t seed, const int64_t* indices, int64_t base_index,
+                       int64_t batch, uint8_t* out_px, int64_t* out_y, void* stream);
+/* transforms.ToTensor() + transforms.Normalize((mean,), (std,)) on the device
+ * (ref: horovod/mnist_horovod.py:34-37; horovod_mnist_elastic.py:45-48; mnist_ddp_elastic.py:166-169):
+ * out[i] = (in[i]/255 - mean)/std in IEEE fp32, bit-identical to torchvision's op order.  Lets a
+ * host feed uint8 batches (4x fewer PCIe bytes than fp32) — in/out 16-byte aligned.               */
+int ddp_normalize_u8(const uint8_t* in, float* out, int64_t n, float mean, float stdv, void* stream);
 
 /* ---- collectives over NCCL / NVLink -----------------------------------------
  * ref: pytorch_elastic/mnist_ddp_elastic.py:26,58 (gloo process group + DDP allreduce);

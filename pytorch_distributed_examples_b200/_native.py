@@ -52,6 +52,8 @@ SIGNATURES = {
                                     c_void_p]),
     "ddp_sampler_indices_static": (c_int, [c_int64, c_int, c_int, c_int, c_uint64, c_uint64, c_int, c_void_p, c_void_p]),
     "ddp_synth_batch": (c_int, [c_uint64, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
+    "ddp_synth_batch_u8": (c_int, [c_uint64, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
+    "ddp_normalize_u8": (c_int, [c_void_p, c_void_p, c_int64, c_float, c_float, c_void_p]),
     "ddp_comm_unique_id": (c_int, [c_void_p]),
     "ddp_comm_init": (c_int, [POINTER(c_void_p), c_void_p, c_int, c_int]),
     "ddp_comm_destroy": (c_int, [c_void_p]),
@@ -201,6 +203,20 @@ class Native:
                                       int(base_index), int(batch), _ptr(out_x, "out_x", torch.float32),
                                       _ptr(out_y, "out_y", torch.int64), _stream())
         self._check(rc, "ddp_synth_batch")
+
+    def synth_batch_u8(self, seed, indices, base_index, batch, out_px, out_y):
+        rc = self.lib.ddp_synth_batch_u8(int(seed) & (2 ** 64 - 1), _ptr(indices, "indices", torch.int64),
+                                         int(base_index), int(batch), _ptr(out_px, "out_px", torch.uint8),
+                                         _ptr(out_y, "out_y", torch.int64), _stream())
+        self._check(rc, "ddp_synth_batch_u8")
+
+    def normalize_u8(self, pixels, out, mean=0.1307, std=0.3081):
+        """ToTensor + Normalize on the device: out = (u8/255 - mean)/std."""
+        if out.numel() != pixels.numel():
+            raise RuntimeError("normalize_u8: size mismatch")
+        rc = self.lib.ddp_normalize_u8(_ptr(pixels, "pixels", torch.uint8), _ptr(out, "out", torch.float32),
+                                       pixels.numel(), float(mean), float(std), _stream())
+        self._check(rc, "ddp_normalize_u8")
 
     # -- collectives --------------------------------------------------------------------------------
     def comm_unique_id(self) -> bytes:

@@ -31,6 +31,22 @@ class SyntheticMNIST(torch.utils.data.Dataset):
         nat.synth_batch(self.seed, indices, base_index, b, x, y)
         return x, y
 
+    def batch_u8(self, indices: torch.Tensor = None, base_index: int = 0, count: int = None):
+        """Raw pixels (uint8 [B,784], int64 labels) — what datasets.MNIST stores before its transform."""
+        nat = _native.get()
+        b = indices.numel() if indices is not None else count
+        px = torch.empty(b, 784, dtype=torch.uint8, device=self.device)
+        y = torch.empty(b, dtype=torch.int64, device=self.device)
+        nat.synth_batch_u8(self.seed, indices, base_index, b, px, y)
+        return px, y
+
+    @staticmethod
+    def transform(pixels_u8: torch.Tensor, mean=0.1307, std=0.3081):
+        """ToTensor() + Normalize((mean,), (std,)) on the device: uint8 [B,784] -> float32 [B,1,28,28]."""
+        out = torch.empty(pixels_u8.shape[0], 1, 28, 28, dtype=torch.float32, device=pixels_u8.device)
+        _native.get().normalize_u8(pixels_u8.contiguous(), out, mean, std)
+        return out
+
     def __getitem__(self, i):
         x, y = self.batch(base_index=int(i), count=1)
         return x[0], y[0]

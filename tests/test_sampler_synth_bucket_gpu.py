@@ -77,6 +77,23 @@ def test_synth_batch_bit_exact(native):
     assert torch.equal(x8.cpu(), fx["x"]) and torch.equal(y8.cpu(), fx["y"])
 
 
+def test_u8_pixels_and_device_transform_bit_exact(native):
+    """datasets.MNIST holds uint8; ToTensor+Normalize (ref: horovod/mnist_horovod.py:34-37) run on the device."""
+    import pytorch_distributed_examples_b200 as pkg
+    ds = pkg.SyntheticMNIST(length=60000, seed=1234)
+    px, y = ds.batch_u8(base_index=100, count=257)
+    x, y2 = ds.batch(base_index=100, count=257)
+    assert torch.equal(y, y2)
+    xt = pkg.SyntheticMNIST.transform(px)
+    assert torch.equal(xt, x), "u8 -> transform must reproduce the float generator bit for bit"
+    ref = px.cpu().float().div(255).sub_(0.1307).div_(0.3081).view(-1, 1, 28, 28)      # torchvision's op order
+    assert torch.equal(xt.cpu(), ref)
+    odd = torch.arange(0, 256, dtype=torch.uint8, device="cuda").repeat(3)[:-5].contiguous()  # n % 16 != 0
+    out = torch.empty(odd.numel(), device="cuda")
+    native.normalize_u8(odd, out)
+    assert torch.equal(out.cpu(), odd.cpu().float().div(255).sub_(0.1307).div_(0.3081))
+
+
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_bucket_flatten_unflatten_roundtrip(native, dtype):
     from pytorch_distributed_examples_b200.bucket import BucketTable, FlatLayout, flatten_into, unflatten_from
