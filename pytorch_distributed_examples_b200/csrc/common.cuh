@@ -99,6 +99,13 @@ int sm_count();
 // per-kernel event timing (api.cu); mark(i) records event i on `stream` when profiling is on
 void prof_mark(int idx, cudaStream_t stream);
 
+// Warm the SM's L1 with a read-only global array that every CTA on the SM will stream through
+// (fc1.weight, 64 KB): all lines are requested at once instead of being missed one loop iteration at a time.
+__device__ __forceinline__ void prefetch_l1_range(const float* base, int nfloats, int tid, int nthreads) {
+  for (int i = tid * 32; i < nfloats; i += nthreads * 32)
+    asm volatile("prefetch.global.L1 [%0];" :: "l"(base + i));
+}
+
 // ---- Philox4x32-10 (counter-based; same constants as Random123 / curand) ------
 struct Philox4 { uint32_t x, y, z, w; };
 __host__ __device__ inline Philox4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,

@@ -27,6 +27,7 @@ head_bwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
                 float* __restrict__ partials, int B) {
   extern __shared__ __align__(16) float smem[];
   const float* w1g = params + OFF_F1W;    // [50][320], read through L1 (ld.global.nc), not staged
+  prefetch_l1_range(w1g, F1 * A2_PER, threadIdx.x, HB_THREADS);
   float* a2_s = smem;                     // [32][324]
   float* dp_s = a2_s + HT * HB_A2S;       // [50][36]  dL/d(fc1 pre-activation), transposed
   float* dz_s = dp_s + F1 * HB_DPS;       // [32][12]
@@ -171,8 +172,9 @@ head_bwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
 #pragma unroll
   for (int a = 0; a < 5; ++a)
 #pragma unroll
-    for (int c = 0; c < 10; ++c)
-      part[OFF_F1W + (jgW * 5 + a) * A2_PER + igW * 10 + c] = accW1[a][c];
+    for (int c = 0; c < 10; c += 2)     // OFF_F1W and igW*10 are even: 8-byte aligned pairs
+      *reinterpret_cast<float2*>(part + OFF_F1W + (jgW * 5 + a) * A2_PER + igW * 10 + c) =
+          make_float2(accW1[a][c], accW1[a][c + 1]);
 #pragma unroll
   for (int q = 0; q < 2; ++q) {
     const int e = tid + q * HB_THREADS;
@@ -305,11 +307,13 @@ conv2_dgrad_kernel(const float* __restrict__ params, const float* __restrict__ d
 constexpr int W2_THREADS = 256;
 constexpr int W2_NS = 2;                              // samples per stage
 constexpr int W2_DYS = O2 * C2 * O2;                  // [oy][co][ox] = 1280
+constexpr int W2_CS = 156;                            // a1 channel stride in smem (144 used): bank = 12*(ci*5+kh) mod 32
+constexpr int W2_A1S = C1 * W2_CS;                    // per-sample a1 footprint in smem
 __global__ void __launch_bounds__(W2_THREADS, 3)
 conv2_wgrad_kernel(const float* __restrict__ da2, const float* __restrict__ a2,
                    const uint8_t* __restrict__ idx2, const float* __restrict__ a1,
                    float drop_scale, float* __restrict__ partials, int B) {
-  __shared__ __align__(16) float a1_s[W2_NS * A1_PER];
+  __shared__ __align__(16) float a1_s[W2_NS * W2_A1S];
   __shared__ __align__(16) float dy_s[W2_NS * W2_DYS];
   __shared__ float bsum_s[A2_PER];
   __shared__ int live_s[W2_NS * C2];   // (sample, co) has any gradient: dead channels are skipped
@@ -330,8 +334,10 @@ conv2_wgrad_kernel(const float* __restrict__ da2, const float* __restrict__ a2,
     const int nvalid = min(W2_NS, B - b0);
     __syncthreads();
     const float4* src = reinterpret_cast<const float4*>(a1 + size_t(b0) * A1_PER);
-    for (int i = tid; i < nvalid * (A1_PER / 4); i += W2_THREADS)
-      reinterpret_cast<float4*>(a1_s)[i] = src[i];
+    for (int i = tid; i < nvalid * (A1_PER / 4); i += W2_THREADS) {
+      const int s = i / (A1_PER / 4), r = i % (A1_PER / 4), c = r / 36, w = r % 36;   // 36 float4 per channel
+      reinterpret_cast<float4*>(a1_s + s * W2_A1S + c * W2_CS)[w] = src[i];
+    }
     for (int s = 0; s < nvalid; ++s) {
 #pragma unroll
       for (int q = 0; q < 2; ++q) {
@@ -353,7 +359,7 @@ conv2_wgrad_kernel(const float* __restrict__ da2, const float* __restrict__ a2,
     __syncthreads();
     if (active) {
       for (int s = 0; s < nvalid; ++s) {
-        const float* ab = a1_s + s * A1_PER + ci * 144 + kh * P1;
+        const float* ab = a1_s + s * W2_A1S + ci * W2_CS + kh * P1;
         const float* db = dy_s + s * W2_DYS + cq * O2;
         bool lv[4];
 #pragma unroll
@@ -422,6 +428,7 @@ conv1_wgrad_kernel(const float* __restrict__ dp1, const uint8_t* __restrict__ id
   const bool active = tid < 250;
   const int oy0 = chunk * 5, oy1 = min(24, oy0 + 5);
   float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+  float acc2[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
   float bacc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // entries tid + 256*q of the 1440 (c,p) cells
   for (int b = blockIdx.x; b < B; b += gridDim.x) {
     __syncthreads();
@@ -457,17 +464,21 @@ conv1_wgrad_kernel(const float* __restrict__ dp1, const uint8_t* __restrict__ id
           float4 v = *reinterpret_cast<const float4*>(dp + 4 * q);
           d[4 * q] = v.x; d[4 * q + 1] = v.y; d[4 * q + 2] = v.z; d[4 * q + 3] = v.w;
         }
+        // two independent accumulator sets (left / right half of the row) double the FFMA ILP
 #pragma unroll
-        for (int ox = 0; ox < 24; ++ox)
+        for (int ox = 0; ox < 12; ++ox)
 #pragma unroll
-          for (int k = 0; k < 5; ++k) acc[k] = fmaf(d[ox], xr[ox + k], acc[k]);
+          for (int k = 0; k < 5; ++k) {
+            acc[k] = fmaf(d[ox], xr[ox + k], acc[k]);
+            acc2[k] = fmaf(d[ox + 12], xr[ox + 12 + k], acc2[k]);
+          }
       }
     }
   }
   // combine the 5 row-chunks in fixed order
   __syncthreads();
 #pragma unroll
-  for (int k = 0; k < 5; ++k) red_s[tid * 5 + k] = acc[k];
+  for (int k = 0; k < 5; ++k) red_s[tid * 5 + k] = acc[k] + acc2[k];
   __syncthreads();
   float* part = partials + size_t(blockIdx.x) * P_ARENA;
   if (active && chunk == 0) {

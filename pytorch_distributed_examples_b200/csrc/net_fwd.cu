@@ -184,16 +184,18 @@ conv2_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a1,
 }
 
 // ---------------------------------------------------------------------------
-// K_F3: head.  Tile of 16 samples per CTA iteration (several CTAs per SM); thread (sg,jg)
-// computes 2 samples x 4 fc1 outputs.  fc1.weight (64 KB) is read through L1 with ld.global.nc
-// (2-4 distinct 16-byte addresses per warp instruction, shared by every CTA on the SM) instead
-// of being staged per CTA; only the a2 tile and the small fc2 operands live in shared memory.
+// K_F3: head.  Tile of 16 samples per CTA iteration.  fc1 is split-K over the lanes of a warp:
+// warp = 4 fc1 outputs, lane = (k-quarter, sample pair); the 4 partial sums meet with two shuffles.
+// 13 warps per CTA and several CTAs per SM keep enough warps in flight for this latency-bound layer.
+// fc1.weight (64 KB) is read through L1 with ld.global.nc (prefetched once per CTA) instead of being
+// staged in shared memory; only the a2 tile and the small fc2 operands live in shared memory.
 // ---------------------------------------------------------------------------
 constexpr int HT = 16;              // samples per tile
-constexpr int HF_THREADS = 128;     // 8 sample-pairs x 13 output-quads = 104 active
+constexpr int HF_WARPS = 13;        // one warp per fc1 output quad (52 >= 50)
+constexpr int HF_THREADS = HF_WARPS * 32;
 constexpr int HF_A2S = 324;         // a2 row stride (floats)
 constexpr int HF_HS = 53;           // h row stride
-__global__ void __launch_bounds__(HF_THREADS, 4)
+__global__ void __launch_bounds__(HF_THREADS, 2)
 head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
                 const int64_t* __restrict__ target, const float* __restrict__ mask1d,
                 uint64_t seed, uint64_t offset, const int64_t* __restrict__ offset_dev, int training,
@@ -209,6 +211,8 @@ head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
   __shared__ float z_s[HT * 12];
   if (offset_dev) offset += uint64_t(*offset_dev);
   const int tid = threadIdx.x;
+  const float* w1g = params + OFF_F1W;
+  prefetch_l1_range(w1g, F1 * A2_PER, tid, HF_THREADS);
   if (tid < 52) b1_s[tid] = tid < F1 ? params[OFF_F1B + tid] : 0.f;
   for (int i = tid; i < 50 * 12; i += HF_THREADS) {
     int k = i / 12, c = i % 12;
@@ -216,11 +220,10 @@ head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
   }
   if (tid < 12) b2_s[tid] = tid < NC ? params[OFF_F2B + tid] : 0.f;
 
-  const int sg = tid & 7, jg = tid >> 3;   // jg < 13 active
-  const float* w1g = params + OFF_F1W;
+  const int jg = tid >> 5, lane = tid & 31, kp = lane >> 3, sg = lane & 7;
   int jrow[4];
 #pragma unroll
-  for (int jj = 0; jj < 4; ++jj) jrow[jj] = min(jg * 4 + jj, F1 - 1) * A2_PER;   // clamp: cols 50,51 are discarded
+  for (int jj = 0; jj < 4; ++jj) jrow[jj] = min(jg * 4 + jj, F1 - 1) * A2_PER + kp * 80;   // clamp: cols 50,51 discarded
   const int ntiles = (B + HT - 1) / HT;
   float loss_acc = 0.f;                    // thread 0 only
   int corr_acc = 0;
@@ -235,16 +238,16 @@ head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
       *reinterpret_cast<float4*>(a2_s + s * HF_A2S + k4 * 4) = v;
     }
     __syncthreads();
-    if (jg < 13) {
+    {
       float acc[2][4];
 #pragma unroll
       for (int i = 0; i < 2; ++i)
 #pragma unroll
         for (int jj = 0; jj < 4; ++jj) acc[i][jj] = 0.f;
-      const float* ar0 = a2_s + sg * HF_A2S;
-      const float* ar1 = a2_s + (sg + 8) * HF_A2S;
-#pragma unroll 4
-      for (int k = 0; k < A2_PER; k += 4) {
+      const float* ar0 = a2_s + sg * HF_A2S + kp * 80;
+      const float* ar1 = a2_s + (sg + 8) * HF_A2S + kp * 80;
+#pragma unroll 5
+      for (int k = 0; k < 80; k += 4) {
         float4 x0 = *reinterpret_cast<const float4*>(ar0 + k);
         float4 x1 = *reinterpret_cast<const float4*>(ar1 + k);
 #pragma unroll
@@ -256,22 +259,34 @@ head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
           acc[1][jj] = fmaf(x1.z, w.z, acc[1][jj]); acc[1][jj] = fmaf(x1.w, w.w, acc[1][jj]);
         }
       }
+      // combine the 4 k-quarters (fixed order: xor 8 then xor 16)
 #pragma unroll
-      for (int i = 0; i < 2; ++i) {
-        const int s = sg + 8 * i;
-        const int b = b0 + s;
+      for (int i = 0; i < 2; ++i)
 #pragma unroll
         for (int jj = 0; jj < 4; ++jj) {
-          const int j = jg * 4 + jj;
-          if (j < F1) {
-            float v = fmaxf(acc[i][jj] + b1_s[j], 0.f);
-            if (training && s < nvalid) {
-              float keep = mask1d ? mask1d[size_t(b) * F1 + j]
-                                  : philox_keep(seed, offset, 2u, uint64_t(b) * F1 + j);
-              v = v * (keep * 2.f);
+          float v = acc[i][jj];
+          v += __shfl_xor_sync(0xffffffffu, v, 8);
+          v += __shfl_xor_sync(0xffffffffu, v, 16);
+          acc[i][jj] = v;
+        }
+      if (kp == 0) {
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const int s = sg + 8 * i;
+          const int b = b0 + s;
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) {
+            const int j = jg * 4 + jj;
+            if (j < F1) {
+              float v = fmaxf(acc[i][jj] + b1_s[j], 0.f);
+              if (training && s < nvalid) {
+                float keep = mask1d ? mask1d[size_t(b) * F1 + j]
+                                    : philox_keep(seed, offset, 2u, uint64_t(b) * F1 + j);
+                v = v * (keep * 2.f);
+              }
+              h_s[s * HF_HS + j] = v;
+              if (s < nvalid) h_out[size_t(b) * F1 + j] = v;
             }
-            h_s[s * HF_HS + j] = v;
-            if (s < nvalid) h_out[size_t(b) * F1 + j] = v;
           }
         }
       }
@@ -332,19 +347,28 @@ head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
       if (tid == 0) { loss_acc += v; corr_acc += okc; }
     }
   }
+  // loss: one partial per CTA, the last CTA to arrive adds them in a fixed order (lane-strided loads that
+  // are all in flight at once, then a shuffle tree) -- deterministic, and no serial chain of L2 round trips
+  __shared__ unsigned int ticket_s;
   if (tid == 0) {
     if (correct_out && corr_acc) atomicAdd(correct_out, (unsigned long long)corr_acc);
+    ticket_s = 0u;
     if (loss_out) {
       loss_part[blockIdx.x] = loss_acc;
       __threadfence();
-      unsigned int ticket = atomicAdd(&counters[0], 1u);
-      if (ticket == gridDim.x - 1) {
-        __threadfence();
-        float total = 0.f;
-        for (unsigned int i = 0; i < gridDim.x; ++i) total += *((volatile float*)(loss_part + i));
-        loss_out[0] = total / float(B);
-        counters[0] = 0u;  // self-reset for the next launch
-      }
+      ticket_s = atomicAdd(&counters[0], 1u) + 1u;
+    }
+  }
+  __syncthreads();
+  if (loss_out && ticket_s == gridDim.x && tid < 32) {
+    __threadfence();
+    float v = 0.f;
+    for (unsigned int i = tid; i < gridDim.x; i += 32) v += __ldcg(loss_part + i);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (tid == 0) {
+      loss_out[0] = v / float(B);
+      counters[0] = 0u;  // self-reset for the next launch
     }
   }
 }

@@ -9,6 +9,27 @@
 
 namespace ddp {
 
+// the 16 pixels of block `blk` of sample `idx`, packed little-endian in 4 words; label returned via ref
+__device__ __forceinline__ void synth_block(uint64_t seed, uint64_t idx, int blk, uint32_t w[4], uint32_t& label) {
+  const uint32_t k0 = uint32_t(seed), k1 = uint32_t(seed >> 32);
+  label = philox4x32_10(uint32_t(idx), uint32_t(idx >> 32), 49u, 0u, k0, k1).x % 10u;
+  if (blk >= 49) return;
+  const Philox4 n = philox4x32_10(uint32_t(idx), uint32_t(idx >> 32), uint32_t(blk), 0u, k0, k1);
+  const uint32_t stroke = philox4x32_10(label, uint32_t(blk), 0x7E3Du, 0x5EEDu, k0, k1).x;
+  const uint32_t nz[4] = {n.x, n.y, n.z, n.w};
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    uint32_t out = 0u;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const uint32_t noise = (nz[q] >> (8 * k)) & 0xffu;
+      const uint32_t px = (noise >> 1) + (((stroke >> (4 * q + k)) & 1u) ? 112u : 0u);
+      out |= px << (8 * k);
+    }
+    w[q] = out;
+  }
+}
+
 __global__ void __launch_bounds__(256)
 synth_batch_kernel(uint64_t seed, const int64_t* __restrict__ indices, int64_t base_index, int64_t batch,
                    float* __restrict__ out_x, int64_t* __restrict__ out_y) {
@@ -17,13 +38,12 @@ synth_batch_kernel(uint64_t seed, const int64_t* __restrict__ indices, int64_t b
   const int blk = int(t % 50);
   if (b >= batch) return;
   const uint64_t idx = uint64_t(indices ? indices[b] : base_index + b);
-  Philox4 r = philox4x32_10(uint32_t(idx), uint32_t(idx >> 32), uint32_t(blk), 0u,
-                            uint32_t(seed), uint32_t(seed >> 32));
+  uint32_t w[4], label;
+  synth_block(seed, idx, blk, w, label);
   if (blk == 49) {
-    if (out_y) out_y[b] = int64_t(r.x % 10u);
+    if (out_y) out_y[b] = int64_t(label);
     return;
   }
-  const uint32_t w[4] = {r.x, r.y, r.z, r.w};
   float4* o = reinterpret_cast<float4*>(out_x + b * IMG_PIX + blk * 16);
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
@@ -46,13 +66,13 @@ synth_batch_u8_kernel(uint64_t seed, const int64_t* __restrict__ indices, int64_
   const int blk = int(t % 50);
   if (b >= batch) return;
   const uint64_t idx = uint64_t(indices ? indices[b] : base_index + b);
-  Philox4 r = philox4x32_10(uint32_t(idx), uint32_t(idx >> 32), uint32_t(blk), 0u,
-                            uint32_t(seed), uint32_t(seed >> 32));
+  uint32_t w[4], label;
+  synth_block(seed, idx, blk, w, label);
   if (blk == 49) {
-    if (out_y) out_y[b] = int64_t(r.x % 10u);
+    if (out_y) out_y[b] = int64_t(label);
     return;
   }
-  *reinterpret_cast<uint4*>(out_px + b * IMG_PIX + blk * 16) = make_uint4(r.x, r.y, r.z, r.w);
+  *reinterpret_cast<uint4*>(out_px + b * IMG_PIX + blk * 16) = make_uint4(w[0], w[1], w[2], w[3]);
 }
 
 // ToTensor + Normalize on the device (ref: horovod/mnist_horovod.py:34-37): out = (u8/255 - mean)/std,

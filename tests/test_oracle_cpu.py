@@ -70,6 +70,8 @@ def test_synth_oracle_properties():
     x, y = synth_oracle.synth_batch(1234, np.arange(64))
     assert x.shape == (64, 1, 28, 28) and x.dtype == np.float32 and y.dtype == np.int64
     assert x.min() >= np.float32(-0.42421296) - 1e-6 and x.max() <= np.float32(2.8214867) + 1e-6
+    px, _ = synth_oracle.synth_pixels(1234, np.arange(64))
+    assert px.dtype == np.uint8 and px.max() <= 239
     assert set(np.unique(y)) <= set(range(10))
     x2, y2 = synth_oracle.synth_batch(1234, np.arange(10, 20))
     assert np.array_equal(x2, x[10:20]) and np.array_equal(y2, y[10:20])      # pure function of (seed, index)
