@@ -13,7 +13,7 @@ from ctypes import POINTER, c_char_p, c_double, c_float, c_int, c_int32, c_int64
 import torch
 
 _LIB_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib")
-LIB_PATH = os.path.join(_LIB_DIR, "libddp_step.so")
+LIB_PATH = os.environ.get("DDP_LIB_PATH") or os.path.join(_LIB_DIR, "libddp_step.so")
 
 OPT_SGD, OPT_ADAM, OPT_ADAMW, OPT_ADADELTA = 0, 1, 2, 3
 DT_F32, DT_BF16, DT_I64, DT_U8 = 0, 1, 2, 3

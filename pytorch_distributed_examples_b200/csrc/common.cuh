@@ -96,6 +96,9 @@ int cuda_rc(cudaError_t e, const char* what);
   } while (0)
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 int sm_count();
+// tensor-core conv2 forward (conv2_fwd_tc.cu)
+int launch_conv2_fwd_tc(const float* params, const float* a1, const float* mask2d, uint64_t seed, uint64_t offset,
+                        const int64_t* offset_dev, int training, float* a2, uint8_t* idx2, int B, cudaStream_t stream);
 // per-kernel event timing (api.cu); mark(i) records event i on `stream` when profiling is on
 void prof_mark(int idx, cudaStream_t stream);
 

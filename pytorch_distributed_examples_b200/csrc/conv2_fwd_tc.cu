@@ -1,0 +1,371 @@
+// K_F2 on the 5th-generation tensor cores: conv2(10->20,5x5) + bias + Dropout2d + maxpool2 + ReLU as a
+// shifted-window implicit GEMM with tcgen05.mma (kind::tf32, fp32 accumulators in TMEM), 3xTF32 split so the
+// result stays within the fp32 parity bar (ref: horovod/mnist_horovod.py:20;  SURVEY §7.3 H1).
+//
+// GEMM view, per group of 4 samples:
+//   A'[r][k]   r = s*96 + y*8 + ox   (s<4, y<12, ox<8)        k = kw*10 + ci  (50, zero-padded to 56)
+//              = a1[s][ci][y][ox+kw]          -- im2col along kw only (5x duplication, built on the fly)
+//   B[kh][k][n] = W[n][ci][kh][kw]            n = output channel (20, zero-padded to 32)
+//   D[m][n] = sum_kh  A'[m + 8*kh][:] . B[kh][:, n]          m = s*96 + oy*8 + ox
+// The kh taps are NOT materialised: shifting the conv window down by one row is a shift of 8 rows of A',
+// i.e. +128 bytes on the start address of the (un-swizzled, K-major) shared-memory descriptor.  Rows with
+// oy >= 8 are computed and discarded (M efficiency 2/3) so that every tile is a plain 128-row MMA.
+// 3xTF32 with two MMAs per (kh, k-step): A_hi x [B_hi | B_lo] (N=64: hi*hi in columns 0-31, hi*lo in 32-63) and
+// A_lo x B_hi (N=32, accumulating into columns 0-31); the epilogue adds the two column groups.  The MMAs are bound
+// by the shared-memory fetch of the 4 KB A tile (N is tiny), so reading A_hi once instead of twice is worth 27%.
+//
+// Warp roles (352 threads, 1 CTA/SM, persistent over groups):
+//   warps 0-3  epilogue: tcgen05.ld accumulators -> bias, dropout, 2x2 max-pool by warp shuffles, ReLU -> a2, idx2
+//   warps 4-7  producers: the group's raw a1 (23 KB) arrives by ONE cp.async.bulk (TMA engine, mbarrier complete_tx),
+//              prefetched a group ahead; producers read it from smem, split into tf32 hi / lo, 16-byte STS into the ring
+//   warps 8-10 one elected lane each issues the tcgen05.mma / tcgen05.commit of one M-tile; warp 8 owns the TMEM allocation
+// Pipelines: full/empty mbarriers over a 3-stage ring of k-steps (producer <-> MMA) and tmem_full/tmem_empty
+// over two accumulator buffers (MMA <-> epilogue), so the epilogue of group g overlaps the MMAs of group g+1.
+#include "common.cuh"
+
+namespace ddp {
+namespace tc2 {
+
+// Developer aid: -DDDP_TC_TIMING accumulates clock64() per warp role into g_tc_dbg (read with ddp_debug_tc_timing,
+// tools/tc_timing.py); it is how the producer / MMA-issue / epilogue balance of this kernel was tuned.
+#ifdef DDP_TC_TIMING
+__device__ unsigned long long g_tc_dbg[160 * 16];
+#define TC_T0(var) const long long var = clock64()
+#define TC_ACC(slot, t0) do { g_tc_dbg[blockIdx.x * 16 + (slot)] += (unsigned long long)(clock64() - (t0)); } while (0)
+#else
+#define TC_T0(var)
+#define TC_ACC(slot, t0)
+#endif
+
+constexpr int G = 4;                        // samples per group
+constexpr int ROWS_PER_S = 96;              // 12 rows x 8 columns of A' per sample
+constexpr int ROWS = G * ROWS_PER_S;        // 384 = 3 M-tiles
+constexpr int ROWS_PAD = ROWS + 32;         // + the deepest kh shift (4*8 rows)
+constexpr int MT = ROWS / 128;              // 3 M-tiles per group
+constexpr int KSTEPS = 7;                   // 56 / 8
+constexpr int NPAD = 32;                    // output channels padded to the MMA N
+constexpr int STAGES = 3;
+constexpr int A_PLANE = ROWS_PAD * 16;      // bytes of one k-chunk plane (4 k values x all rows)
+constexpr int A_HL = 2 * A_PLANE;           // one k-step of hi (or lo): 2 chunks
+constexpr int A_STAGE = 2 * A_HL;           // hi + lo
+constexpr int B_ROWS = 2 * NPAD;            // [B_hi rows 0-31 | B_lo rows 32-63] of one (kh, kstep)
+constexpr int B_PLANE = B_ROWS * 16;        // one k-chunk plane: 1 KB
+constexpr int B_TILE = 2 * B_PLANE;         // one (kh, kstep): 2 KB
+constexpr int SMEM_A = STAGES * A_STAGE;    // 79,872
+constexpr int SMEM_B = 5 * KSTEPS * B_TILE; // 71,680
+constexpr int RAW_BYTES = G * A1_PER * 4;    // one group's a1: 23,040 B
+constexpr int SMEM_RAW = 2 * RAW_BYTES;     // double-buffered
+constexpr int SMEM_MISC = 1024;             // barriers, tmem pointer, bias, noise
+constexpr int SMEM_BYTES = SMEM_A + SMEM_B + SMEM_RAW + SMEM_MISC;
+constexpr int THREADS = 352;                // 4 epilogue + 4 producer + 3 MMA-issuer warps
+constexpr int DCOLS = 2 * NPAD;              // accumulator columns per tile: [hi*hi + lo*hi | hi*lo]
+constexpr int TMEM_COLS = 512;              // 2 buffers x 3 tiles x 64 columns = 384 -> next power of two
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+  // un-swizzled K-major: LBO = byte stride between k-chunks (16 B of K), SBO = byte stride between 8-row groups
+  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)((lbo >> 4) & 0x3FFFu) << 16) |
+         ((uint64_t)((sbo >> 4) & 0x3FFFu) << 32) | ((uint64_t)1 << 46);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" :: "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done = 0;
+  uint32_t spins = 0;
+  while (!done) {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.b32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    if (++spins > (1u << 26)) __trap();   // a protocol bug must abort the launch, never hang the GPU
+  }
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+               "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+               :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+               "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                 "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+                 "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+                 "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+               : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float rna_tf32(float v) {      // round-to-nearest (ties away) to the 10-bit tf32 mantissa
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+  return __uint_as_float(r);
+}
+__device__ __forceinline__ void split_tf32(float v, float& hi, float& lo) {
+  // v = hi + lo with both parts exactly representable in tf32 (the tensor core would otherwise TRUNCATE the
+  // 13 low mantissa bits, a biased 2^-20 error); v - hi is exact in fp32, and rounding it leaves 2^-22 of |v|
+  hi = rna_tf32(v);
+  lo = rna_tf32(v - hi);
+}
+
+__global__ void __launch_bounds__(THREADS, 1)
+conv2_fwd_tc_kernel(const float* __restrict__ params, const float* __restrict__ a1,
+                    const float* __restrict__ mask2d, uint64_t seed, uint64_t offset,
+                    const int64_t* __restrict__ offset_dev, int training,
+                    float* __restrict__ a2, uint8_t* __restrict__ idx2, int B) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  unsigned char* a_ring = smem_raw;
+  unsigned char* b_mat = smem_raw + SMEM_A;
+  float* raw_s = reinterpret_cast<float*>(b_mat + SMEM_B);          // [2][G*1440]
+  unsigned char* misc = b_mat + SMEM_B + SMEM_RAW;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(misc);            // [STAGES]
+  uint64_t* empty_bar = full_bar + STAGES;                           // [STAGES]
+  uint64_t* tfull_bar = empty_bar + STAGES;                          // [2]
+  uint64_t* tempty_bar = tfull_bar + 2;                              // [2]
+  uint64_t* rfull_bar = tempty_bar + 2;                              // [2] raw a1 tile landed (tx bytes)
+  uint64_t* rempty_bar = rfull_bar + 2;                              // [2] producers done reading it
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(rempty_bar + 2);
+  float* bias_s = reinterpret_cast<float*>(misc + 128);              // [32]
+  float* noise_s = bias_s + 32;                                      // [2 buffers][G][20]
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (offset_dev) offset += uint64_t(*offset_dev);
+  TC_T0(t_kernel);
+
+  // ---- one-time setup: weights -> B (hi, lo), barriers, TMEM ---------------------------------------
+  for (int i = tid; i < 5 * KSTEPS * NPAD * 2; i += THREADS) {         // one 16-byte chunk (4 k) per item
+    const int chunk = i & 1, n = (i >> 1) % NPAD, kj = (i >> 1) / NPAD, j = kj % KSTEPS, kh = kj / KSTEPS;
+    float hi[4], lo[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int k = j * 8 + chunk * 4 + e;
+      float w = 0.f;
+      if (k < 50 && n < C2) w = params[OFF_C2W + n * 250 + (k % 10) * 25 + kh * 5 + k / 10];
+      split_tf32(w, hi[e], lo[e]);
+    }
+    const int off = (kh * KSTEPS + j) * B_TILE + chunk * B_PLANE + n * 16;
+    *reinterpret_cast<float4*>(b_mat + off) = make_float4(hi[0], hi[1], hi[2], hi[3]);
+    *reinterpret_cast<float4*>(b_mat + off + NPAD * 16) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+  }
+  if (tid < 32) bias_s[tid] = tid < C2 ? params[OFF_C2B + tid] : 0.f;
+  // zero the whole stage ring once: pad rows / pad k stay finite forever
+  for (int i = tid; i < SMEM_A / 16; i += THREADS) reinterpret_cast<float4*>(a_ring)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (tid == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 128); mbar_init(&empty_bar[s], MT); }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tfull_bar[b], MT); mbar_init(&tempty_bar[b], 128);
+      mbar_init(&rfull_bar[b], 1); mbar_init(&rempty_bar[b], 128);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;");
+  }
+  if (warp == 8) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(tmem_ptr)), "n"(TMEM_COLS));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;");
+  const uint32_t tmem = *tmem_ptr;
+  const int ngroups = (B + G - 1) / G;
+  if (tid == 0) TC_ACC(0, t_kernel);   // slot 0: setup
+
+  if (warp >= 4 && warp < 8) {
+    // ======================= producers =======================
+    const int pt = tid - 128;                       // 0..127
+    // each thread owns rows pt, pt+128, pt+256 of A' (both k-chunks): decompose them once
+    uint32_t it = 0, gi = 0;                        // running k-step / group counters -> ring slots / phases
+    int row_src[3], row_s[3];
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+      const int r = pt + 128 * q;
+      const int sidx = r / ROWS_PER_S, rem = r % ROWS_PER_S;
+      row_s[q] = sidx;
+      row_src[q] = sidx * A1_PER + (rem >> 3) * P1 + (rem & 7);     // + ci*144 + kw per k
+    }
+    auto issue_raw = [&](int grp, int rb) {         // one elected thread: bulk-copy the group's a1 into raw_s[rb]
+      const int b0 = grp * G;
+      const uint32_t bytes = uint32_t(min(G, B - b0)) * (A1_PER * 4);
+      asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}"
+                   :: "r"(smem_u32(&rfull_bar[rb])), "r"(bytes) : "memory");
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   :: "r"(smem_u32(raw_s + rb * (G * A1_PER))), "l"(a1 + size_t(b0) * A1_PER), "r"(bytes),
+                      "r"(smem_u32(&rfull_bar[rb])) : "memory");
+    };
+    if (pt == 0 && blockIdx.x < ngroups) issue_raw(blockIdx.x, 0);
+    for (int grp = blockIdx.x; grp < ngroups; grp += gridDim.x, ++gi) {
+      const int rb = gi & 1;
+      const int nvalid = min(G, B - grp * G);
+      // prefetch the next group's tile into the other buffer once its previous readers are done
+      if (pt == 0 && grp + int(gridDim.x) < ngroups) {
+        if (gi >= 1) mbar_wait(&rempty_bar[rb ^ 1], ((gi - 1) >> 1) & 1);
+        issue_raw(grp + gridDim.x, rb ^ 1);
+      }
+      { TC_T0(tw); mbar_wait(&rfull_bar[rb], (gi >> 1) & 1); if (pt == 0) TC_ACC(1, tw); }   // slot 1: producer waits raw tile
+      const float* raw = raw_s + rb * (G * A1_PER);
+      for (int j = 0; j < KSTEPS; ++j, ++it) {
+        const int slot = it % STAGES;
+        { TC_T0(tw); if (it >= STAGES) mbar_wait(&empty_bar[slot], ((it / STAGES) - 1) & 1); if (pt == 0) TC_ACC(2, tw); }  // slot 2: producer waits empty
+        TC_T0(tb);
+        unsigned char* st = a_ring + slot * A_STAGE;
+        // this k-step's 8 k values (warp-uniform): source offset ci*144 + kw, or "padding" for k >= 50
+        int koff[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { const int k = j * 8 + e; koff[e] = (k % 10) * 144 + k / 10; }
+        {
+#pragma unroll
+          for (int q = 0; q < 3; ++q) {
+            const float* src = raw + row_src[q];
+            const bool live = row_s[q] < nvalid;
+            float hi[8], lo[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              float v = 0.f;
+              if (live && (j * 8 + e) < 50) v = src[koff[e]];
+              split_tf32(v, hi[e], lo[e]);
+            }
+            const int off = (pt + 128 * q) * 16;
+            *reinterpret_cast<float4*>(st + off) = make_float4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<float4*>(st + A_PLANE + off) = make_float4(hi[4], hi[5], hi[6], hi[7]);
+            *reinterpret_cast<float4*>(st + A_HL + off) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+            *reinterpret_cast<float4*>(st + A_HL + A_PLANE + off) = make_float4(lo[4], lo[5], lo[6], lo[7]);
+          }
+        }
+        if (pt == 0) TC_ACC(3, tb);   // slot 3: producer build time
+        { TC_T0(tf); asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        mbar_arrive(&full_bar[slot]); if (pt == 0) TC_ACC(4, tf); }   // slot 4: fence + arrive
+      }
+      mbar_arrive(&rempty_bar[rb]);
+    }
+  } else if (warp >= 8) {
+    // ======================= MMA issuers: warp 8+t owns M-tile t (a single thread's issue rate is the limit) ====
+    if (lane == 0) {
+      const int t = warp - 8;
+      const uint32_t idesc_base = (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(128 >> 4) << 24);   // D f32, A/B tf32 K-major, M=128
+      const uint32_t idesc64 = idesc_base | (uint32_t(DCOLS >> 3) << 17), idesc32 = idesc_base | (uint32_t(NPAD >> 3) << 17);
+      const uint32_t a_base = smem_u32(a_ring), b_base = smem_u32(b_mat);
+      uint32_t it = 0, gi = 0;
+      for (int grp = blockIdx.x; grp < ngroups; grp += gridDim.x, ++gi) {
+        const int buf = gi & 1;
+        { TC_T0(tw); if (gi >= 2) mbar_wait(&tempty_bar[buf], ((gi >> 1) - 1) & 1); if (t == 0) TC_ACC(5, tw); }   // slot 5: MMA waits tmem empty
+        asm volatile("tcgen05.fence::after_thread_sync;");
+        for (int j = 0; j < KSTEPS; ++j, ++it) {
+          const int slot = it % STAGES;
+          { TC_T0(tw); mbar_wait(&full_bar[slot], (it / STAGES) & 1); if (t == 0) TC_ACC(6, tw); }   // slot 6: MMA waits full
+          TC_T0(ti);
+          asm volatile("tcgen05.fence::after_thread_sync;");
+          // descriptor arithmetic: the start-address field is the low 14 bits in units of 16 B, so a byte offset
+          // is added as (bytes >> 4); rows are 16 B apart, hence "+ rows" below
+          const uint64_t a_hi0 = make_desc(a_base + slot * A_STAGE, A_PLANE, 128);
+          const uint64_t a_lo0 = a_hi0 + (A_HL >> 4);
+          const uint64_t b0 = make_desc(b_base + j * B_TILE, B_PLANE, 128);
+          const uint32_t d = tmem + uint32_t((buf * MT + t) * DCOLS);
+          {
+#pragma unroll
+            for (int kh = 0; kh < 5; ++kh) {
+              const uint64_t rows = uint64_t(t * 128 + kh * 8);
+              const uint64_t bsel = uint64_t((kh * KSTEPS * B_TILE) >> 4);
+              umma_tf32(d, a_hi0 + rows, b0 + bsel, idesc64, (j | kh) ? 1u : 0u);   // hi*hi | hi*lo
+              umma_tf32(d, a_lo0 + rows, b0 + bsel, idesc32, 1u);                   // + lo*hi into columns 0-31
+            }
+          }
+          umma_commit(&empty_bar[slot]);            // stage reusable once these MMAs have read it
+          if (t == 0) TC_ACC(7, ti);   // slot 7: MMA issue time
+        }
+        umma_commit(&tfull_bar[buf]);               // accumulators of this group complete
+      }
+    }
+  } else {
+    // ======================= epilogue (warps 0-3 <-> TMEM lanes 32*warp ..) =======================
+    uint32_t gi = 0;
+    for (int grp = blockIdx.x; grp < ngroups; grp += gridDim.x, ++gi) {
+      const int buf = gi & 1;
+      const int b0 = grp * G;
+      // dropout noise of this group's (sample, channel) pairs: x * noise, noise in {0, 2} (1 in eval mode)
+      float* nz = noise_s + buf * (G * C2);
+      if (tid < G * C2) {
+        const int s = tid / C2, co = tid % C2, b = b0 + s;
+        float noise = 1.f;
+        if (training && b < B) {
+          const float keep = mask2d ? mask2d[size_t(b) * C2 + co] : philox_keep(seed, offset, 1u, uint64_t(b) * C2 + co);
+          noise = keep * 2.f;
+        }
+        nz[tid] = noise;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      { TC_T0(tw); mbar_wait(&tfull_bar[buf], (gi >> 1) & 1); if (tid == 0) TC_ACC(8, tw); }   // slot 8: epilogue waits accumulators
+      TC_T0(te);
+      asm volatile("tcgen05.fence::after_thread_sync;");
+#pragma unroll 1
+      for (int t = 0; t < MT; ++t) {
+        uint32_t acc[32], acc_hl[32];
+        const uint32_t taddr = tmem + (uint32_t(warp * 32) << 16) + uint32_t((buf * MT + t) * DCOLS);
+        tmem_ld32(taddr, acc);
+        tmem_ld32(taddr + NPAD, acc_hl);
+        const int m = t * 128 + warp * 32 + lane;
+        const int s = m / ROWS_PER_S, rem = m % ROWS_PER_S, oy = rem >> 3, ox = rem & 7;
+        const int b = b0 + s;
+        const bool writer = (oy < 8) && !(oy & 1) && !(ox & 1) && (b < B);
+        const int pp = (oy >> 1) * 4 + (ox >> 1);
+        const float* nzs = nz + s * C2;
+#pragma unroll
+        for (int co = 0; co < C2; ++co) {
+          const float v00 = (__uint_as_float(acc[co]) + __uint_as_float(acc_hl[co]) + bias_s[co]) * nzs[co];
+          const float v01 = __shfl_xor_sync(0xffffffffu, v00, 1);    // (oy, ox+1)
+          const float v10 = __shfl_xor_sync(0xffffffffu, v00, 8);    // (oy+1, ox)
+          const float v11 = __shfl_xor_sync(0xffffffffu, v00, 9);    // (oy+1, ox+1)
+          float best = v00; int bi = 0;                              // first-max in window scan order
+          if (v01 > best) { best = v01; bi = 1; }
+          if (v10 > best) { best = v10; bi = 2; }
+          if (v11 > best) { best = v11; bi = 3; }
+          if (writer) {
+            const size_t o = size_t(b) * A2_PER + co * 16 + pp;
+            a2[o] = fmaxf(best, 0.f);
+            idx2[o] = uint8_t(bi);
+          }
+        }
+      }
+      asm volatile("tcgen05.fence::before_thread_sync;");
+      mbar_arrive(&tempty_bar[buf]);
+      if (tid == 0) TC_ACC(9, te);   // slot 9: epilogue work
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;");
+  __syncthreads();
+  if (tid == 0) TC_ACC(10, t_kernel);   // slot 10: whole kernel
+  if (warp == 8) {
+    asm volatile("tcgen05.fence::after_thread_sync;");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "n"(TMEM_COLS));
+  }
+}
+
+}  // namespace tc2
+
+#ifdef DDP_TC_TIMING
+extern "C" int ddp_debug_tc_timing(unsigned long long* out, int reset) {
+  if (reset) { static unsigned long long z[160 * 16] = {0}; return (int)cudaMemcpyToSymbol(tc2::g_tc_dbg, z, sizeof(z)); }
+  return (int)cudaMemcpyFromSymbol(out, tc2::g_tc_dbg, sizeof(unsigned long long) * 160 * 16);
+}
+#endif
+
+int launch_conv2_fwd_tc(const float* params, const float* a1, const float* mask2d, uint64_t seed, uint64_t offset,
+                        const int64_t* offset_dev, int training, float* a2, uint8_t* idx2, int B, cudaStream_t stream) {
+  static bool attr_done = false;
+  if (!attr_done) {
+    DDP_CUDA(cudaFuncSetAttribute(tc2::conv2_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tc2::SMEM_BYTES));
+    attr_done = true;
+  }
+  const int ngroups = (B + tc2::G - 1) / tc2::G;
+  const int sms = sm_count();
+  const int grid = ngroups < sms ? ngroups : sms;
+  tc2::conv2_fwd_tc_kernel<<<grid, tc2::THREADS, tc2::SMEM_BYTES, stream>>>(params, a1, mask2d, seed, offset, offset_dev,
+                                                                         training, a2, idx2, B);
+  return 0;
+}
+
+}  // namespace ddp

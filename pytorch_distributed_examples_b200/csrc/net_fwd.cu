@@ -1,8 +1,8 @@
 // Forward kernels of the MNIST CNN `Net` (ref: horovod/mnist_horovod.py:18-25):
 //   K_F1  conv1(1->10,5x5)+bias -> maxpool2 -> ReLU                     x  -> a1,idx1
-//   K_F2  conv2(10->20,5x5)+bias -> Dropout2d -> maxpool2 -> ReLU       a1 -> a2,idx2
+//   K_F2  conv2(10->20,5x5)+bias -> Dropout2d -> maxpool2 -> ReLU       a1 -> a2,idx2   (tensor cores: conv2_fwd_tc.cu)
 //   K_F3  fc1+bias -> ReLU -> dropout -> fc2+bias -> log_softmax (-> NLL mean, argmax)
-// fp32 FFMA with register tiling; conv outputs before pooling never leave registers.
+// K_F1 / K_F3 are fp32 FFMA with register tiling; conv outputs before pooling never leave the SM.
 #include "common.cuh"
 
 namespace ddp {
@@ -83,102 +83,6 @@ conv1_fwd_kernel(const float* __restrict__ params, const float* __restrict__ x,
       pool4(acc[0][c], acc[1][c], acc[2][c], acc[3][c], best, bi);
       a1[ob + c * 144] = fmaxf(best, 0.f);
       idx1[ob + c * 144] = uint8_t(bi);
-    }
-  }
-}
-
-// ---------------------------------------------------------------------------
-// K_F2: one warp per sample.  lane = g*16 + pp: pp = pooled position (4x4),
-// g = half of the 20 output channels.  Per input channel: 6x6 patch in registers,
-// 40 accumulators (4 conv positions x 10 channels), weights via LDS.128 broadcast.
-// ---------------------------------------------------------------------------
-constexpr int F2_WARPS = 8;
-constexpr int F2_THREADS = F2_WARPS * 32;
-constexpr int F2_WS = 250 * 24;  // [ci*25+tap][g][12]
-constexpr int F2_SMEM = (F2_WS + 24 + F2_WARPS * A1_PER) * 4;
-__global__ void __launch_bounds__(F2_THREADS, 2)
-conv2_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a1,
-                 const float* __restrict__ mask2d, uint64_t seed, uint64_t offset,
-                 const int64_t* __restrict__ offset_dev, int training,
-                 float* __restrict__ a2, uint8_t* __restrict__ idx2, int B) {
-  if (offset_dev) offset += uint64_t(*offset_dev);
-  extern __shared__ __align__(16) float smem[];
-  float* w_s = smem;
-  float* b_s = w_s + F2_WS;
-  float* in_s = b_s + 24;
-  const int tid = threadIdx.x;
-  for (int i = tid; i < F2_WS; i += F2_THREADS) {
-    int j = i % 12, g = (i / 12) & 1, ct = i / 24;
-    w_s[i] = j < 10 ? params[OFF_C2W + (g * 10 + j) * 250 + ct] : 0.f;
-  }
-  if (tid < 24) { int j = tid % 12, g = tid / 12; b_s[tid] = j < 10 ? params[OFF_C2B + g * 10 + j] : 0.f; }
-  const int warp = tid >> 5, lane = tid & 31;
-  const int g = lane >> 4, pp = lane & 15, py = pp >> 2, px = pp & 3;
-  const int ngroups = (B + F2_WARPS - 1) / F2_WARPS;
-  for (int grp = blockIdx.x; grp < ngroups; grp += gridDim.x) {
-    const int b0 = grp * F2_WARPS;
-    const int nvalid = min(F2_WARPS, B - b0);
-    __syncthreads();
-    const float4* src = reinterpret_cast<const float4*>(a1 + size_t(b0) * A1_PER);
-    float4* dst = reinterpret_cast<float4*>(in_s);
-    for (int i = tid; i < nvalid * (A1_PER / 4); i += F2_THREADS) dst[i] = src[i];
-    __syncthreads();
-    if (warp >= nvalid) continue;
-    const int b = b0 + warp;
-    const float* sample = in_s + warp * A1_PER + (2 * py) * P1 + 2 * px;
-
-    float acc[4][10];
-#pragma unroll
-    for (int q = 0; q < 4; ++q)
-#pragma unroll
-      for (int j = 0; j < 10; ++j) acc[q][j] = 0.f;
-
-#pragma unroll 1
-    for (int ci = 0; ci < C1; ++ci) {
-      float patch[6][6];
-      const float* ip = sample + ci * 144;
-#pragma unroll
-      for (int r = 0; r < 6; ++r)
-#pragma unroll
-        for (int j = 0; j < 3; ++j) {
-          float2 v = *reinterpret_cast<const float2*>(ip + r * P1 + 2 * j);
-          patch[r][2 * j] = v.x; patch[r][2 * j + 1] = v.y;
-        }
-      const float* wbase = w_s + (ci * 25) * 24 + g * 12;
-#pragma unroll
-      for (int kh = 0; kh < 5; ++kh)
-#pragma unroll
-        for (int kw = 0; kw < 5; ++kw) {
-          const float4* wp = reinterpret_cast<const float4*>(wbase + (kh * 5 + kw) * 24);
-          float4 w0 = wp[0], w1 = wp[1], w2 = wp[2];
-          float w[10] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w, w2.x, w2.y};
-#pragma unroll
-          for (int dy = 0; dy < 2; ++dy)
-#pragma unroll
-            for (int dx = 0; dx < 2; ++dx) {
-              float v = patch[dy + kh][dx + kw];
-#pragma unroll
-              for (int j = 0; j < 10; ++j) acc[dy * 2 + dx][j] = fmaf(v, w[j], acc[dy * 2 + dx][j]);
-            }
-        }
-    }
-    // epilogue: bias, channel dropout (x * noise, noise in {0,2}), pool, ReLU
-#pragma unroll
-    for (int j = 0; j < 10; ++j) {
-      const int co = g * 10 + j;
-      float noise = 1.f;
-      if (training) {
-        float keep = mask2d ? mask2d[size_t(b) * C2 + co]
-                            : philox_keep(seed, offset, 1u, uint64_t(b) * C2 + co);
-        noise = keep * 2.f;
-      }
-      const float bias = b_s[g * 12 + j];
-      float best; int bi;
-      pool4((acc[0][j] + bias) * noise, (acc[1][j] + bias) * noise, (acc[2][j] + bias) * noise,
-            (acc[3][j] + bias) * noise, best, bi);
-      const size_t o = size_t(b) * A2_PER + co * 16 + pp;
-      a2[o] = fmaxf(best, 0.f);
-      idx2[o] = uint8_t(bi);
     }
   }
 }
@@ -393,11 +297,6 @@ extern "C" int ddp_net_forward(const float* params, const float* x, const int64_
   const int sms = sm_count();
   Workspace ws = carve_workspace(workspace, batch);
 
-  static bool attr_done = false;
-  if (!attr_done) {
-    DDP_CUDA(cudaFuncSetAttribute(conv2_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, F2_SMEM));
-    attr_done = true;
-  }
   prof_mark(0, stream);
   {
     int npairs = (B + 1) / 2;
@@ -405,12 +304,8 @@ extern "C" int ddp_net_forward(const float* params, const float* x, const int64_
     conv1_fwd_kernel<<<grid, F1_THREADS, 0, stream>>>(params, x, ws.a1, ws.idx1, B);
   }
   prof_mark(1, stream);
-  {
-    int ngroups = (B + F2_WARPS - 1) / F2_WARPS;
-    int grid = ngroups < sms * 2 ? ngroups : sms * 2;
-    conv2_fwd_kernel<<<grid, F2_THREADS, F2_SMEM, stream>>>(params, ws.a1, mask2d, seed, offset, offset_dev, training,
-                                                          ws.a2, ws.idx2, B);
-  }
+  if (int rc = launch_conv2_fwd_tc(params, ws.a1, mask2d, seed, offset, offset_dev, training, ws.a2, ws.idx2, B, stream))
+    return rc;
   prof_mark(2, stream);
   {
     int ntiles = (B + HT - 1) / HT;
