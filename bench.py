@@ -143,6 +143,9 @@ def main():
         return
     args.warmup = max(args.warmup, 3)
 
+    # keep stdout to the ONE JSON line: NCCL_DEBUG=VERSION (this image's default) makes NCCL print its banner there
+    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"
     import torch
     import torch.distributed as dist
     import pytorch_distributed_examples_b200 as pkg
@@ -270,6 +273,9 @@ def main():
         return
     args.warmup = max(args.warmup, 3)
 
+    # keep stdout to the ONE JSON line: NCCL_DEBUG=VERSION (this image's default) makes NCCL print its banner there
+    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"
     import torch
     import torch.distributed as dist
     import pytorch_distributed_examples_b200 as pkg
