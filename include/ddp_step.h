@@ -10,9 +10,11 @@
  * No C++ exception crosses the boundary; `ddp_last_error()` gives the message
  * of the last failing call on the calling thread.
  *
- * Memory: the library allocates nothing on the device.  All buffers are owned
- * by the caller (PyTorch's caching allocator in the Python host layer).  All
- * launches are asynchronous on the given stream and are CUDA-graph capturable.
+ * Memory: every buffer is owned by the caller (PyTorch's caching allocator in
+ * the Python host layer); the library allocates nothing on the device, with one
+ * stated exception: ddp_peer_create, whose NVLink receive buffers are
+ * communicator resources.  All launches are asynchronous on the given stream
+ * and are CUDA-graph capturable.
  *
  * "ref:" citations point at the reference interface each entry point replaces
  * (/root/reference = ArnauGabrielAtienza/pytorch_distributed_examples);
@@ -187,6 +189,29 @@ int ddp_comm_abort(void* comm);
 int ddp_allreduce_sum(void* comm, void* buf, int64_t count, int dtype, void* stream);
 int ddp_allreduce_max(void* comm, void* buf, int64_t count, int dtype, void* stream);
 int ddp_broadcast(void* comm, void* buf, int64_t nbytes, int root, void* stream);
+
+/* ---- one-shot allreduce over NVLink peer memory, fused with the update ---------
+ * For latency-bound buckets on ONE node (world <= 8): replaces ncclAllReduce + ddp_fused_update for the
+ * gradient averaging hvd.DistributedOptimizer.step() / DDP perform every step
+ * (ref: horovod/mnist_horovod.py:53,64 ; pytorch_elastic/mnist_ddp_elastic.py:58).  Each rank pushes its
+ * bucket into every peer's receive slot through cudaIpc-mapped NVLink addresses, publishes an epoch flag,
+ * waits for the W flags addressed to it, sums the W slots in rank order (replicas stay bit-identical) and
+ * applies the optimizer rule — one kernel.  The receive buffers are communicator resources allocated by
+ * ddp_peer_create (the one place this library calls cudaMalloc); handles travel through the host's
+ * rendezvous store: create -> local_handle -> (exchange) -> connect.  n % 4 == 0, n <= max_elems.
+ * Every rank must launch the call for the same step; do not overlap two calls on one communicator.      */
+#define DDP_IPC_HANDLE_BYTES 64
+int ddp_peer_create(void** peer_out, int world, int rank, int64_t max_elems);
+int ddp_peer_local_handle(void* peer, void* handle_out /* DDP_IPC_HANDLE_BYTES */);
+int ddp_peer_connect(void* peer, const void* all_handles /* world x DDP_IPC_HANDLE_BYTES, rank order */);
+int ddp_peer_destroy(void* peer);
+/* in-place sum over ranks */
+int ddp_peer_allreduce(void* peer, float* bucket, int64_t n, void* stream);
+/* sum over ranks, 1/world, optimizer update (same arguments as ddp_fused_update; hyper->write_back_grad
+ * stores the averaged gradient back into bucket) */
+int ddp_peer_allreduce_update(void* peer, float* bucket, int64_t n, int opt, float* params,
+                              float* state1, float* state2, const ddp_hyper_t* hyper, int64_t step,
+                              const int64_t* step_dev, void* stream);
 
 /* ---- elastic state snapshot -------------------------------------------------
  * ref: horovod_mnist_elastic.py:71-72 (state.commit), :104 (TorchState);

@@ -20,6 +20,7 @@ DT_F32, DT_BF16, DT_I64, DT_U8 = 0, 1, 2, 3
 ARENA_ELEMS = 21848
 PARAM_COUNT = 21840
 UID_BYTES = 128
+IPC_HANDLE_BYTES = 64
 BUCKET_CHUNK_BYTES = 16384
 
 
@@ -61,6 +62,13 @@ SIGNATURES = {
     "ddp_allreduce_sum": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "ddp_allreduce_max": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "ddp_broadcast": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p]),
+    "ddp_peer_create": (c_int, [POINTER(c_void_p), c_int, c_int, c_int64]),
+    "ddp_peer_local_handle": (c_int, [c_void_p, c_void_p]),
+    "ddp_peer_connect": (c_int, [c_void_p, c_void_p]),
+    "ddp_peer_destroy": (c_int, [c_void_p]),
+    "ddp_peer_allreduce": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
+    "ddp_peer_allreduce_update": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p, POINTER(Hyper),
+                                          c_int64, c_void_p, c_void_p]),
     "ddp_state_snapshot": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "ddp_state_restore": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "ddp_prof_enable": (c_int, [c_int]),
@@ -247,6 +255,36 @@ class Native:
     def broadcast(self, comm, buf, root: int):
         self._check(self.lib.ddp_broadcast(comm, _ptr(buf, "buf"), buf.numel() * buf.element_size(), root, _stream()),
                     "ddp_broadcast")
+
+    # -- NVLink peer-memory allreduce (+ fused update) ----------------------------------------------
+    def peer_create(self, world: int, rank: int, max_elems: int):
+        handle = c_void_p()
+        self._check(self.lib.ddp_peer_create(ctypes.byref(handle), world, rank, int(max_elems)), "ddp_peer_create")
+        return handle
+
+    def peer_local_handle(self, peer) -> bytes:
+        buf = ctypes.create_string_buffer(IPC_HANDLE_BYTES)
+        self._check(self.lib.ddp_peer_local_handle(peer, buf), "ddp_peer_local_handle")
+        return buf.raw
+
+    def peer_connect(self, peer, handles: bytes):
+        buf = ctypes.create_string_buffer(handles, len(handles))
+        self._check(self.lib.ddp_peer_connect(peer, buf), "ddp_peer_connect")
+
+    def peer_destroy(self, peer):
+        self._check(self.lib.ddp_peer_destroy(peer), "ddp_peer_destroy")
+
+    def peer_allreduce(self, peer, bucket):
+        self._check(self.lib.ddp_peer_allreduce(peer, _ptr(bucket, "bucket", torch.float32), bucket.numel(), _stream()),
+                    "ddp_peer_allreduce")
+
+    def peer_allreduce_update(self, peer, opt, bucket, params, state1, state2, n, hyper: Hyper, step=1, step_dev=None):
+        rc = self.lib.ddp_peer_allreduce_update(peer, _ptr(bucket, "bucket", torch.float32), int(n), opt,
+                                                _ptr(params, "params", torch.float32),
+                                                _ptr(state1, "state1", torch.float32), _ptr(state2, "state2", torch.float32),
+                                                ctypes.byref(hyper), int(step), _ptr(step_dev, "step_dev", torch.int64),
+                                                _stream())
+        self._check(rc, "ddp_peer_allreduce_update")
 
     # -- elastic snapshot ---------------------------------------------------------------------------
     def state_snapshot(self, device_arena, pinned_host):

@@ -48,6 +48,8 @@ class Communicator:
         self.rank = self.ranks.index(global_rank)
         self.generation = generation
         self.handle = None
+        self.peer = None          # NVLink peer-memory context (enable_peer)
+        self.peer_max_elems = 0
         self._obj_seq = 0
         nat = _native.get()
         if self.world > 1:
@@ -58,6 +60,36 @@ class Communicator:
             else:
                 uid = bytes(store.get(key))
             self.handle = nat.comm_init(uid, self.world, self.rank)
+
+    # -- NVLink peer-memory path for latency-bound buckets -------------------------------------------
+    def enable_peer(self, max_elems: int) -> bool:
+        """Set up the one-shot peer-memory allreduce (csrc/peer.cu) for buckets of up to ``max_elems`` floats.
+        Needs every rank on ONE node with NVLink/P2P IPC (world <= 8); returns False (and NCCL stays the path)
+        when the topology does not allow it.  Collective: every member must call it."""
+        if self.world <= 1 or self.world > 8 or not torch.cuda.is_available():
+            return False
+        local_world = int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", "1")))
+        if local_world < self.world:
+            return False              # ranks spread over several nodes: no shared NVLink domain
+        if self.peer is not None and self.peer_max_elems >= max_elems:
+            return True
+        nat = _native.get()
+        max_elems = (int(max_elems) + 3) // 4 * 4
+        peer = nat.peer_create(self.world, self.rank, max_elems)
+        base = f"ddp_step/peer/gen{self.generation}/{max_elems}"
+        self.store.set(f"{base}/{self.rank}", nat.peer_local_handle(peer))
+        handles = b"".join(bytes(self.store.get(f"{base}/{r}")) for r in range(self.world))
+        nat.peer_connect(peer, handles)
+        # nobody may push before everyone has mapped everyone: rendezvous once through NCCL
+        flag = torch.zeros(1, device="cuda")
+        self.allreduce_sum_(flag)
+        torch.cuda.current_stream().synchronize()
+        self.peer, self.peer_max_elems = peer, max_elems
+        return True
+
+    def peer_allreduce_(self, t: torch.Tensor):
+        _native.get().peer_allreduce(self.peer, t)
+        return t
 
     # -- tensor collectives (in place, on the current stream) ---------------------------------------
     def allreduce_sum_(self, t: torch.Tensor):
@@ -87,6 +119,9 @@ class Communicator:
         return pickle.loads(bytes(self.store.get(key)))
 
     def destroy(self):
+        if self.peer is not None:
+            _native.get().peer_destroy(self.peer)
+            self.peer = None
         if self.handle is not None:
             _native.get().comm_destroy(self.handle)
             self.handle = None

@@ -146,6 +146,18 @@ class _Group:
         if use_step_dev:
             nat.step_increment(self.step_dev)
 
+    def update_peer(self, comm, use_step_dev=False):
+        """allreduce(sum) over NVLink peer memory + 1/N + update in ONE kernel (csrc/peer.cu)."""
+        self.graph_mode = bool(use_step_dev)
+        self.ensure_state()
+        nat = _native.get()
+        self.steps += 1
+        nat.peer_allreduce_update(comm.peer, self.kind, self.bucket, self.param_arena, self.state1, self.state2,
+                                  self.layout.total, self.hyper(), step=self.steps,
+                                  step_dev=self.step_dev if use_step_dev else None)
+        if use_step_dev:
+            nat.step_increment(self.step_dev)
+
     # -- torch.optim state interop (state_dict / load_state_dict / elastic commit) --------------------
     _STATE_KEYS = {_native.OPT_SGD: ("momentum_buffer", None), _native.OPT_ADAM: ("exp_avg", "exp_avg_sq"),
                    _native.OPT_ADAMW: ("exp_avg", "exp_avg_sq"), _native.OPT_ADADELTA: ("square_avg", "acc_delta")}

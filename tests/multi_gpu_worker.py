@@ -43,7 +43,18 @@ def main():
     hvd.broadcast_(b, root_rank=W - 1)
     assert torch.equal(b, torch.arange(10, device="cuda", dtype=torch.float32) * W)
     assert hvd.broadcast_object({"r": R}, root_rank=0) == {"r": 0}
-    log("collectives ok")
+    # 1b. NVLink peer-memory allreduce == NCCL allreduce (sum order differs: rank order vs ring)
+    c = hvd._require()
+    assert c.enable_peer(21848)
+    torch.manual_seed(R)
+    for it in range(5):                           # several epochs: both slot parities, flags reused
+        a = torch.randn(21848, device="cuda")
+        b_ = a.clone()
+        c.allreduce_sum_(a)
+        c.peer_allreduce_(b_)
+        assert (a - b_).abs().max().item() <= 1e-5 * a.abs().max().item(), "peer allreduce != NCCL"
+        same_on_all_ranks(b_, "peer allreduce")   # rank-ordered sum: bit-identical on every rank
+    log("collectives ok (NCCL + NVLink peer memory)")
 
     # 2. reference loop with hvd.DistributedOptimizer == real 2-process gloo DDP (golden), when W == 2
     if W == 2:
@@ -125,7 +136,11 @@ def main():
         o = hvd.DistributedOptimizer(torch.optim.SGD(m.parameters(), lr=0.01, momentum=0.9))
         ds = pkg.SyntheticMNIST(length=1 << 20, seed=9)
         B = 256
-        step = pkg.TrainStep(m, o, B, communicator=hvd._require(), use_graph=True) if mode == "graph" else None
+        step = None
+        if mode.startswith("graph"):
+            step = pkg.TrainStep(m, o, B, communicator=hvd._require(), use_graph=True,
+                                 collective="nccl" if mode == "graph-nccl" else "auto")
+            assert step.use_peer == (mode == "graph")
         losses = []
         for k in range(6):
             x, y = ds.batch(base_index=(k * W + R) * B, count=B)
@@ -136,7 +151,9 @@ def main():
         return losses, m.flat_params.clone()
 
     l_mod, p_mod = run_steps("module")
-    l_gr, p_gr = run_steps("graph")
+    l_gr, p_gr = run_steps("graph")          # collective="auto": peer-memory allreduce fused with the update
+    l_nc, p_nc = run_steps("graph-nccl")
+    assert (p_nc - p_gr).abs().max().item() <= 1e-6 * p_nc.abs().max().item(), "peer path != NCCL path"
     assert max(abs(a - b) for a, b in zip(l_mod, l_gr)) <= 1e-5, (l_mod, l_gr)
     assert (p_mod - p_gr).abs().max().item() <= 1e-6 * p_mod.abs().max().item()
     same_on_all_ranks(p_gr, "TrainStep")
