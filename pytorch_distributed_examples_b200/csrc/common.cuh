@@ -59,7 +59,7 @@ inline Workspace carve_workspace(void* base, int64_t B) {
 // partials           : MAX_PARTS x P_ARENA floats (per-CTA partial weight gradients)
 // da2                : [B,320] f32  dL/d(a2)
 // dp1                : [B,1440] f32 dL/d(pooled conv1, pre-ReLU)
-constexpr int MAX_PARTS = 296;  // 2 CTAs per SM on 148 SMs
+constexpr int MAX_PARTS = 592;  // up to 4 CTAs per SM on 148 SMs
 struct Scratch {
   unsigned int* counters;
   float* loss_part;
@@ -107,6 +107,31 @@ void prof_mark(int idx, cudaStream_t stream);
 __device__ __forceinline__ void prefetch_l1_range(const float* base, int nfloats, int tid, int nthreads) {
   for (int i = tid * 32; i < nfloats; i += nthreads * 32)
     asm volatile("prefetch.global.L1 [%0];" :: "l"(base + i));
+}
+
+// ---- mbarrier + bulk-copy (TMA engine, 1-D) helpers -----------------------------------------------------
+// cp.async.bulk moves a contiguous block global -> shared without touching registers and signals an
+// mbarrier with the byte count (complete_tx); one thread issues, everybody waits on the barrier.
+__device__ __forceinline__ uint32_t smem_addr_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbarrier_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_addr_u32(bar)), "r"(count));
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbarrier_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}"
+               :: "r"(smem_addr_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_copy_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               :: "r"(smem_addr_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_addr_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbarrier_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done = 0, spins = 0;
+  while (!done) {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.b32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(smem_addr_u32(bar)), "r"(parity) : "memory");
+    if (++spins > (1u << 26)) __trap();
+  }
 }
 
 // ---- Philox4x32-10 (counter-based; same constants as Random123 / curand) ------

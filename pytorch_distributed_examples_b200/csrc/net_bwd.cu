@@ -18,7 +18,7 @@ constexpr int HB_THREADS = 320;
 constexpr int HB_A2S = 324;   // a2 tile row stride
 constexpr int HB_DPS = 36;    // dpT row stride ([j][s])
 constexpr int HB_HS = 53;     // h tile row stride
-constexpr int HB_SMEM = (HT * HB_A2S + F1 * HB_DPS + HT * 12 + HT * HB_HS + NC * 52) * 4;
+constexpr int HB_SMEM = (F1 * A2_PER + HT * HB_A2S + F1 * HB_DPS + HT * 12 + HT * HB_HS + NC * 52) * 4 + 16;
 __global__ void __launch_bounds__(HB_THREADS, 1)
 head_bwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
                 const float* __restrict__ h, const float* __restrict__ logp,
@@ -26,14 +26,28 @@ head_bwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
                 float nll_coef, float drop_scale, float* __restrict__ da2,
                 float* __restrict__ partials, int B) {
   extern __shared__ __align__(16) float smem[];
-  const float* w1g = params + OFF_F1W;    // [50][320], read through L1 (ld.global.nc), not staged
-  prefetch_l1_range(w1g, F1 * A2_PER, threadIdx.x, HB_THREADS);
-  float* a2_s = smem;                     // [32][324]
+  // fc1.weight (64 KB) and each a2 tile arrive by cp.async.bulk + mbarrier (no register staging)
+  float* w1_s = smem;                     // [50][320] natural layout
+  float* a2_s = w1_s + F1 * A2_PER;       // [32][324]
   float* dp_s = a2_s + HT * HB_A2S;       // [50][36]  dL/d(fc1 pre-activation), transposed
   float* dz_s = dp_s + F1 * HB_DPS;       // [32][12]
   float* h_s = dz_s + HT * 12;            // [32][53]
   float* w2_s = h_s + HT * HB_HS;         // [10][52]
+  uint64_t* bar = reinterpret_cast<uint64_t*>(w2_s + NC * 52);
   const int tid = threadIdx.x;
+  const int ntiles_all = (B + HT - 1) / HT;
+  if (tid == 0) mbarrier_init(bar, 1);
+  __syncthreads();
+  auto issue_tile = [&](int tile, bool with_w1) {       // thread 0 only
+    const int tb0 = tile * HT;
+    const int nv = min(HT, B - tb0);
+    mbarrier_expect_tx(bar, uint32_t(nv) * (A2_PER * 4) + (with_w1 ? F1 * A2_PER * 4 : 0));
+    if (with_w1) bulk_copy_g2s(w1_s, params + OFF_F1W, F1 * A2_PER * 4, bar);
+    for (int s = 0; s < nv; ++s)
+      bulk_copy_g2s(a2_s + s * HB_A2S, a2 + size_t(tb0 + s) * A2_PER, A2_PER * 4, bar);
+  };
+  if (tid == 0 && int(blockIdx.x) < ntiles_all) issue_tile(blockIdx.x, true);
+  uint32_t phase = 0;
   for (int i = tid; i < NC * 52; i += HB_THREADS) {
     int c = i / 52, j = i % 52;
     w2_s[i] = j < F1 ? params[OFF_F2W + c * F1 + j] : 0.f;
@@ -52,13 +66,10 @@ head_bwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
   for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int b0 = tile * HT;
     const int nvalid = min(HT, B - b0);
-    __syncthreads();
-    for (int i = tid; i < HT * (A2_PER / 4); i += HB_THREADS) {
-      int s = i / (A2_PER / 4), k4 = i % (A2_PER / 4);
-      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (s < nvalid) v = *reinterpret_cast<const float4*>(a2 + size_t(b0 + s) * A2_PER + k4 * 4);
-      *reinterpret_cast<float4*>(a2_s + s * HB_A2S + k4 * 4) = v;
-    }
+    __syncthreads();                        // previous tile fully consumed (h_s, dz_s, dp_s)
+    if (tile != int(blockIdx.x) && tid == 0) issue_tile(tile, false);   // first tile was issued before the loop
+    for (int i = tid; i < (HT - nvalid) * A2_PER; i += HB_THREADS)       // rows past the batch: keep them zero
+      a2_s[(nvalid + i / A2_PER) * HB_A2S + i % A2_PER] = 0.f;
     for (int i = tid; i < HT * F1; i += HB_THREADS) {
       int s = i / F1, j = i % F1;
       h_s[s * HB_HS + j] = s < nvalid ? h[size_t(b0) * F1 + i] : 0.f;
@@ -87,6 +98,8 @@ head_bwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
       for (int c = 0; c < NC; ++c)
         dz_s[s * 12 + c] = (s < nvalid) ? g[c] - expf(lp[c]) * sum : 0.f;
     }
+    mbarrier_wait(bar, phase);              // a2 tile (and, first time, fc1.weight) have landed
+    phase ^= 1u;
     __syncthreads();
     // dp[s][j] = relu'/dropout' * sum_c dz[s][c] * W2[c][j]
     for (int e = tid; e < HT * F1; e += HB_THREADS) {
@@ -147,8 +160,8 @@ head_bwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
 #pragma unroll 2
       for (int j = 0; j < F1; ++j) {
         float4 d = *reinterpret_cast<const float4*>(dp_s + j * HB_DPS + sgD * 4);
-        float4 wa = __ldg(reinterpret_cast<const float4*>(w1g + j * A2_PER + igD * 4));
-        float4 wb = __ldg(reinterpret_cast<const float4*>(w1g + j * A2_PER + 160 + igD * 4));
+        float4 wa = *reinterpret_cast<const float4*>(w1_s + j * A2_PER + igD * 4);
+        float4 wb = *reinterpret_cast<const float4*>(w1_s + j * A2_PER + 160 + igD * 4);
         float dv[4] = {d.x, d.y, d.z, d.w};
         float wv[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
 #pragma unroll
@@ -420,27 +433,42 @@ constexpr int W1_DYS = C1 * 576;
 __global__ void __launch_bounds__(W1_THREADS, 3)
 conv1_wgrad_kernel(const float* __restrict__ dp1, const uint8_t* __restrict__ idx1,
                    const float* __restrict__ x, float* __restrict__ partials, int B) {
-  __shared__ __align__(16) float dy_s[W1_DYS];
-  __shared__ __align__(16) float x_s[IMG_PIX];
-  __shared__ float red_s[256 * 5];
+  __shared__ __align__(128) float dy_s[W1_DYS];                 // dense dy1 of the current sample; reused for reductions
+  __shared__ __align__(128) float x_s2[2][IMG_PIX];             // double-buffered raw inputs, bulk-copied a sample ahead
+  __shared__ __align__(128) float dp_s2[2][A1_PER];
+  __shared__ __align__(128) uint8_t ix_s2[2][A1_PER];
+  __shared__ __align__(8) uint64_t bar[2];
+  float* red_s = dy_s;                                           // [256*5] after the sample loop
   const int tid = threadIdx.x;
   const int kh = tid % 5, chunk = (tid / 5) % 5, c = tid / 25;  // c < 10 for tid < 250
   const bool active = tid < 250;
   const int oy0 = chunk * 5, oy1 = min(24, oy0 + 5);
+  auto issue = [&](int b, int buf) {                             // thread 0: prefetch one sample's x, dp1, idx1
+    mbarrier_expect_tx(&bar[buf], IMG_PIX * 4 + A1_PER * 4 + A1_PER);
+    bulk_copy_g2s(x_s2[buf], x + size_t(b) * IMG_PIX, IMG_PIX * 4, &bar[buf]);
+    bulk_copy_g2s(dp_s2[buf], dp1 + size_t(b) * A1_PER, A1_PER * 4, &bar[buf]);
+    bulk_copy_g2s(ix_s2[buf], idx1 + size_t(b) * A1_PER, A1_PER, &bar[buf]);
+  };
+  if (tid == 0) {
+    mbarrier_init(&bar[0], 1); mbarrier_init(&bar[1], 1);
+    if (int(blockIdx.x) < B) issue(blockIdx.x, 0);
+    if (int(blockIdx.x + gridDim.x) < B) issue(blockIdx.x + gridDim.x, 1);
+  }
+  __syncthreads();
   float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
   float acc2[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
   float bacc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // entries tid + 256*q of the 1440 (c,p) cells
-  for (int b = blockIdx.x; b < B; b += gridDim.x) {
-    __syncthreads();
-    if (tid < IMG_PIX / 4)
-      reinterpret_cast<float4*>(x_s)[tid] = __ldg(reinterpret_cast<const float4*>(x + size_t(b) * IMG_PIX) + tid);
+  uint32_t it = 0;
+  for (int b = blockIdx.x; b < B; b += gridDim.x, ++it) {
+    const int buf = it & 1;
+    mbarrier_wait(&bar[buf], (it >> 1) & 1);
+    const float* x_s = x_s2[buf];
 #pragma unroll
     for (int q = 0; q < 6; ++q) {
       const int e = tid + q * W1_THREADS;   // = cc*144 + p
       if (e < A1_PER) {
-        const size_t o = size_t(b) * A1_PER + e;
-        const float gv = dp1[o];
-        const int id = idx1[o];
+        const float gv = dp_s2[buf][e];
+        const int id = ix_s2[buf][e];
         const int cc = e / 144, p = e % 144, py = p / 12, px = p % 12;
         bacc[q] += gv;
         float* d = dy_s + cc * 576 + (2 * py) * 24 + 2 * px;
@@ -474,9 +502,10 @@ conv1_wgrad_kernel(const float* __restrict__ dp1, const uint8_t* __restrict__ id
           }
       }
     }
+    __syncthreads();                                             // dy_s and the raw buffers of `buf` are free
+    if (tid == 0 && b + 2 * int(gridDim.x) < B) issue(b + 2 * gridDim.x, buf);
   }
   // combine the 5 row-chunks in fixed order
-  __syncthreads();
 #pragma unroll
   for (int k = 0; k < 5; ++k) red_s[tid * 5 + k] = acc[k] + acc2[k];
   __syncthreads();
@@ -503,13 +532,13 @@ conv1_wgrad_kernel(const float* __restrict__ dp1, const uint8_t* __restrict__ id
     float s = 0.f;
 #pragma unroll
     for (int i = 0; i < 9; ++i) s += dy_s[cc * 144 + l * 9 + i];
-    red_s[tid] = s;
+    dy_s[2048 + tid] = s;            // second stage lives past the 1440 staged cells (red_s aliases dy_s)
   }
   __syncthreads();
   if (tid < C1) {
     float s = 0.f;
 #pragma unroll
-    for (int l = 0; l < 16; ++l) s += red_s[tid * 16 + l];
+    for (int l = 0; l < 16; ++l) s += dy_s[2048 + tid * 16 + l];
     part[OFF_C1B + tid] = s;
   }
 }
@@ -596,13 +625,13 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
   {
     int nstages = (B + W2_NS - 1) / W2_NS;
     parts_c2 = nstages < MAX_PARTS ? nstages : MAX_PARTS;
-    if (parts_c2 > sms * 2) parts_c2 = sms * 2;
+    if (parts_c2 > sms * 3) parts_c2 = sms * 3;      // 3 CTAs/SM: one stages while the others compute
     conv2_wgrad_kernel<<<parts_c2, W2_THREADS, 0, stream>>>(sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale,
                                                            sc.partials, B);
   }
   prof_mark(7, stream);
   {
-    parts_c1 = B < sms * 2 ? B : sms * 2;
+    parts_c1 = B < sms * 3 ? B : sms * 3;
     if (parts_c1 > MAX_PARTS) parts_c1 = MAX_PARTS;
     conv1_wgrad_kernel<<<parts_c1, W1_THREADS, 0, stream>>>(sc.dp1, ws.idx1, x, sc.partials, B);
   }

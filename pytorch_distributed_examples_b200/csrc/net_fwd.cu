@@ -27,25 +27,36 @@ conv1_fwd_kernel(const float* __restrict__ params, const float* __restrict__ x,
                  float* __restrict__ a1, uint8_t* __restrict__ idx1, int B) {
   __shared__ __align__(16) float w_s[25 * 12];   // [tap][c padded to 12]
   __shared__ float b_s[12];
-  __shared__ __align__(16) float img[2 * IMG_PIX];
+  __shared__ __align__(128) float img_s[2][2 * IMG_PIX];   // double-buffered pair of images (bulk-copied)
+  __shared__ __align__(8) uint64_t bar[2];
   const int tid = threadIdx.x;
+  const int npairs = (B + 1) >> 1;
+  auto issue = [&](int pair, int buf) {                    // thread 0: prefetch a pair of images
+    const int b0 = pair * 2;
+    const uint32_t bytes = uint32_t(min(2, B - b0)) * (IMG_PIX * 4);
+    mbarrier_expect_tx(&bar[buf], bytes);
+    bulk_copy_g2s(img_s[buf], x + size_t(b0) * IMG_PIX, bytes, &bar[buf]);
+  };
+  if (tid == 0) {
+    mbarrier_init(&bar[0], 1); mbarrier_init(&bar[1], 1);
+    if (int(blockIdx.x) < npairs) issue(blockIdx.x, 0);
+    if (int(blockIdx.x + gridDim.x) < npairs) issue(blockIdx.x + gridDim.x, 1);
+  }
   for (int i = tid; i < 25 * 12; i += F1_THREADS) {
     int tap = i / 12, c = i % 12;
     w_s[i] = c < C1 ? params[OFF_C1W + c * 25 + tap] : 0.f;
   }
   if (tid < 12) b_s[tid] = tid < C1 ? params[OFF_C1B + tid] : 0.f;
+  __syncthreads();
   const int s = tid / 144, p = tid % 144, py = p / 12, px = p % 12;
-  const int npairs = (B + 1) >> 1;
-  for (int pair = blockIdx.x; pair < npairs; pair += gridDim.x) {
+  uint32_t it = 0;
+  for (int pair = blockIdx.x; pair < npairs; pair += gridDim.x, ++it) {
+    const int buf = it & 1;
     const int b0 = pair * 2;
     const int nvalid = min(2, B - b0);
-    __syncthreads();
-    const float4* src = reinterpret_cast<const float4*>(x + size_t(b0) * IMG_PIX);
-    float4* dst = reinterpret_cast<float4*>(img);
-    for (int i = tid; i < nvalid * (IMG_PIX / 4); i += F1_THREADS) dst[i] = __ldg(src + i);
-    __syncthreads();
-    if (s >= nvalid) continue;
-
+    mbarrier_wait(&bar[buf], (it >> 1) & 1);
+    const float* img = img_s[buf];
+    if (s < nvalid) {
     float patch[6][6];
     const float* ip = img + s * IMG_PIX + (2 * py) * IMG + 2 * px;
 #pragma unroll
@@ -84,21 +95,24 @@ conv1_fwd_kernel(const float* __restrict__ params, const float* __restrict__ x,
       a1[ob + c * 144] = fmaxf(best, 0.f);
       idx1[ob + c * 144] = uint8_t(bi);
     }
+    }
+    __syncthreads();                                        // everyone is done with img_s[buf]
+    if (tid == 0 && pair + 2 * int(gridDim.x) < npairs) issue(pair + 2 * gridDim.x, buf);
   }
 }
 
 // ---------------------------------------------------------------------------
-// K_F3: head.  Tile of 16 samples per CTA iteration.  fc1 is split-K over the lanes of a warp:
-// warp = 4 fc1 outputs, lane = (k-quarter, sample pair); the 4 partial sums meet with two shuffles.
-// 13 warps per CTA and several CTAs per SM keep enough warps in flight for this latency-bound layer.
-// fc1.weight (64 KB) is read through L1 with ld.global.nc (prefetched once per CTA) instead of being
-// staged in shared memory; only the a2 tile and the small fc2 operands live in shared memory.
+// K_F3: head.  Tile of 16 samples per CTA iteration.  fc1.weight (64 KB) and the a2 tile arrive in shared
+// memory by cp.async.bulk (one thread issues, an mbarrier counts the bytes) -- no register staging, no chain
+// of exposed L2 latencies.  fc1 is split-K over the lanes of a warp: warp = 4 fc1 outputs, lane =
+// (k-quarter, sample pair); the 4 partial sums meet with two shuffles.  13 warps per CTA, 2 CTAs per SM.
 // ---------------------------------------------------------------------------
 constexpr int HT = 16;              // samples per tile
 constexpr int HF_WARPS = 13;        // one warp per fc1 output quad (52 >= 50)
 constexpr int HF_THREADS = HF_WARPS * 32;
-constexpr int HF_A2S = 324;         // a2 row stride (floats)
+constexpr int HF_A2S = 324;         // a2 row stride (floats): conflict-free LDS.128 across samples
 constexpr int HF_HS = 53;           // h row stride
+constexpr int HF_SMEM = (F1 * A2_PER + HT * HF_A2S + 52 + HT * HF_HS + 50 * 12 + 12 + HT * 12) * 4 + 16;
 __global__ void __launch_bounds__(HF_THREADS, 2)
 head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
                 const int64_t* __restrict__ target, const float* __restrict__ mask1d,
@@ -107,16 +121,29 @@ head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
                 float* __restrict__ logp_out, float* __restrict__ loss_out,
                 int64_t* __restrict__ argmax_out, unsigned long long* __restrict__ correct_out,
                 float* __restrict__ loss_part, unsigned int* __restrict__ counters, int B) {
-  __shared__ __align__(16) float a2_s[HT * HF_A2S];   // [16][324]
-  __shared__ float b1_s[52];
-  __shared__ float h_s[HT * HF_HS];                   // [16][53]
-  __shared__ __align__(16) float w2_s[50 * 12];       // [k][c padded to 12]
-  __shared__ float b2_s[12];
-  __shared__ float z_s[HT * 12];
+  extern __shared__ __align__(128) float smem[];
+  float* w1_s = smem;                    // [50][320] natural layout (bulk copy)
+  float* a2_s = w1_s + F1 * A2_PER;      // [16][324]
+  float* b1_s = a2_s + HT * HF_A2S;      // [52]
+  float* h_s = b1_s + 52;                // [16][53]
+  float* w2_s = h_s + HT * HF_HS;        // [50][12]
+  float* b2_s = w2_s + 50 * 12;          // [12]
+  float* z_s = b2_s + 12;                // [16][12]
+  uint64_t* bar = reinterpret_cast<uint64_t*>(z_s + HT * 12);   // 8-byte aligned: all sizes above are even
   if (offset_dev) offset += uint64_t(*offset_dev);
   const int tid = threadIdx.x;
-  const float* w1g = params + OFF_F1W;
-  prefetch_l1_range(w1g, F1 * A2_PER, tid, HF_THREADS);
+  const int ntiles = (B + HT - 1) / HT;
+  if (tid == 0) mbarrier_init(bar, 1);
+  __syncthreads();
+  auto issue_tile = [&](int tile, bool with_w1) {       // thread 0 only
+    const int b0 = tile * HT;
+    const int nvalid = min(HT, B - b0);
+    mbarrier_expect_tx(bar, uint32_t(nvalid) * (A2_PER * 4) + (with_w1 ? F1 * A2_PER * 4 : 0));
+    if (with_w1) bulk_copy_g2s(w1_s, params + OFF_F1W, F1 * A2_PER * 4, bar);
+    for (int s = 0; s < nvalid; ++s)
+      bulk_copy_g2s(a2_s + s * HF_A2S, a2 + size_t(b0 + s) * A2_PER, A2_PER * 4, bar);
+  };
+  if (tid == 0 && blockIdx.x < ntiles) issue_tile(blockIdx.x, true);
   if (tid < 52) b1_s[tid] = tid < F1 ? params[OFF_F1B + tid] : 0.f;
   for (int i = tid; i < 50 * 12; i += HF_THREADS) {
     int k = i / 12, c = i % 12;
@@ -128,19 +155,17 @@ head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
   int jrow[4];
 #pragma unroll
   for (int jj = 0; jj < 4; ++jj) jrow[jj] = min(jg * 4 + jj, F1 - 1) * A2_PER + kp * 80;   // clamp: cols 50,51 discarded
-  const int ntiles = (B + HT - 1) / HT;
   float loss_acc = 0.f;                    // thread 0 only
   int corr_acc = 0;
+  uint32_t phase = 0;
   for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int b0 = tile * HT;
     const int nvalid = min(HT, B - b0);
-    __syncthreads();
-    for (int i = tid; i < HT * (A2_PER / 4); i += HF_THREADS) {
-      int s = i / (A2_PER / 4), k4 = i % (A2_PER / 4);
-      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (s < nvalid) v = *reinterpret_cast<const float4*>(a2 + size_t(b0 + s) * A2_PER + k4 * 4);
-      *reinterpret_cast<float4*>(a2_s + s * HF_A2S + k4 * 4) = v;
-    }
+    // rows past the batch are not copied: keep them finite
+    for (int i = tid; i < (HT - nvalid) * A2_PER; i += HF_THREADS)
+      a2_s[(nvalid + i / A2_PER) * HF_A2S + i % A2_PER] = 0.f;
+    mbarrier_wait(bar, phase);
+    phase ^= 1u;
     __syncthreads();
     {
       float acc[2][4];
@@ -156,7 +181,7 @@ head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
         float4 x1 = *reinterpret_cast<const float4*>(ar1 + k);
 #pragma unroll
         for (int jj = 0; jj < 4; ++jj) {
-          float4 w = __ldg(reinterpret_cast<const float4*>(w1g + jrow[jj] + k));
+          float4 w = *reinterpret_cast<const float4*>(w1_s + jrow[jj] + k);
           acc[0][jj] = fmaf(x0.x, w.x, acc[0][jj]); acc[0][jj] = fmaf(x0.y, w.y, acc[0][jj]);
           acc[0][jj] = fmaf(x0.z, w.z, acc[0][jj]); acc[0][jj] = fmaf(x0.w, w.w, acc[0][jj]);
           acc[1][jj] = fmaf(x1.x, w.x, acc[1][jj]); acc[1][jj] = fmaf(x1.y, w.y, acc[1][jj]);
@@ -196,6 +221,8 @@ head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
       }
     }
     __syncthreads();
+    // the a2 tile is consumed: prefetch the next one while fc2 / softmax run
+    if (tid == 0 && tile + int(gridDim.x) < ntiles) issue_tile(tile + gridDim.x, false);
     // fc2: thread (s, class pair)
     if (tid < HT * 5) {
       const int s = tid / 5, c2 = (tid % 5) * 2;
@@ -312,7 +339,12 @@ extern "C" int ddp_net_forward(const float* params, const float* x, const int64_
     int grid = ntiles < MAX_PARTS ? ntiles : MAX_PARTS;   // one loss partial per CTA
     Scratch sc{};
     if (scratch) sc = carve_scratch(scratch, batch);
-    head_fwd_kernel<<<grid, HF_THREADS, 0, stream>>>(
+    static bool attr_done = false;
+    if (!attr_done) {
+      DDP_CUDA(cudaFuncSetAttribute(head_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HF_SMEM));
+      attr_done = true;
+    }
+    head_fwd_kernel<<<grid, HF_THREADS, HF_SMEM, stream>>>(
         params, ws.a2, target, mask1d, seed, offset, offset_dev, training, ws.h, out_logp, out_loss, out_argmax,
         reinterpret_cast<unsigned long long*>(out_correct), sc.loss_part, sc.counters, B);
   }
