@@ -126,6 +126,9 @@ typedef struct {
   double beta1, beta2, eps, rho;
   int nesterov;
   int write_back_grad; /* 1: store the averaged gradient back into grad (f32 only) */
+  int bump_step_dev;   /* 1 (with step_dev != NULL): the kernel's last CTA also does *step_dev += 1,
+                          saving the separate ddp_step_increment launch; calls on different streams
+                          must then not overlap (one library-internal ticket counter) */
 } ddp_hyper_t;
 int ddp_fused_update(int opt, const void* grad, int grad_dtype, float* params,
                      float* state1, float* state2, int64_t n, float inv_world,

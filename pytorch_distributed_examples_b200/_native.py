@@ -27,7 +27,7 @@ BUCKET_CHUNK_BYTES = 16384
 class Hyper(ctypes.Structure):
     _fields_ = [("lr", c_double), ("momentum", c_double), ("dampening", c_double), ("weight_decay", c_double),
                 ("beta1", c_double), ("beta2", c_double), ("eps", c_double), ("rho", c_double),
-                ("nesterov", c_int), ("write_back_grad", c_int)]
+                ("nesterov", c_int), ("write_back_grad", c_int), ("bump_step_dev", c_int)]
 
 
 # name -> (restype, argtypes); also the list of symbols the not-gpu test checks against include/ddp_step.h

@@ -545,36 +545,39 @@ conv1_wgrad_kernel(const float* __restrict__ dp1, const uint8_t* __restrict__ id
 
 // ---------------------------------------------------------------------------
 // K_R reduce per-CTA partials into the gradient bucket, fixed order.
-// 256 threads = 8 warps x 32 consecutive elements; warp w sums parts w, w+8, ...
+// 1024 threads = 32 warps x 32 consecutive elements; warp w sums parts w, w+32, ... (all its loads in flight at
+// once), then warp 0 adds the 32 warp sums in order.
 // ---------------------------------------------------------------------------
 __device__ __forceinline__ bool arena_is_pad(int e) {
   return (e >= 250 && e < OFF_C1B) || (e >= OFF_C1B + 10 && e < OFF_C2W) ||
          (e >= OFF_F1B + 50 && e < OFF_F2W) || (e >= OFF_F2B + 10);
 }
-__global__ void __launch_bounds__(256)
+constexpr int RP_WARPS = 32;
+__global__ void __launch_bounds__(RP_WARPS * 32)
 reduce_partials_kernel(const float* __restrict__ partials, int parts_c1, int parts_c2,
                        int parts_head, float* __restrict__ bucket) {
-  __shared__ float red[8][33];
+  __shared__ float red[RP_WARPS][33];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int e = blockIdx.x * 32 + lane;
   float s = 0.f;
   if (e < P_ARENA && !arena_is_pad(e)) {
     const int parts = e < OFF_C2W ? parts_c1 : (e < OFF_F1W ? parts_c2 : parts_head);
     const float* p = partials + e;
-    int i = warp;
-    for (; i + 24 < parts; i += 32) {
-      float v0 = p[size_t(i) * P_ARENA], v1 = p[size_t(i + 8) * P_ARENA];
-      float v2 = p[size_t(i + 16) * P_ARENA], v3 = p[size_t(i + 24) * P_ARENA];
-      s += v0; s += v1; s += v2; s += v3;
+    float v[(MAX_PARTS + RP_WARPS - 1) / RP_WARPS];
+#pragma unroll
+    for (int q = 0; q < (MAX_PARTS + RP_WARPS - 1) / RP_WARPS; ++q) {
+      const int i = warp + q * RP_WARPS;
+      v[q] = i < parts ? __ldcg(p + size_t(i) * P_ARENA) : 0.f;
     }
-    for (; i < parts; i += 8) s += p[size_t(i) * P_ARENA];
+#pragma unroll
+    for (int q = 0; q < (MAX_PARTS + RP_WARPS - 1) / RP_WARPS; ++q) s += v[q];
   }
   red[warp][lane] = s;
   __syncthreads();
   if (warp == 0 && e < P_ARENA) {
     float t = 0.f;
 #pragma unroll
-    for (int w = 0; w < 8; ++w) t += red[w][lane];
+    for (int w = 0; w < RP_WARPS; ++w) t += red[w][lane];
     bucket[e] = t;
   }
 }
@@ -636,7 +639,7 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
     conv1_wgrad_kernel<<<parts_c1, W1_THREADS, 0, stream>>>(sc.dp1, ws.idx1, x, sc.partials, B);
   }
   prof_mark(8, stream);
-  reduce_partials_kernel<<<(P_ARENA + 31) / 32, 256, 0, stream>>>(sc.partials, parts_c1, parts_c2,
+  reduce_partials_kernel<<<(P_ARENA + 31) / 32, RP_WARPS * 32, 0, stream>>>(sc.partials, parts_c1, parts_c2,
                                                                   parts_head, grad_bucket);
   prof_mark(9, stream);
   DDP_CUDA(cudaGetLastError());

@@ -98,6 +98,7 @@ peer_allreduce_kernel(PeerDev pd, const float* __restrict__ bucket, float* __res
       for (int p = 0; p < W; ++p) st_release_sys(pd.flags[p] + (par * W + R) * PEER_FLAG_STRIDE, e);
       *pd.ticket = 0u;
       *pd.epoch = e;
+      if (UPDATE && kc.bump_step && step_dev) *const_cast<int64_t*>(step_dev) += 1;   // all CTAs read it at their start
     }
   }
   // 3. wait for every source's flag for this epoch

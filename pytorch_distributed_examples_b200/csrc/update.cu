@@ -13,6 +13,8 @@
 
 namespace ddp {
 
+__device__ unsigned int g_update_ticket = 0;   // last-CTA detection for bump_step_dev
+
 template <int OPT, bool HAS1, bool HAS2, typename GT>
 __global__ void __launch_bounds__(256)
 fused_update_kernel(const GT* __restrict__ grad, float* __restrict__ params, float* __restrict__ state1,
@@ -66,6 +68,16 @@ fused_update_kernel(const GT* __restrict__ grad, float* __restrict__ params, flo
     if (HAS1) state1[i] = s1;
     if (HAS2) state2[i] = s2;
     if (grad_wb) grad_wb[i] = go;
+  }
+  if (k.bump_step && step_dev) {            // every CTA read *step_dev at its start, before taking a ticket
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      if (atomicAdd(&g_update_ticket, 1u) == gridDim.x - 1) {
+        g_update_ticket = 0u;
+        *const_cast<int64_t*>(step_dev) += 1;
+      }
+    }
   }
 }
 

@@ -13,7 +13,7 @@ struct UpdateConsts {
   float step_size, bc2_sqrt;   // Adam: lr/(1-beta1^t), sqrt(1-beta2^t)
   float decay;                 // AdamW: 1 - lr*wd
   double lr_d, beta1_d, beta2_d;
-  int nesterov, first_step, write_back;
+  int nesterov, first_step, write_back, bump_step;
 };
 
 template <int OPT>
@@ -79,7 +79,7 @@ inline UpdateConsts make_update_consts(const ddp_hyper_t* h, float inv_world) {
   k.eps = float(h->eps); k.rho = float(h->rho); k.one_minus_rho = float(1.0 - h->rho);
   k.decay = float(1.0 - h->lr * h->weight_decay);
   k.lr_d = h->lr; k.beta1_d = h->beta1; k.beta2_d = h->beta2;
-  k.nesterov = h->nesterov; k.write_back = h->write_back_grad;
+  k.nesterov = h->nesterov; k.write_back = h->write_back_grad; k.bump_step = h->bump_step_dev;
   return k;
 }
 

@@ -141,10 +141,10 @@ class _Group:
         self.ensure_state()
         nat = _native.get()
         self.steps += 1
+        hyper = self.hyper()
+        hyper.bump_step_dev = int(bool(use_step_dev))     # the update kernel's last CTA advances the device counter
         nat.fused_update(self.kind, self.bucket, self.param_arena, self.state1, self.state2, self.layout.total,
-                         inv_world, self.hyper(), step=self.steps, step_dev=self.step_dev if use_step_dev else None)
-        if use_step_dev:
-            nat.step_increment(self.step_dev)
+                         inv_world, hyper, step=self.steps, step_dev=self.step_dev if use_step_dev else None)
 
     def update_peer(self, comm, use_step_dev=False):
         """allreduce(sum) over NVLink peer memory + 1/N + update in ONE kernel (csrc/peer.cu)."""
@@ -152,11 +152,11 @@ class _Group:
         self.ensure_state()
         nat = _native.get()
         self.steps += 1
+        hyper = self.hyper()
+        hyper.bump_step_dev = int(bool(use_step_dev))
         nat.peer_allreduce_update(comm.peer, self.kind, self.bucket, self.param_arena, self.state1, self.state2,
-                                  self.layout.total, self.hyper(), step=self.steps,
+                                  self.layout.total, hyper, step=self.steps,
                                   step_dev=self.step_dev if use_step_dev else None)
-        if use_step_dev:
-            nat.step_increment(self.step_dev)
 
     # -- torch.optim state interop (state_dict / load_state_dict / elastic commit) --------------------
     _STATE_KEYS = {_native.OPT_SGD: ("momentum_buffer", None), _native.OPT_ADAM: ("exp_avg", "exp_avg_sq"),

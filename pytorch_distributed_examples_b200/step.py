@@ -22,7 +22,7 @@ from . import _native
 from .net import Net
 from .optim import FusedUpdater
 
-KERNELS_PER_STEP = 3 + 5 + 2   # forward, backward(+reduce), fused update + step counter
+KERNELS_PER_STEP = 3 + 5 + 1   # forward, backward(+reduce), fused update (which also advances the step counter)
 
 
 class TrainStep:

@@ -54,6 +54,8 @@ class FakeNative:
             raise NotImplementedError
         if hyper.write_back_grad:
             grad.copy_(g)
+        if hyper.bump_step_dev and step_dev is not None:
+            step_dev += 1
 
     def step_increment(self, step_dev):
         step_dev += 1
