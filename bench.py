@@ -394,8 +394,12 @@ def main():
         achieved = flops / dur_s / 1e12
         sm_mhz = clock_info.get("sm_mhz") or 1900.0
         ffma_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "r01_ncu_traffic_b4096.json")
+        if B == 4096 and os.path.exists(tpath):          # DRAM bytes per launch from the committed ncu --set full capture
+            traffic = json.load(open(tpath)).get(top)
         line["roofline"] = {"kernel": top, "bound": "tensor", "achieved": achieved, "peak": peaks["tflops"],
-                            "unit": "TFLOP/s", "frac": achieved / peaks["tflops"], "traffic": None,
+                            "unit": "TFLOP/s", "frac": achieved / peaks["tflops"], "traffic": traffic,
                             "peak_source": f"MEASURED_PEAKS.json bf16 sustained ({peaks['source']})",
                             "note": "fp32 FFMA kernel (1e-5 parity bar rules out single-pass TF32/BF16); "
                                     "fraction of the fp32 FFMA peak given beside it",
