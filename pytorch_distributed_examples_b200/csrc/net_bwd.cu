@@ -25,7 +25,7 @@ head_bwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
                 const float* __restrict__ dlogp, const int64_t* __restrict__ target,
                 float nll_coef, float drop_scale, float* __restrict__ da2,
                 float* __restrict__ partials, int B) {
-  extern __shared__ __align__(16) float smem[];
+  extern __shared__ __align__(128) float smem[];
   // fc1.weight (64 KB) and each a2 tile arrive by cp.async.bulk + mbarrier (no register staging)
   float* w1_s = smem;                     // [50][320] natural layout
   float* a2_s = w1_s + F1 * A2_PER;       // [32][324]
@@ -205,20 +205,20 @@ head_bwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
 // da2/a2/idx2; out-of-range taps are predicated to zero.
 // Output dp1 = da1 * (a1 > 0): gradient w.r.t. the pooled conv1 map before ReLU.
 // ---------------------------------------------------------------------------
-constexpr int D2_WARPS = 16;
+constexpr int D2_WARPS = 8;
 constexpr int D2_THREADS = D2_WARPS * 32;
 constexpr int D2_WS = C2 * 25 * 2 * 8;              // [co][tap][g][8]
-constexpr int D2_PER_WARP = C2 * 64 + A1_PER;       // dy2 + staged output
+constexpr int D2_PER_WARP = A1_PER;                // dy2 [20][8][8] (1280 floats), later reused for the staged output [10][144]
 constexpr int D2_SMEM = (D2_WS + D2_WARPS * D2_PER_WARP) * 4;
-__global__ void __launch_bounds__(D2_THREADS, 1)
+__global__ void __launch_bounds__(D2_THREADS, 2)
 conv2_dgrad_kernel(const float* __restrict__ params, const float* __restrict__ da2,
                    const float* __restrict__ a2, const uint8_t* __restrict__ idx2,
                    const float* __restrict__ a1, float drop_scale, float* __restrict__ dp1, int B) {
-  extern __shared__ __align__(16) float smem[];
+  extern __shared__ __align__(128) float smem[];
   float* w_s = smem;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   float* dy_s = smem + D2_WS + warp * D2_PER_WARP;  // [20][8][8]
-  float* out_s = dy_s + C2 * 64;                    // [10][144]
+  float* out_s = dy_s;                              // [10][144]: written only after the last read of dy2
   for (int i = tid; i < D2_WS; i += D2_THREADS) {
     int cc = i & 7, g = (i >> 3) & 1, ct = i >> 4;  // ct = co*25 + tap
     int co = ct / 25, tap = ct % 25;
@@ -291,6 +291,7 @@ conv2_dgrad_kernel(const float* __restrict__ params, const float* __restrict__ d
         }
     }
     // stage through smem so the global store (and the a1 mask read) is coalesced
+    __syncwarp();                                     // every lane is done reading dy2 before it is overwritten
 #pragma unroll
     for (int k = 0; k < 5; ++k)
 #pragma unroll
@@ -322,43 +323,68 @@ constexpr int W2_NS = 2;                              // samples per stage
 constexpr int W2_DYS = O2 * C2 * O2;                  // [oy][co][ox] = 1280
 constexpr int W2_CS = 156;                            // a1 channel stride in smem (144 used): bank = 12*(ci*5+kh) mod 32
 constexpr int W2_A1S = C1 * W2_CS;                    // per-sample a1 footprint in smem
+// shared-memory layout (dynamic): a1 double-buffered in its padded layout (bulk-copied per channel), raw a2 / da2 /
+// idx2 double-buffered, dy2 + bias staging + live flags single
+constexpr int W2_RAW = W2_NS * A2_PER;                          // floats of a2 (or da2) per stage
+constexpr int W2_SMEM = (2 * W2_NS * W2_A1S + 2 * 2 * W2_RAW + W2_NS * W2_DYS + A2_PER) * 4 + 2 * W2_RAW + W2_NS * C2 * 4 + 32;
 __global__ void __launch_bounds__(W2_THREADS, 3)
 conv2_wgrad_kernel(const float* __restrict__ da2, const float* __restrict__ a2,
                    const uint8_t* __restrict__ idx2, const float* __restrict__ a1,
                    float drop_scale, float* __restrict__ partials, int B) {
-  __shared__ __align__(16) float a1_s[W2_NS * W2_A1S];
-  __shared__ __align__(16) float dy_s[W2_NS * W2_DYS];
-  __shared__ float bsum_s[A2_PER];
-  __shared__ int live_s[W2_NS * C2];   // (sample, co) has any gradient: dead channels are skipped
+  extern __shared__ __align__(128) float smem[];
+  float* a1_s2 = smem;                                   // [2][W2_NS][10][156]
+  float* ra2 = a1_s2 + 2 * W2_NS * W2_A1S;               // [2][W2_NS*320] raw a2
+  float* rda2 = ra2 + 2 * W2_RAW;                        // [2][W2_NS*320] raw da2
+  float* dy_s = rda2 + 2 * W2_RAW;                       // [W2_NS][8][20][8]
+  float* bsum_s = dy_s + W2_NS * W2_DYS;                 // [320]
+  int* live_s = reinterpret_cast<int*>(bsum_s + A2_PER); // [W2_NS*20]
+  uint64_t* bar = reinterpret_cast<uint64_t*>(live_s + W2_NS * C2);   // [2]
+  uint8_t* ridx = reinterpret_cast<uint8_t*>(bar + 2);   // [2][W2_NS*320] raw idx2
   const int tid = threadIdx.x;
   // cq (output-channel residue mod 5) is the SLOWEST index so that a warp is (almost) uniform in co
   // and the dead-channel skip below is (almost) divergence-free
   const int cq = tid / 50, kh = tid % 5, ci = (tid % 50) / 5;   // cq < 5 for tid < 250
   const bool active = tid < 250;
+  const int nstages = (B + W2_NS - 1) / W2_NS;
+  auto issue = [&](int st, int buf) {                    // thread 0: prefetch one stage's inputs (cp.async.bulk)
+    const int b0 = st * W2_NS;
+    const int nv = min(W2_NS, B - b0);
+    mbarrier_expect_tx(&bar[buf], uint32_t(nv) * (A1_PER * 4 + 2 * A2_PER * 4 + A2_PER));
+    for (int s = 0; s < nv; ++s)
+      for (int c = 0; c < C1; ++c)                       // channel by channel into the conflict-free padded layout
+        bulk_copy_g2s(a1_s2 + (buf * W2_NS + s) * W2_A1S + c * W2_CS, a1 + size_t(b0 + s) * A1_PER + c * 144, 144 * 4, &bar[buf]);
+    bulk_copy_g2s(ra2 + buf * W2_RAW, a2 + size_t(b0) * A2_PER, uint32_t(nv) * A2_PER * 4, &bar[buf]);
+    bulk_copy_g2s(rda2 + buf * W2_RAW, da2 + size_t(b0) * A2_PER, uint32_t(nv) * A2_PER * 4, &bar[buf]);
+    bulk_copy_g2s(ridx + buf * W2_RAW, idx2 + size_t(b0) * A2_PER, uint32_t(nv) * A2_PER, &bar[buf]);
+  };
+  if (tid == 0) {
+    mbarrier_init(&bar[0], 1); mbarrier_init(&bar[1], 1);
+    if (int(blockIdx.x) < nstages) issue(blockIdx.x, 0);
+    if (int(blockIdx.x + gridDim.x) < nstages) issue(blockIdx.x + gridDim.x, 1);
+  }
+  __syncthreads();
   float acc[4][5];
 #pragma unroll
   for (int j = 0; j < 4; ++j)
 #pragma unroll
     for (int k = 0; k < 5; ++k) acc[j][k] = 0.f;
   float bacc[2] = {0.f, 0.f};  // bias-gradient share of entries tid and tid+256
-  const int nstages = (B + W2_NS - 1) / W2_NS;
-  for (int st = blockIdx.x; st < nstages; st += gridDim.x) {
+  uint32_t it = 0;
+  for (int st = blockIdx.x; st < nstages; st += gridDim.x, ++it) {
+    const int buf = it & 1;
     const int b0 = st * W2_NS;
     const int nvalid = min(W2_NS, B - b0);
-    __syncthreads();
-    const float4* src = reinterpret_cast<const float4*>(a1 + size_t(b0) * A1_PER);
-    for (int i = tid; i < nvalid * (A1_PER / 4); i += W2_THREADS) {
-      const int s = i / (A1_PER / 4), r = i % (A1_PER / 4), c = r / 36, w = r % 36;   // 36 float4 per channel
-      reinterpret_cast<float4*>(a1_s + s * W2_A1S + c * W2_CS)[w] = src[i];
-    }
+    mbarrier_wait(&bar[buf], (it >> 1) & 1);
+    const float* a1_s = a1_s2 + buf * W2_NS * W2_A1S;
+    // dy2 (one non-zero per 2x2 pool window) from the raw tiles, all in shared memory
     for (int s = 0; s < nvalid; ++s) {
 #pragma unroll
       for (int q = 0; q < 2; ++q) {
         const int e = tid + q * W2_THREADS;
         if (e < A2_PER) {
-          const size_t o = size_t(b0 + s) * A2_PER + e;
-          const float gv = a2[o] > 0.f ? da2[o] * drop_scale : 0.f;
-          const int id = idx2[o];
+          const int o = buf * W2_RAW + s * A2_PER + e;
+          const float gv = ra2[o] > 0.f ? rda2[o] * drop_scale : 0.f;
+          const int id = ridx[o];
           const int co = e >> 4, pp = e & 15, py = pp >> 2, px = pp & 3;
           bacc[q] += gv;
           const unsigned bal = __ballot_sync(0xffffffffu, gv != 0.f);   // e < 320 is warp-uniform here
@@ -401,6 +427,8 @@ conv2_wgrad_kernel(const float* __restrict__ da2, const float* __restrict__ a2,
         }
       }
     }
+    __syncthreads();                                     // dy_s and the buffers of `buf` are free
+    if (tid == 0 && st + 2 * int(gridDim.x) < nstages) issue(st + 2 * gridDim.x, buf);
   }
   float* part = partials + size_t(blockIdx.x) * P_ARENA;
   if (active) {
@@ -607,6 +635,7 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
   if (!attr_done) {
     DDP_CUDA(cudaFuncSetAttribute(head_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HB_SMEM));
     DDP_CUDA(cudaFuncSetAttribute(conv2_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, D2_SMEM));
+    DDP_CUDA(cudaFuncSetAttribute(conv2_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, W2_SMEM));
     attr_done = true;
   }
   int parts_head, parts_c2, parts_c1;
@@ -618,9 +647,11 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
                                                                  nll_coef, drop_scale, sc.da2, sc.partials, B);
   }
   prof_mark(5, stream);
+  // (conv2_wgrad is independent of dgrad -> conv1_wgrad and was tried on a forked stream: each kernel already
+  //  fills the register files, so the CTAs do not co-reside and shrinking the grids to make them fit lost 30 %.)
   {
     int nblk = (B + D2_WARPS - 1) / D2_WARPS;
-    int grid = nblk < sms ? nblk : sms;
+    int grid = nblk < sms * 2 ? nblk : sms * 2;
     conv2_dgrad_kernel<<<grid, D2_THREADS, D2_SMEM, stream>>>(params, sc.da2, ws.a2, ws.idx2, ws.a1,
                                                              drop_scale, sc.dp1, B);
   }
@@ -629,7 +660,7 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
     int nstages = (B + W2_NS - 1) / W2_NS;
     parts_c2 = nstages < MAX_PARTS ? nstages : MAX_PARTS;
     if (parts_c2 > sms * 3) parts_c2 = sms * 3;      // 3 CTAs/SM: one stages while the others compute
-    conv2_wgrad_kernel<<<parts_c2, W2_THREADS, 0, stream>>>(sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale,
+    conv2_wgrad_kernel<<<parts_c2, W2_THREADS, W2_SMEM, stream>>>(sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale,
                                                            sc.partials, B);
   }
   prof_mark(7, stream);
