@@ -451,123 +451,137 @@ conv2_wgrad_kernel(const float* __restrict__ da2, const float* __restrict__ a2,
 }
 
 // ---------------------------------------------------------------------------
-// K_B1 conv1 weight/bias gradient.  One sample per stage; dy1 (24x24 per channel,
-// one non-zero per pool window) rebuilt dense in smem from dp1/idx1.
-// thread <-> (c, kh, chunk of output rows); 5 accumulators (kw), sliding over ox.
+// K_B1 conv1 weight/bias gradient.  Two samples per stage; dy1 (24x24 per channel, one non-zero per pool
+// window) is rebuilt dense in smem from dp1/idx1.  thread <-> (sample slot, output row oy, kh): it holds the
+// input row oy+kh in registers and sweeps all 10 channels over it -- 50 accumulators (c, kw), 18 FFMA per LDS.128.
 //   dW[c][kh][kw] = sum_b sum_oy,ox dy1[b][c][oy][ox] * x[b][oy+kh][ox+kw]
+// Raw inputs (x, dp1, idx1) of the next stage are bulk-prefetched (cp.async.bulk + mbarrier) while this one computes.
 // ---------------------------------------------------------------------------
 constexpr int W1_THREADS = 256;
-constexpr int W1_DYS = C1 * 576;
-__global__ void __launch_bounds__(W1_THREADS, 3)
+constexpr int W1_NS = 2;                                    // samples per stage
+constexpr int W1_ACTIVE = W1_NS * 120;                      // (slot, oy 24, kh 5)
+constexpr int W1_DYS = C1 * 576;                            // dense dy1 of one sample
+constexpr int W1_RAWF = W1_NS * (IMG_PIX + A1_PER);         // floats per raw buffer: x + dp1
+constexpr int W1_SMEM = (W1_NS * W1_DYS + 2 * W1_RAWF) * 4 + 2 * W1_NS * A1_PER + 64;
+__global__ void __launch_bounds__(W1_THREADS, 2)
 conv1_wgrad_kernel(const float* __restrict__ dp1, const uint8_t* __restrict__ idx1,
                    const float* __restrict__ x, float* __restrict__ partials, int B) {
-  __shared__ __align__(128) float dy_s[W1_DYS];                 // dense dy1 of the current sample; reused for reductions
-  __shared__ __align__(128) float x_s2[2][IMG_PIX];             // double-buffered raw inputs, bulk-copied a sample ahead
-  __shared__ __align__(128) float dp_s2[2][A1_PER];
-  __shared__ __align__(128) uint8_t ix_s2[2][A1_PER];
-  __shared__ __align__(8) uint64_t bar[2];
-  float* red_s = dy_s;                                           // [256*5] after the sample loop
+  extern __shared__ __align__(128) float smem[];
+  float* dy_s = smem;                                        // [W1_NS][10][24][24]; reused for the final reductions
+  float* rawf = dy_s + W1_NS * W1_DYS;                       // [2 buffers][ x: NS*784 | dp1: NS*1440 ]
+  uint64_t* bar = reinterpret_cast<uint64_t*>(rawf + 2 * W1_RAWF);   // [2]
+  uint8_t* rawi = reinterpret_cast<uint8_t*>(bar + 2);       // [2 buffers][NS*1440] idx1
   const int tid = threadIdx.x;
-  const int kh = tid % 5, chunk = (tid / 5) % 5, c = tid / 25;  // c < 10 for tid < 250
-  const bool active = tid < 250;
-  const int oy0 = chunk * 5, oy1 = min(24, oy0 + 5);
-  auto issue = [&](int b, int buf) {                             // thread 0: prefetch one sample's x, dp1, idx1
-    mbarrier_expect_tx(&bar[buf], IMG_PIX * 4 + A1_PER * 4 + A1_PER);
-    bulk_copy_g2s(x_s2[buf], x + size_t(b) * IMG_PIX, IMG_PIX * 4, &bar[buf]);
-    bulk_copy_g2s(dp_s2[buf], dp1 + size_t(b) * A1_PER, A1_PER * 4, &bar[buf]);
-    bulk_copy_g2s(ix_s2[buf], idx1 + size_t(b) * A1_PER, A1_PER, &bar[buf]);
+  const bool active = tid < W1_ACTIVE;
+  const int sl = tid / 120, r = tid % 120, kh = r % 5, oy = r / 5;
+  const int nstages = (B + W1_NS - 1) / W1_NS;
+  auto issue = [&](int st, int buf) {                        // thread 0: prefetch one stage's x, dp1, idx1
+    const int b0 = st * W1_NS;
+    const uint32_t nv = uint32_t(min(W1_NS, B - b0));
+    mbarrier_expect_tx(&bar[buf], nv * (IMG_PIX * 4 + A1_PER * 4 + A1_PER));
+    bulk_copy_g2s(rawf + buf * W1_RAWF, x + size_t(b0) * IMG_PIX, nv * IMG_PIX * 4, &bar[buf]);
+    bulk_copy_g2s(rawf + buf * W1_RAWF + W1_NS * IMG_PIX, dp1 + size_t(b0) * A1_PER, nv * A1_PER * 4, &bar[buf]);
+    bulk_copy_g2s(rawi + buf * W1_NS * A1_PER, idx1 + size_t(b0) * A1_PER, nv * A1_PER, &bar[buf]);
   };
   if (tid == 0) {
     mbarrier_init(&bar[0], 1); mbarrier_init(&bar[1], 1);
-    if (int(blockIdx.x) < B) issue(blockIdx.x, 0);
-    if (int(blockIdx.x + gridDim.x) < B) issue(blockIdx.x + gridDim.x, 1);
+    if (int(blockIdx.x) < nstages) issue(blockIdx.x, 0);
+    if (int(blockIdx.x + gridDim.x) < nstages) issue(blockIdx.x + gridDim.x, 1);
   }
   __syncthreads();
-  float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
-  float acc2[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
-  float bacc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // entries tid + 256*q of the 1440 (c,p) cells
-  uint32_t it = 0;
-  for (int b = blockIdx.x; b < B; b += gridDim.x, ++it) {
-    const int buf = it & 1;
-    mbarrier_wait(&bar[buf], (it >> 1) & 1);
-    const float* x_s = x_s2[buf];
+  float acc[C1][5];
 #pragma unroll
-    for (int q = 0; q < 6; ++q) {
-      const int e = tid + q * W1_THREADS;   // = cc*144 + p
+  for (int c = 0; c < C1; ++c)
+#pragma unroll
+    for (int k = 0; k < 5; ++k) acc[c][k] = 0.f;
+  float bacc[2] = {0.f, 0.f};                                // bias share: channels 2*kh, 2*kh+1 of this thread's row
+  int dst_off[6];                                            // where entry tid + 256*q (= cc*144 + p) lands in the dense dy1
+#pragma unroll
+  for (int q = 0; q < 6; ++q) {
+    const int e = tid + q * W1_THREADS, cc = e / 144, p = e % 144;
+    dst_off[q] = cc * 576 + (2 * (p / 12)) * 24 + 2 * (p % 12);
+  }
+  uint32_t it = 0;
+  for (int st = blockIdx.x; st < nstages; st += gridDim.x, ++it) {
+    const int buf = it & 1;
+    const int nvalid = min(W1_NS, B - st * W1_NS);
+    mbarrier_wait(&bar[buf], (it >> 1) & 1);
+    const float* x_s = rawf + buf * W1_RAWF;
+    const float* dp_s = x_s + W1_NS * IMG_PIX;
+    const uint8_t* ix_s = rawi + buf * W1_NS * A1_PER;
+#pragma unroll
+    for (int q = 0; q < 6; ++q) {                                      // entry e = tid + 256*q = cc*144 + p of each sample
+      const int e = tid + q * W1_THREADS;
       if (e < A1_PER) {
-        const float gv = dp_s2[buf][e];
-        const int id = ix_s2[buf][e];
-        const int cc = e / 144, p = e % 144, py = p / 12, px = p % 12;
-        bacc[q] += gv;
-        float* d = dy_s + cc * 576 + (2 * py) * 24 + 2 * px;
-        *reinterpret_cast<float2*>(d) = make_float2(id == 0 ? gv : 0.f, id == 1 ? gv : 0.f);
-        *reinterpret_cast<float2*>(d + 24) = make_float2(id == 2 ? gv : 0.f, id == 3 ? gv : 0.f);
+        for (int s2 = 0; s2 < nvalid; ++s2) {
+          const float gv = dp_s[s2 * A1_PER + e];
+          const int id = ix_s[s2 * A1_PER + e];
+          float* d = dy_s + s2 * W1_DYS + dst_off[q];
+          *reinterpret_cast<float2*>(d) = make_float2(id == 0 ? gv : 0.f, id == 1 ? gv : 0.f);
+          *reinterpret_cast<float2*>(d + 24) = make_float2(id == 2 ? gv : 0.f, id == 3 ? gv : 0.f);
+        }
       }
     }
     __syncthreads();
-    if (active) {
-      for (int oy = oy0; oy < oy1; ++oy) {
-        float xr[28], d[24];
-        const float* xp = x_s + (oy + kh) * IMG;
-        const float* dp = dy_s + c * 576 + oy * 24;
+    if (active && sl < nvalid) {
+      float xr[28];
+      const float* xp = x_s + sl * IMG_PIX + (oy + kh) * IMG;
 #pragma unroll
-        for (int q = 0; q < 7; ++q) {
-          float4 v = *reinterpret_cast<const float4*>(xp + 4 * q);
-          xr[4 * q] = v.x; xr[4 * q + 1] = v.y; xr[4 * q + 2] = v.z; xr[4 * q + 3] = v.w;
-        }
+      for (int q = 0; q < 7; ++q) {
+        float4 v = *reinterpret_cast<const float4*>(xp + 4 * q);
+        xr[4 * q] = v.x; xr[4 * q + 1] = v.y; xr[4 * q + 2] = v.z; xr[4 * q + 3] = v.w;
+      }
+      const float* dbase = dy_s + sl * W1_DYS + oy * 24;
+#pragma unroll
+      for (int c = 0; c < C1; ++c) {
+        float d[24];
 #pragma unroll
         for (int q = 0; q < 6; ++q) {
-          float4 v = *reinterpret_cast<const float4*>(dp + 4 * q);
+          float4 v = *reinterpret_cast<const float4*>(dbase + c * 576 + 4 * q);
           d[4 * q] = v.x; d[4 * q + 1] = v.y; d[4 * q + 2] = v.z; d[4 * q + 3] = v.w;
         }
-        // two independent accumulator sets (left / right half of the row) double the FFMA ILP
 #pragma unroll
-        for (int ox = 0; ox < 12; ++ox)
+        for (int ox = 0; ox < 24; ++ox)
 #pragma unroll
-          for (int k = 0; k < 5; ++k) {
-            acc[k] = fmaf(d[ox], xr[ox + k], acc[k]);
-            acc2[k] = fmaf(d[ox + 12], xr[ox + 12 + k], acc2[k]);
-          }
+          for (int k = 0; k < 5; ++k) acc[c][k] = fmaf(d[ox], xr[ox + k], acc[c][k]);
+        if ((c >> 1) == kh) {                                 // bias: every thread sums 2 of the 10 channels of its row
+          float sum = 0.f;
+#pragma unroll
+          for (int ox = 0; ox < 24; ++ox) sum += d[ox];
+          bacc[c & 1] += sum;
+        }
       }
     }
-    __syncthreads();                                             // dy_s and the raw buffers of `buf` are free
-    if (tid == 0 && b + 2 * int(gridDim.x) < B) issue(b + 2 * gridDim.x, buf);
+    __syncthreads();                                         // dy_s and the raw buffers of `buf` are free
+    if (tid == 0 && st + 2 * int(gridDim.x) < nstages) issue(st + 2 * gridDim.x, buf);
   }
-  // combine the 5 row-chunks in fixed order
-#pragma unroll
-  for (int k = 0; k < 5; ++k) red_s[tid * 5 + k] = acc[k] + acc2[k];
-  __syncthreads();
+  // fixed-order reduction over the 48 (slot, oy) threads of every (c, kh, kw): two passes of 5 channels
   float* part = partials + size_t(blockIdx.x) * P_ARENA;
-  if (active && chunk == 0) {
+  float* red = dy_s;                                         // [240][25]
 #pragma unroll
-    for (int k = 0; k < 5; ++k) {
-      float s = 0.f;
+  for (int half = 0; half < 2; ++half) {
+    __syncthreads();
+    if (active) {
 #pragma unroll
-      for (int ch = 0; ch < 5; ++ch) s += red_s[((c * 5 + ch) * 5 + kh) * 5 + k];
-      part[OFF_C1W + c * 25 + kh * 5 + k] = s;
+      for (int c = 0; c < 5; ++c)
+#pragma unroll
+        for (int k = 0; k < 5; ++k) red[tid * 25 + c * 5 + k] = acc[half * 5 + c][k];
+    }
+    __syncthreads();
+    if (tid < 125) {                                         // (c_local, kh, kw)
+      const int cl = tid / 25, kh2 = (tid % 25) / 5, kw = tid % 5;
+      float sum = 0.f;
+      for (int t = 0; t < W1_NS * 24; ++t) sum += red[((t / 24) * 120 + (t % 24) * 5 + kh2) * 25 + cl * 5 + kw];
+      part[OFF_C1W + (half * 5 + cl) * 25 + kh2 * 5 + kw] = sum;
     }
   }
-  // bias gradient: sum of the 144 cells of each channel (reuse dy_s as staging)
   __syncthreads();
-#pragma unroll
-  for (int q = 0; q < 6; ++q) {
-    const int e = tid + q * W1_THREADS;
-    if (e < A1_PER) dy_s[e] = bacc[q];
-  }
+  if (active) { red[tid * 2] = bacc[0]; red[tid * 2 + 1] = bacc[1]; }
   __syncthreads();
-  if (tid < C1 * 16) {           // 16 threads per channel, 9 cells each, then fixed-order combine
-    const int cc = tid >> 4, l = tid & 15;
-    float s = 0.f;
-#pragma unroll
-    for (int i = 0; i < 9; ++i) s += dy_s[cc * 144 + l * 9 + i];
-    dy_s[2048 + tid] = s;            // second stage lives past the 1440 staged cells (red_s aliases dy_s)
-  }
-  __syncthreads();
-  if (tid < C1) {
-    float s = 0.f;
-#pragma unroll
-    for (int l = 0; l < 16; ++l) s += dy_s[2048 + tid * 16 + l];
-    part[OFF_C1B + tid] = s;
+  if (tid < C1) {                                            // channel c was summed by the threads with kh == c/2
+    float sum = 0.f;
+    for (int t = 0; t < W1_NS * 24; ++t) sum += red[((t / 24) * 120 + (t % 24) * 5 + (tid >> 1)) * 2 + (tid & 1)];
+    part[OFF_C1B + tid] = sum;
   }
 }
 
@@ -636,6 +650,7 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
     DDP_CUDA(cudaFuncSetAttribute(head_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HB_SMEM));
     DDP_CUDA(cudaFuncSetAttribute(conv2_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, D2_SMEM));
     DDP_CUDA(cudaFuncSetAttribute(conv2_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, W2_SMEM));
+    DDP_CUDA(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, W1_SMEM));
     attr_done = true;
   }
   int parts_head, parts_c2, parts_c1;
@@ -665,9 +680,10 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
   }
   prof_mark(7, stream);
   {
-    parts_c1 = B < sms * 3 ? B : sms * 3;
+    const int nst1 = (B + W1_NS - 1) / W1_NS;
+    parts_c1 = nst1 < sms * 2 ? nst1 : sms * 2;
     if (parts_c1 > MAX_PARTS) parts_c1 = MAX_PARTS;
-    conv1_wgrad_kernel<<<parts_c1, W1_THREADS, 0, stream>>>(sc.dp1, ws.idx1, x, sc.partials, B);
+    conv1_wgrad_kernel<<<parts_c1, W1_THREADS, W1_SMEM, stream>>>(sc.dp1, ws.idx1, x, sc.partials, B);
   }
   prof_mark(8, stream);
   reduce_partials_kernel<<<(P_ARENA + 31) / 32, RP_WARPS * 32, 0, stream>>>(sc.partials, parts_c1, parts_c2,
