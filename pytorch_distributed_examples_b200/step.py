@@ -52,7 +52,10 @@ class TrainStep:
         self.xs = [torch.zeros(self.batch, 1, 28, 28, dtype=torch.float32, device=dev) for _ in range(slots)]
         self.ys = [torch.zeros(self.batch, dtype=torch.int64, device=dev) for _ in range(slots)]
         self.logp = torch.empty(self.batch, 10, dtype=torch.float32, device=dev)
-        self.loss = torch.zeros(1, dtype=torch.float32, device=dev)
+        self.losses = [torch.zeros(1, dtype=torch.float32, device=dev) for _ in range(slots)]   # one per slot/graph
+        self.loss = self.losses[0]
+        self._loss_host = None             # pinned host copies + events for asynchronous loss read-back
+        self._loss_events = [None] * slots
         self.ws = torch.empty(nat.workspace_bytes(self.batch), dtype=torch.uint8, device=dev)
         self.scratch = torch.zeros(nat.scratch_bytes(self.batch), dtype=torch.uint8, device=dev)
         self.copy_stream = torch.cuda.Stream(device=dev)
@@ -78,7 +81,7 @@ class TrainStep:
         m, g = self.model, self.group
         x, y = self.xs[slot], self.ys[slot]
         nat.net_forward(m._arena, x, y, None, None, m.dropout_seed, 0, True, self.ws, self.logp,
-                        out_loss=self.loss, scratch=self.scratch, offset_dev=g.step_dev)
+                        out_loss=self.losses[slot], scratch=self.scratch, offset_dev=g.step_dev)
         nat.net_backward(m._arena, x, self.logp, None, y, 1.0, True, self.ws, self.scratch, m._grad_arena)
         g.bucket = m._grad_arena
         g.adopted = True
@@ -96,7 +99,7 @@ class TrainStep:
         g = self.group
         g.ensure_state()
         g.sync_step_to_device()
-        keep = [t.clone() for t in (g.param_arena, g.step_dev, self.loss)]
+        keep = [t.clone() for t in (g.param_arena, g.step_dev, self.losses[0])]
         keep_s = [s.clone() if s is not None else None for s in (g.state1, g.state2)]
         host_steps = g.steps
         side = torch.cuda.Stream()
@@ -107,7 +110,7 @@ class TrainStep:
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         with torch.no_grad():             # undo the warm-up steps
-            g.param_arena.copy_(keep[0]); g.step_dev.copy_(keep[1]); self.loss.copy_(keep[2])
+            g.param_arena.copy_(keep[0]); g.step_dev.copy_(keep[1]); self.losses[0].copy_(keep[2])
             for s, k in zip((g.state1, g.state2), keep_s):
                 if s is not None:
                     s.copy_(k)
@@ -169,7 +172,29 @@ class TrainStep:
             ev = torch.cuda.Event()
             ev.record()
             self._consumed[slot] = ev
+        self.loss = self.losses[slot]
         return self.loss
+
+    def post_loss(self, slot: int):
+        """Queue an asynchronous device->host copy of the loss of the step just enqueued on ``slot`` (pinned
+        memory + event), so the host can read step i's loss while step i+1 is already running."""
+        if self._loss_host is None:
+            self._loss_host = torch.zeros(len(self.xs), dtype=torch.float32).pin_memory()
+            self._loss_stream = torch.cuda.Stream(device=self.xs[0].device)
+        done = torch.cuda.Event()
+        done.record()                                  # the step just enqueued on the compute stream
+        ls = self._loss_stream
+        ls.wait_event(done)
+        with torch.cuda.stream(ls):                    # off the compute stream: the next step is not queued behind the copy
+            self._loss_host[slot:slot + 1].copy_(self.losses[slot], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(ls)
+        self._loss_events[slot] = ev
+
+    def read_loss(self, slot: int) -> float:
+        """The loss posted by ``post_loss(slot)``; waits only for that step, not for later ones."""
+        self._loss_events[slot].synchronize()
+        return float(self._loss_host[slot])
 
     def __call__(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
         """One step on (data [B,1,28,28], target [B]); returns the device loss tensor (no host sync).

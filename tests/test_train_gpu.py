@@ -172,3 +172,45 @@ def test_device_loader_epoch_matches_reference_batching(native):
     loader = pkg.DeviceLoader(ds, batch_size=128, sampler=sampler)
     sizes = [d.shape[0] for d, _ in loader]
     assert len(loader) == 235 and sizes == [128] * 234 + [48]
+
+
+def test_pipelined_host_loop_equals_direct_steps(native):
+    """The end-to-end loop bench.py times (uint8 pinned host batches prefetched on the copy stream,
+    normalised on the device, loss read back one step late) gives the same losses and parameters as
+    feeding the same normalised batches directly."""
+    import pytorch_distributed_examples_b200 as pkg
+    torch.manual_seed(5)
+    sd = {k: v.detach().clone() for k, v in net_oracle.OracleNet().state_dict().items()}
+    B, steps = 128, 7
+    ds = pkg.SyntheticMNIST(length=1 << 20, seed=77)
+    host = []
+    for k in range(steps):
+        px, yy = ds.batch_u8(base_index=k * B, count=B)
+        host.append((px.cpu().pin_memory(), yy.cpu().pin_memory()))
+
+    def fresh(slots):
+        model = pkg.Net(); model.load_state_dict(sd); model = model.cuda().train(); model.dropout_seed = 3
+        topt = net_oracle.make_optimizer("sgd", model.parameters(), lr=0.01, momentum=0.9)
+        return model, pkg.TrainStep(model, topt, B, slots=slots)
+
+    model_a, step_a = fresh(1)
+    direct = []
+    for px, yy in host:
+        x = torch.empty(B, 1, 28, 28, device="cuda")
+        native.normalize_u8(px.cuda().reshape(-1), x)
+        direct.append(step_a(x, yy.cuda()).item())
+
+    model_b, step_b = fresh(2)
+    piped, prev = [], None
+    step_b.stage_u8(0, *host[0])
+    for k in range(steps):
+        if k + 1 < steps:
+            step_b.stage_u8((k + 1) % 2, *host[k + 1])
+        step_b.run_slot(k % 2)
+        step_b.post_loss(k % 2)
+        if prev is not None:
+            piped.append(step_b.read_loss(prev))
+        prev = k % 2
+    piped.append(step_b.read_loss(prev))
+    assert piped == direct
+    assert torch.equal(model_a.flat_params, model_b.flat_params)
