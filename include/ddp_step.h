@@ -216,6 +216,29 @@ int ddp_peer_allreduce_update(void* peer, float* bucket, int64_t n, int opt, flo
                               float* state1, float* state2, const ddp_hyper_t* hyper, int64_t step,
                               const int64_t* step_dev, void* stream);
 
+/* ---- two-shot allreduce for large buckets in symmetric memory (NVSwitch multicast / peer load-store) ----
+ * For bandwidth-bound buckets on ONE node (ResNet-50: 102 MB fp32 / 51 MB bf16): replaces the per-bucket
+ * allreduce + 1/N of DDP (ref: pytorch_elastic/mnist_ddp_elastic.py:58; torch: distributed/algorithms/
+ * ddp_comm_hooks/default_hooks.py:35-54) and of hvd.DistributedOptimizer (ref: horovod/mnist_horovod.py:53).
+ * The bucket lives in a SYMMETRIC buffer: the same allocation size on every rank, every rank's replica mapped
+ * into this process (replicas[q], q = rank order; replicas[rank] is the local one) and, optionally, all
+ * replicas bound to one NVSwitch multicast object mapped at `multicast` (0 = none).  The host layer gets such
+ * memory from torch.distributed._symmetric_memory (plumbing) — the library allocates nothing here.
+ * The last DDP_SYM_FLAG_BYTES of the buffer, starting at flag_offset (128-byte aligned, zeroed once before
+ * the first call and never touched by the caller again), hold the synchronisation flags.
+ * In place: elements [byte_offset, byte_offset + n*elt) of every replica are replaced by scale * sum over
+ * ranks; rank r reduces the r-th W-th of the range (in the switch with multimem.ld_reduce when `multicast`
+ * is given, else by loading the W replicas in rank order) and writes the result into every replica, so all
+ * replicas end bit-identical.  dtype 0 = f32, 1 = bf16 (fp32 accumulation); n*elt % 16 == 0.
+ * max_ctas <= 0 lets the library size the grid; unroll = 16-byte vectors in flight per thread (0 = default 4;
+ * 2, 4, 8 are tuning values).  Every rank must launch the call for the same step with
+ * the same arguments; calls on one buffer must not overlap.                                            */
+#define DDP_SYM_FLAG_BYTES 4096
+int64_t ddp_sym_flag_bytes(void);
+int ddp_sym_allreduce(const uint64_t* replicas /* host array [world] of device addresses */, uint64_t multicast,
+                      int64_t flag_offset, int world, int rank, int64_t byte_offset, int64_t n, int dtype,
+                      float scale, int max_ctas, int unroll, void* stream);
+
 /* ---- elastic state snapshot -------------------------------------------------
  * ref: horovod_mnist_elastic.py:71-72 (state.commit), :104 (TorchState);
  *      pytorch_elastic/mnist_ddp_elastic.py:95-104 (snapshot.pt).

@@ -69,6 +69,9 @@ SIGNATURES = {
     "ddp_peer_allreduce": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "ddp_peer_allreduce_update": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p, POINTER(Hyper),
                                           c_int64, c_void_p, c_void_p]),
+    "ddp_sym_flag_bytes": (c_int64, []),
+    "ddp_sym_allreduce": (c_int, [POINTER(ctypes.c_uint64), ctypes.c_uint64, c_int64, c_int, c_int, c_int64, c_int64, c_int,
+                                  c_float, c_int, c_int, c_void_p]),
     "ddp_state_snapshot": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "ddp_state_restore": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "ddp_prof_enable": (c_int, [c_int]),
@@ -285,6 +288,17 @@ class Native:
                                                 ctypes.byref(hyper), int(step), _ptr(step_dev, "step_dev", torch.int64),
                                                 _stream())
         self._check(rc, "ddp_peer_allreduce_update")
+
+    # -- two-shot allreduce in symmetric memory ------------------------------------------------------
+    def sym_flag_bytes(self) -> int:
+        return int(self.lib.ddp_sym_flag_bytes())
+
+    def sym_allreduce(self, replicas, multicast, flag_offset, world, rank, byte_offset, n, dtype, scale, max_ctas=0, unroll=0):
+        """In-place scale * sum over ranks of n elements at byte_offset of a symmetric buffer (see ddp_step.h)."""
+        arr = (ctypes.c_uint64 * world)(*[int(a) for a in replicas])
+        rc = self.lib.ddp_sym_allreduce(arr, int(multicast or 0), int(flag_offset), int(world), int(rank), int(byte_offset),
+                                        int(n), _DTYPES[dtype], float(scale), int(max_ctas), int(unroll), _stream())
+        self._check(rc, "ddp_sym_allreduce")
 
     # -- elastic snapshot ---------------------------------------------------------------------------
     def state_snapshot(self, device_arena, pinned_host):

@@ -50,6 +50,8 @@ class Communicator:
         self.handle = None
         self.peer = None          # NVLink peer-memory context (enable_peer)
         self.peer_max_elems = 0
+        self.sym = None           # symmetric buffer for the two-shot large-bucket allreduce (enable_symmetric)
+        self.sym_error = None
         self._obj_seq = 0
         nat = _native.get()
         if self.world > 1:
@@ -87,6 +89,55 @@ class Communicator:
         self.peer, self.peer_max_elems = peer, max_elems
         return True
 
+    def enable_symmetric(self, nbytes: int, multicast: bool = True) -> bool:
+        """Set up the two-shot allreduce for LARGE buckets (csrc/sym_allreduce.cu): a symmetric buffer of
+        ``nbytes`` (+ flag block) on every rank, each replica mapped on every peer and, when the NVSwitch
+        supports it and ``multicast`` is True, bound to one multicast object so the reduction runs in the switch.
+        The memory comes from torch's symmetric-memory allocator (device-memory plumbing) and therefore needs an
+        initialised torch.distributed NCCL group containing exactly this communicator's ranks, one node,
+        world <= 8.  Returns False (NCCL stays the path) when any of that is missing.  Collective."""
+        import torch.distributed as dist
+        if self.world <= 1 or self.world > 8 or not torch.cuda.is_available():
+            return False
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() != self.world \
+                or dist.get_rank() != self.rank:
+            return False
+        if self.sym is not None and self.sym["capacity"] >= nbytes:
+            return True
+        nat = _native.get()
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            cap = (int(nbytes) + 127) // 128 * 128
+            total = cap + nat.sym_flag_bytes()
+            dev = torch.device("cuda", torch.cuda.current_device())
+            buf = symm_mem.empty(total, dtype=torch.uint8, device=dev)
+            buf.zero_()
+            hdl = symm_mem.rendezvous(buf, dist.group.WORLD)
+            torch.cuda.synchronize()
+            hdl.barrier()                  # every replica is zeroed before anyone's first flag store can land
+            torch.cuda.synchronize()
+        except Exception as exc:           # no NVLink P2P / unsupported platform: stay on NCCL
+            self.sym_error = repr(exc)
+            return False
+        mc = int(hdl.multicast_ptr) if (multicast and getattr(hdl, "multicast_ptr", 0)) else 0
+        self.sym = dict(buf=buf, hdl=hdl, capacity=cap, flag_offset=cap, multicast=mc,
+                        replicas=[int(p) for p in hdl.buffer_ptrs])
+        return True
+
+    def sym_view(self, dtype: torch.dtype, n: int, byte_offset: int = 0) -> torch.Tensor:
+        """The local replica's elements [byte_offset, byte_offset + n) as a tensor: fill it with this rank's
+        gradients, call ``sym_allreduce_``, read the average back from the same tensor."""
+        esz = torch.empty(0, dtype=dtype).element_size()
+        if byte_offset % 16 or byte_offset + n * esz > self.sym["capacity"]:
+            raise RuntimeError("sym_view: range outside the symmetric buffer (or offset not 16-byte aligned)")
+        return self.sym["buf"][byte_offset:byte_offset + n * esz].view(dtype)
+
+    def sym_allreduce_(self, dtype: torch.dtype, n: int, byte_offset: int = 0, scale: float = 1.0, max_ctas: int = 0, unroll: int = 0):
+        """In place on the current stream: elements <- scale * sum over ranks (all replicas end bit-identical)."""
+        s = self.sym
+        _native.get().sym_allreduce(s["replicas"], s["multicast"], s["flag_offset"], self.world, self.rank,
+                                    byte_offset, n, dtype, scale, max_ctas, unroll)
+
     def peer_allreduce_(self, t: torch.Tensor):
         _native.get().peer_allreduce(self.peer, t)
         return t
@@ -122,6 +173,7 @@ class Communicator:
         if self.peer is not None:
             _native.get().peer_destroy(self.peer)
             self.peer = None
+        self.sym = None
         if self.handle is not None:
             _native.get().comm_destroy(self.handle)
             self.handle = None

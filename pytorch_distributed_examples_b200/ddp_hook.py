@@ -20,7 +20,12 @@ from .optim import optimizer_kind
 
 
 class HookState:
-    def __init__(self, communicator=None, device=None):
+    """``symmetric_bytes`` > 0 (collective: pass the same value on every rank) additionally sets up the two-shot
+    NVSwitch allreduce (csrc/sym_allreduce.cu) for buckets of at least ``symmetric_min_bytes`` and at most
+    ``symmetric_bytes``: the bucket is staged through a symmetric buffer, reduced in the switch, and handed
+    back averaged.  Smaller / larger buckets, and boxes without NVLink symmetric memory, use ncclAllReduce."""
+
+    def __init__(self, communicator=None, device=None, symmetric_bytes: int = 0, symmetric_min_bytes: int = 1 << 20):
         if communicator is None:
             from . import hvd
             communicator = hvd._require()
@@ -28,6 +33,31 @@ class HookState:
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.stream = torch.cuda.Stream(device=self.device, priority=-1)
         self.calls = 0
+        self.sym_calls = 0
+        self.symmetric = bool(symmetric_bytes) and communicator.enable_symmetric(int(symmetric_bytes))
+        self.symmetric_min_bytes = int(symmetric_min_bytes)
+
+
+def _average_bucket(state: HookState, buf: torch.Tensor):
+    """buf <- mean over ranks, on the current (comm) stream."""
+    comm, world = state.comm, state.comm.world
+    nbytes = buf.numel() * buf.element_size()
+    if state.symmetric and state.symmetric_min_bytes <= nbytes <= comm.sym["capacity"] \
+            and buf.dtype in (torch.float32, torch.bfloat16):
+        per16 = 16 // buf.element_size()
+        n = buf.numel()
+        n_pad = -(-n // per16) * per16
+        v = comm.sym_view(buf.dtype, n_pad)
+        v[:n].copy_(buf)
+        if n_pad != n:
+            v[n:].zero_()
+        comm.sym_allreduce_(buf.dtype, n_pad, 0, 1.0 / world)
+        buf.copy_(v[:n])
+        state.sym_calls += 1
+        return
+    comm.allreduce_sum_(buf)
+    if world > 1:
+        _native.get().scale(buf, 1.0 / world)
 
 
 def _run_on_comm_stream(state: HookState, buf: torch.Tensor, body):
@@ -46,14 +76,7 @@ def _run_on_comm_stream(state: HookState, buf: torch.Tensor, body):
 
 def allreduce_hook(state: HookState, bucket: dist.GradBucket) -> torch.futures.Future[torch.Tensor]:
     buf = bucket.buffer()
-    world = state.comm.world
-
-    def body():
-        state.comm.allreduce_sum_(buf)
-        if world > 1:
-            _native.get().scale(buf, 1.0 / world)
-
-    return _run_on_comm_stream(state, buf, body)
+    return _run_on_comm_stream(state, buf, lambda: _average_bucket(state, buf))
 
 
 class FusedUpdateHook:
@@ -64,8 +87,8 @@ class FusedUpdateHook:
     the new packing when a bucket's composition changes."""
 
     class State(HookState):
-        def __init__(self, optimizer: torch.optim.Optimizer, communicator=None, device=None):
-            super().__init__(communicator, device)
+        def __init__(self, optimizer: torch.optim.Optimizer, communicator=None, device=None, **kw):
+            super().__init__(communicator, device, **kw)
             self.optimizer = optimizer
             self.kind = optimizer_kind(optimizer)
             self.buckets = {}       # bucket index -> dict(key, arena, state1, state2, shell)
@@ -121,9 +144,14 @@ class FusedUpdateHook:
             state.iteration += 1
 
         def body():
-            state.comm.allreduce_sum_(buf)
             hyper = b["shell"].hyper(write_back=True)   # leave the averaged gradient in the bucket for DDP
+            if state.symmetric:
+                _average_bucket(state, buf)
+                inv = 1.0
+            else:
+                state.comm.allreduce_sum_(buf)
+                inv = 1.0 / world
             _native.get().fused_update(state.kind, buf, b["arena"], b["state1"], b["state2"], buf.numel(),
-                                       1.0 / world, hyper, step=step)
+                                       inv, hyper, step=step)
 
         return _run_on_comm_stream(state, buf, body)

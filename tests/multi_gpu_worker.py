@@ -55,6 +55,33 @@ def main():
         assert (a - b_).abs().max().item() <= 1e-5 * a.abs().max().item(), "peer allreduce != NCCL"
         same_on_all_ranks(b_, "peer allreduce")   # rank-ordered sum: bit-identical on every rank
     log("collectives ok (NCCL + NVLink peer memory)")
+    # 1c. two-shot allreduce in symmetric memory (NVSwitch multicast and peer load/store) == NCCL allreduce / W
+    n_max = 3_000_000
+    if c.enable_symmetric(n_max * 4 + 8192):
+        modes = ([("multicast", c.sym["multicast"])] if c.sym["multicast"] else []) + [("peer", 0)]
+        for mode, mc in modes:
+            saved = c.sym["multicast"]
+            c.sym["multicast"] = mc
+            for dtype, tol in ((torch.float32, 1e-5), (torch.bfloat16, 2e-2)):
+                for it, (n, off) in enumerate(((n_max, 0), (1000 * 4 + 8, 4096), (8, 16), (2_000_003 // 8 * 8, 1024))):
+                    torch.manual_seed(1000 * it + R)
+                    src = torch.randn(n, device="cuda").to(dtype)
+                    ref = src.float().clone()
+                    c.allreduce_sum_(ref)
+                    ref /= W
+                    v = c.sym_view(dtype, n, off)
+                    guard = c.sym_view(torch.uint8, 64, off + n * v.element_size())   # bytes right after the range
+                    guard.fill_(7)
+                    v.copy_(src)
+                    c.sym_allreduce_(dtype, n, off, scale=1.0 / W)
+                    err = (v.float() - ref).abs().max().item()
+                    assert err <= tol * ref.abs().max().item(), (mode, dtype, n, err)
+                    assert torch.all(guard == 7), "sym allreduce wrote outside its range"
+                    same_on_all_ranks(v.float(), f"sym allreduce {mode}")
+            c.sym["multicast"] = saved
+        log(f"symmetric two-shot allreduce ok (modes: {[m for m, _ in modes]})")
+    else:
+        log(f"symmetric memory unavailable on this box: {c.sym_error}")
 
     # 2. reference loop with hvd.DistributedOptimizer == real 2-process gloo DDP (golden), when W == 2
     if W == 2:
@@ -89,6 +116,10 @@ def main():
         o = torch.optim.SGD(d.parameters(), lr=0.05)
         if hook == "allreduce":
             d.register_comm_hook(pkg.HookState(), pkg.allreduce_hook)
+        elif hook == "allreduce_sym":                      # bucket staged through symmetric memory, reduced in the switch
+            st = pkg.HookState(symmetric_bytes=1 << 20, symmetric_min_bytes=0)
+            assert st.symmetric, c.sym_error
+            d.register_comm_hook(st, pkg.allreduce_hook)
         ds = pkg.SyntheticMNIST(length=4096, seed=3)
         for k in range(4):
             x, y = ds.batch(base_index=(k * W + R) * 32, count=32)
@@ -102,6 +133,10 @@ def main():
     hooked = ddp_run("allreduce")
     assert (hooked - base).abs().max().item() <= 1e-6 * base.abs().max().item(), "allreduce_hook != stock DDP"
     same_on_all_ranks(hooked, "ddp hook")
+    if c.sym is not None:
+        hooked_sym = ddp_run("allreduce_sym")
+        assert (hooked_sym - base).abs().max().item() <= 1e-6 * base.abs().max().item(), "symmetric allreduce_hook != stock DDP"
+        same_on_all_ranks(hooked_sym, "ddp hook (symmetric)")
 
     # FusedUpdateHook on the DDP script's own model family (MLP of ref: mnist_ddp_elastic.py:133-159, Adam :173);
     # (Net keeps its parameters in its own C-layout arena, so the optimizer-in-hook variant targets foreign modules)
@@ -112,7 +147,8 @@ def main():
         d = DDP(m, device_ids=[local], gradient_as_bucket_view=True)
         o = torch.optim.Adam(d.parameters(), lr=1e-3)
         if fused:
-            d.register_comm_hook(pkg.FusedUpdateHook.State(o), pkg.FusedUpdateHook.hook)
+            kw = dict(symmetric_bytes=1 << 20, symmetric_min_bytes=0) if fused == "sym" else {}
+            d.register_comm_hook(pkg.FusedUpdateHook.State(o, **kw), pkg.FusedUpdateHook.hook)
         crit = torch.nn.CrossEntropyLoss()
         ds = pkg.SyntheticMNIST(length=4096, seed=4)
         for k in range(4):
@@ -127,6 +163,10 @@ def main():
     mb, mf = mlp_run(False), mlp_run(True)
     assert (mf - mb).abs().max().item() <= 1e-5 * mb.abs().max().item() + 1e-2 * 1e-3, "FusedUpdateHook != DDP + Adam"
     same_on_all_ranks(mf, "fused hook")
+    if c.sym is not None:
+        ms = mlp_run("sym")
+        assert (ms - mb).abs().max().item() <= 1e-5 * mb.abs().max().item() + 1e-2 * 1e-3, "symmetric FusedUpdateHook != DDP + Adam"
+        same_on_all_ranks(ms, "fused hook (symmetric)")
     log("DDP comm hooks ok")
 
     # 4. TrainStep (allreduce captured in the CUDA graph) == module path

@@ -68,12 +68,34 @@ def main():
             nat.fused_update(_native.OPT_SGD, bucket, params, mom, None, layout.total, 1.0 / N, h, step=2)
         t_all = timed(whole)
         busbw = S / t_ar * 2 * (N - 1) / N / 1e9 if N > 1 else None
+        sym = {}
+        if N > 1 and c.enable_symmetric(S):
+            n_ar = -(-layout.total // 8) * 8          # whole 16-byte vectors; the pad elements are zero
+            c.sym_view(dtype, n_ar).zero_()
+            v = c.sym_view(dtype, layout.total)
+            v.copy_(bucket)
+            saved = c.sym["multicast"]
+            for mode, mc in ((("multicast", saved),) if saved else ()) + (("peer", 0),):
+                c.sym["multicast"] = mc
+                for ctas, un in ((0, 4), (0, 8), (0, 2), (64, 4), (64, 8), (96, 8)):
+                    t = timed(lambda: c.sym_allreduce_(dtype, n_ar, 0, 1.0 / N, max_ctas=ctas, unroll=un), reps=12, warm=3)
+                    sym[f"{mode}_ctas{ctas or 'all'}_unroll{un}"] = {"us": t * 1e6, "busbw_GBps": S / t * 2 * (N - 1) / N / 1e9,
+                                                         "busbw_frac_of_900": S / t * 2 * (N - 1) / N / 1e9 / 900}
+            c.sym["multicast"] = saved
+
+            def whole_sym():
+                flatten_into(v, grads, layout, table)
+                c.sym_allreduce_(dtype, n_ar, 0, 1.0)
+                nat.fused_update(_native.OPT_SGD, v, params, mom, None, layout.total, 1.0 / N, h, step=2)
+            sym["flatten+allreduce+update_us"] = timed(whole_sym) * 1e6
+        elif N > 1:
+            sym = {"unavailable": c.sym_error}
         out[name] = {"bucket_bytes": S, "flatten_us": t_flat * 1e6, "flatten_GBps": 2 * S / t_flat / 1e9,
                      "allreduce_us": t_ar * 1e6, "allreduce_algbw_GBps": S / t_ar / 1e9, "allreduce_busbw_GBps": busbw,
                      "busbw_frac_of_900": busbw / 900 if busbw else None,
                      "fused_update_us": t_upd * 1e6,
                      "fused_update_GBps": (S + 16 * layout.total) / t_upd / 1e9,
-                     "flatten+allreduce+update_us": t_all * 1e6}
+                     "flatten+allreduce+update_us": t_all * 1e6, "symmetric_two_shot": sym}
         del grads, bucket, params, mom
     # the CNN's 87 KB bucket: latency
     small = torch.zeros(21848, device="cuda")

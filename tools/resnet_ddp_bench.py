@@ -38,22 +38,30 @@ def main():
     crit = torch.nn.CrossEntropyLoss()
     out = {"n_gpus": W, "per_gpu_batch": args.batch, "model": "resnet50 (25,557,032 params)", "autocast": "bf16"}
     finals = {}
-    for variant in ("stock_ddp", "allreduce_hook", "fused_update_hook"):
+    sym_kw = dict(symmetric_bytes=40 << 20)      # DDP's fp32 buckets are <= ~30 MiB (25 MiB cap + one tensor)
+    for variant in ("stock_ddp", "allreduce_hook", "fused_update_hook", "allreduce_hook_sym", "fused_update_hook_sym"):
         torch.manual_seed(0)
         model = torchvision.models.resnet50(num_classes=1000).cuda()
         ddp = DDP(model, device_ids=[local], gradient_as_bucket_view=True)
         opt = torch.optim.SGD(ddp.parameters(), lr=0.01, momentum=0.9)
+        hook_state = None
         if variant == "allreduce_hook":
             ddp.register_comm_hook(pkg.HookState(), pkg.allreduce_hook)
         elif variant == "fused_update_hook":
             ddp.register_comm_hook(pkg.FusedUpdateHook.State(opt), pkg.FusedUpdateHook.hook)
+        elif variant == "allreduce_hook_sym":
+            hook_state = pkg.HookState(**sym_kw)
+            ddp.register_comm_hook(hook_state, pkg.allreduce_hook)
+        elif variant == "fused_update_hook_sym":
+            hook_state = pkg.FusedUpdateHook.State(opt, **sym_kw)
+            ddp.register_comm_hook(hook_state, pkg.FusedUpdateHook.hook)
 
         def step():
             opt.zero_grad(set_to_none=False)
             with torch.autocast("cuda", dtype=torch.bfloat16):
                 loss = crit(ddp(x), y)
             loss.backward()
-            if variant != "fused_update_hook":
+            if not variant.startswith("fused_update_hook"):
                 opt.step()
             return loss
 
@@ -69,10 +77,13 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         finals[variant] = torch.cat([p.detach().float().reshape(-1) for p in model.parameters()])
         out[variant] = {"ms_per_step": t.item(), "images_per_s": W * args.batch / (t.item() * 1e-3), "loss": float(loss.detach())}
+        if hook_state is not None:
+            out[variant]["symmetric_bucket_calls"] = hook_state.sym_calls
+            out[variant]["hook_calls"] = hook_state.calls
         del ddp, opt, model
         torch.cuda.empty_cache()
     ref = finals["stock_ddp"]
-    for v in ("allreduce_hook", "fused_update_hook"):
+    for v in ("allreduce_hook", "fused_update_hook", "allreduce_hook_sym", "fused_update_hook_sym"):
         out[v]["max_param_diff_vs_stock"] = float((finals[v] - ref).abs().max())
     out["param_scale"] = float(ref.abs().max())
     if R == 0:
