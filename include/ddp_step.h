@@ -230,8 +230,8 @@ int ddp_peer_allreduce_update(void* peer, float* bucket, int64_t n, int opt, flo
  * ranks; rank r reduces the r-th W-th of the range (in the switch with multimem.ld_reduce when `multicast`
  * is given, else by loading the W replicas in rank order) and writes the result into every replica, so all
  * replicas end bit-identical.  dtype 0 = f32, 1 = bf16 (fp32 accumulation); n*elt % 16 == 0.
- * max_ctas <= 0 lets the library size the grid; unroll = 16-byte vectors in flight per thread (0 = default 4;
- * 2, 4, 8 are tuning values).  Every rank must launch the call for the same step with
+ * max_ctas <= 0 lets the library size the grid; unroll = 16-byte vectors in flight per thread (0 = the
+ * library's measured default; 1, 2, 4, 8 are tuning values).  Every rank must launch the call for the same step with
  * the same arguments; calls on one buffer must not overlap.                                            */
 #define DDP_SYM_FLAG_BYTES 4096
 int64_t ddp_sym_flag_bytes(void);

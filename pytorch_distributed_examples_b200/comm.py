@@ -119,9 +119,11 @@ class Communicator:
         except Exception as exc:           # no NVLink P2P / unsupported platform: stay on NCCL
             self.sym_error = repr(exc)
             return False
-        mc = int(hdl.multicast_ptr) if (multicast and getattr(hdl, "multicast_ptr", 0)) else 0
+        # per-direction NVLink traffic: (1 + 1/W) S through the switch vs 2 (W-1)/W S with peer loads/stores,
+        # so the multicast path only pays from 4 ranks up (measured: tools/bucket_bench.py at W=2 and W=8)
+        mc = int(hdl.multicast_ptr) if (multicast and self.world >= 4 and getattr(hdl, "multicast_ptr", 0)) else 0
         self.sym = dict(buf=buf, hdl=hdl, capacity=cap, flag_offset=cap, multicast=mc,
-                        replicas=[int(p) for p in hdl.buffer_ptrs])
+                        multicast_available=int(getattr(hdl, "multicast_ptr", 0) or 0), replicas=[int(p) for p in hdl.buffer_ptrs])
         return True
 
     def sym_view(self, dtype: torch.dtype, n: int, byte_offset: int = 0) -> torch.Tensor:

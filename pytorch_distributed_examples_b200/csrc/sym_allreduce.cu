@@ -18,7 +18,7 @@
 // Protocol per launch (epoch e = previous + 1, kept on the device so graph replays stay in step):
 //   0. CTA 0 publishes "my replica holds this step's gradients" (st.release.sys flag[0][me] = e on every rank);
 //      every CTA waits until all W sources have published e.
-//   1. all CTAs: reduce + broadcast my chunk (grid-stride, 16-byte vectors, 4 in flight per thread).
+//   1. all CTAs: reduce + broadcast my chunk (grid-stride, 16-byte vectors, 2-4 in flight per thread).
 //   2. the last CTA to finish publishes flag[1][me] = e everywhere, then waits for all W sources' flag[1] == e:
 //      when the kernel ends, every chunk has landed in this replica and nobody is still reading it.
 // CTAs never wait on CTAs of the same GPU, only on other GPUs, so the grid need not be co-resident.
@@ -29,7 +29,6 @@ namespace ddp {
 
 constexpr int SYM_MAX_WORLD = 8;
 constexpr int SYM_THREADS = 512;
-constexpr int SYM_UNROLL = 4;                          // default number of 16-byte vectors in flight per thread
 constexpr int SYM_FLAG_STRIDE = 32;                       // u32 per flag (128 B)
 constexpr int SYM_EPOCH_OFF = 2 * SYM_MAX_WORLD * SYM_FLAG_STRIDE * 4;   // 2048
 constexpr int SYM_TICKET_OFF = SYM_EPOCH_OFF + 128;
@@ -167,7 +166,7 @@ sym_allreduce_kernel(SymDev sd, int64_t byte_off, int64_t nvec, float scale) {
 #pragma unroll
       for (int u = 0; u < UNROLL; u += 2) {           // 2 vectors x W replicas in flight per thread
         uint4 a[SYM_MAX_WORLD], b[SYM_MAX_WORLD];
-        const int64_t ia = i0 + u * gthreads, ib = ia + gthreads;
+        const int64_t ia = i0 + u * gthreads, ib = (u + 1 < UNROLL) ? ia + gthreads : hi;
 #pragma unroll
         for (int q = 0; q < SYM_MAX_WORLD; ++q)
           if (q < W) {
@@ -245,17 +244,19 @@ extern "C" int ddp_sym_allreduce(const uint64_t* replicas, uint64_t multicast, i
   int dev = 0, sms = 148;
   DDP_CUDA(cudaGetDevice(&dev));
   DDP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  const int un = unroll > 0 ? unroll : SYM_UNROLL;
-  DDP_REQUIRE(un == 2 || un == 4 || un == 8, "unroll must be 0 (default), 2, 4 or 8");
+  const bool mc = multicast != 0, bf = dtype == 1;
+  // Measured on 8 x B200 (tools/sym_probe.py): the switch path is fastest with FEWER requests in flight
+  // (64 CTAs x 2 vectors per thread); the load/store path wants every SM and 4 vectors per thread.
+  const int un = unroll > 0 ? unroll : (mc ? 2 : 4);
+  DDP_REQUIRE(un == 1 || un == 2 || un == 4 || un == 8, "unroll must be 0 (default), 1, 2, 4 or 8");
   int64_t want = (per + int64_t(SYM_THREADS) * un - 1) / (int64_t(SYM_THREADS) * un);
-  int cap = max_ctas > 0 ? max_ctas : sms;
+  int cap = max_ctas > 0 ? max_ctas : (mc ? 64 : sms);
   int grid = int(want < 1 ? 1 : (want > cap ? cap : want));
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  const bool mc = multicast != 0, bf = dtype == 1;
 #define SYM_LAUNCH(MC, BF, UN) sym_allreduce_kernel<MC, BF, UN><<<grid, SYM_THREADS, 0, stream>>>(sd, byte_offset, nvec, scale)
 #define SYM_PICK(UN) do { if (mc && bf) SYM_LAUNCH(true, true, UN); else if (mc) SYM_LAUNCH(true, false, UN); \
                           else if (bf) SYM_LAUNCH(false, true, UN); else SYM_LAUNCH(false, false, UN); } while (0)
-  if (un == 2) SYM_PICK(2); else if (un == 4) SYM_PICK(4); else SYM_PICK(8);
+  if (un == 1) SYM_PICK(1); else if (un == 2) SYM_PICK(2); else if (un == 4) SYM_PICK(4); else SYM_PICK(8);
 #undef SYM_PICK
 #undef SYM_LAUNCH
   DDP_CUDA(cudaGetLastError());

@@ -58,7 +58,7 @@ def main():
     # 1c. two-shot allreduce in symmetric memory (NVSwitch multicast and peer load/store) == NCCL allreduce / W
     n_max = 3_000_000
     if c.enable_symmetric(n_max * 4 + 8192):
-        modes = ([("multicast", c.sym["multicast"])] if c.sym["multicast"] else []) + [("peer", 0)]
+        modes = ([("multicast", c.sym["multicast_available"])] if c.sym["multicast_available"] else []) + [("peer", 0)]
         for mode, mc in modes:
             saved = c.sym["multicast"]
             c.sym["multicast"] = mc

@@ -75,12 +75,34 @@ def main():
             v = c.sym_view(dtype, layout.total)
             v.copy_(bucket)
             saved = c.sym["multicast"]
-            for mode, mc in ((("multicast", saved),) if saved else ()) + (("peer", 0),):
+            avail = c.sym["multicast_available"]
+            def back_to_back(fn, iters=20, reps=5):
+                """nccl-tests convention: `iters` launches back to back, one event pair around them, per-launch mean."""
+                ts = []
+                for _ in range(reps + 1):
+                    dist.barrier(); torch.cuda.synchronize()
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record()
+                    for _ in range(iters):
+                        fn()
+                    b.record(); torch.cuda.synchronize()
+                    t = torch.tensor([a.elapsed_time(b) / iters], device="cuda", dtype=torch.float64)
+                    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                    ts.append(t.item())
+                return statistics.median(ts[1:]) * 1e-3
+
+            def row(t):
+                return {"us": t * 1e6, "busbw_GBps": S / t * 2 * (N - 1) / N / 1e9, "busbw_frac_of_900": S / t * 2 * (N - 1) / N / 1e9 / 900}
+            bucket.zero_()                           # sums stay finite over the back-to-back launches
+            t = back_to_back(lambda: c.allreduce_sum_(bucket))
+            sym["nccl_back_to_back"] = row(t)
+            for mode, mc in ((("multicast", avail),) if avail else ()) + (("peer", 0),):
                 c.sym["multicast"] = mc
-                for ctas, un in ((0, 4), (0, 8), (0, 2), (64, 4), (64, 8), (96, 8)):
-                    t = timed(lambda: c.sym_allreduce_(dtype, n_ar, 0, 1.0 / N, max_ctas=ctas, unroll=un), reps=12, warm=3)
-                    sym[f"{mode}_ctas{ctas or 'all'}_unroll{un}"] = {"us": t * 1e6, "busbw_GBps": S / t * 2 * (N - 1) / N / 1e9,
-                                                         "busbw_frac_of_900": S / t * 2 * (N - 1) / N / 1e9 / 900}
+                variants = ((0, 0), (64, 1), (48, 2), (96, 2), (64, 4)) if mc else ((0, 0),)
+                for ctas, un in variants:
+                    tag = f"{mode}_ctas{ctas or 'default'}_unroll{un or 'default'}"
+                    fn = lambda: c.sym_allreduce_(dtype, n_ar, 0, 1.0 / N, max_ctas=ctas, unroll=un)
+                    sym[tag] = {"single_shot": row(timed(fn, reps=10, warm=3)), "back_to_back": row(back_to_back(fn))}
             c.sym["multicast"] = saved
 
             def whole_sym():
