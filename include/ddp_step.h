@@ -239,6 +239,42 @@ int ddp_sym_allreduce(const uint64_t* replicas /* host array [world] of device a
                       int64_t flag_offset, int world, int rank, int64_t byte_offset, int64_t n, int dtype,
                       float scale, int max_ctas, int unroll, void* stream);
 
+/* ---- the DDP script's own model: MLP + cross-entropy -----------------------------
+ * ref: pytorch_elastic/mnist_ddp_elastic.py:133-159 `Model(hidden_layers=5, features=1024)` built at :172,
+ *      nn.CrossEntropyLoss at :174, the loop body `_run_batch` at :70-75.
+ * Linear(in,F) -> ReLU -> hidden_layers x [Linear(F,F) -> ReLU] -> Linear(F,out).  The wide layers run on the
+ * tensor cores as 3xTF32 GEMMs (tcgen05 + TMA; fp32-accurate), the classifier/loss/bias sums as small kernels.
+ * Parameter arena: reference state_dict order (input_layer.weight, input_layer.bias, hidden_layers.i.weight,
+ * hidden_layers.i.bias, ..., final_layer.weight, final_layer.bias), every tensor padded to 4 floats;
+ * ddp_mlp_param_layout returns the number of tensors and fills offsets/sizes (in floats).
+ * Constraints: in_features % 4 == 0, features % 4 == 0, hidden_layers <= 5, out_features <= 16,
+ * batch % 4 == 0.  The workspace (ddp_mlp_workspace_bytes, caller-allocated, 256-byte aligned) carries the
+ * saved activations from forward to backward.
+ * forward : out_logits [batch][out] (optional), out_loss = mean cross-entropy (optional, needs target).
+ * backward: gradients of loss_scale * loss into grad_bucket (same layout as the arena).  Either `dlogits`
+ *           [batch][out] (what autograd hands to the module's backward; then target may be NULL) or, with
+ *           dlogits NULL, the fused cross-entropy gradient (softmax - onehot)/batch from `target`.         */
+typedef struct ddp_mlp_shape {
+  int in_features, features, hidden_layers, out_features;
+} ddp_mlp_shape_t;
+int64_t ddp_mlp_param_count(const ddp_mlp_shape_t* shape);
+int ddp_mlp_param_layout(const ddp_mlp_shape_t* shape, int64_t* offsets, int64_t* sizes, int max_tensors);
+int64_t ddp_mlp_workspace_bytes(const ddp_mlp_shape_t* shape, int64_t batch);
+int ddp_mlp_forward(const ddp_mlp_shape_t* shape, const float* params, const float* x, const int64_t* target,
+                    int64_t batch, void* workspace, float* out_logits, float* out_loss, void* stream);
+int ddp_mlp_backward(const ddp_mlp_shape_t* shape, const float* params, const float* dlogits, const int64_t* target,
+                     float loss_scale, int64_t batch, void* workspace, float* grad_bucket, void* stream);
+/* Building blocks of the above (no counterpart in the reference).  ddp_split_tf32: src [rows][cols] -> two
+ * tf32-exact planes hi = rna_tf32(v), lo = rna_tf32(v - hi), row-major and (when hiT/loT are given)
+ * transposed [cols][rows].  ddp_gemm_tn_3xtf32: c[M][N] (ldc) = A[M][K] . B[N][K]^T from such planes with three
+ * tensor-core products per k-step (lo*hi + hi*lo + hi*hi); the tensor-core accumulator is drained into
+ * round-to-nearest fp32 sums every 128 k values; K % 4 == 0, operands 16-byte aligned; tile_n = 0 (default)
+ * or 128 selects the N tile.                                                                             */
+int ddp_split_tf32(const float* src, int64_t rows, int64_t cols, float* hi, float* lo, float* hiT, float* loT,
+                   void* stream);
+int ddp_gemm_tn_3xtf32(const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, int M, int N, int K,
+                       float* c, int ldc, int tile_n, void* stream);
+
 /* ---- elastic state snapshot -------------------------------------------------
  * ref: horovod_mnist_elastic.py:71-72 (state.commit), :104 (TorchState);
  *      pytorch_elastic/mnist_ddp_elastic.py:95-104 (snapshot.pt).

@@ -31,7 +31,7 @@ import torch.nn.functional as F
 
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, REPO)
-from oracle import net_oracle, sampler_oracle, synth_oracle  # noqa: E402
+from oracle import mlp_oracle, net_oracle, sampler_oracle, synth_oracle  # noqa: E402
 
 REF = "/root/reference"
 OUT = os.path.join(REPO, "tests", "golden")
@@ -205,8 +205,48 @@ def gen_sampler():
     print(f"sampler: {len(cases)} cases")
 
 
+def gen_mlp(tag, hidden_layers, features, steps, batch, seed):
+    """The DDP script's own Model + CrossEntropyLoss + Adam through its own Trainer._run_batch
+    (ref: pytorch_elastic/mnist_ddp_elastic.py:70-75,133-159,172-174), imported from the reference file."""
+    ref_mod = reference_ddp_module()
+    torch.manual_seed(seed)
+    ref = ref_mod.Model(hidden_layers=hidden_layers, features=features)
+    sd0 = {k: v.detach().clone() for k, v in ref.state_dict().items()}
+    xs, ys = synth(1234, 9000 + 100 * seed, steps * batch)
+    xs = xs.view(steps, batch, 1, 28, 28); ys = ys.view(steps, batch)
+    # single forward/backward
+    crit = nn.CrossEntropyLoss()
+    logits_ref = ref(xs[0]); loss_ref = crit(logits_ref, ys[0]); loss_ref.backward()
+    grads_ref = {k: p.grad.detach().clone() for k, p in ref.named_parameters()}
+    logits_o, loss_o, grads_o = mlp_oracle.forward_backward(sd0, xs[0], ys[0], hidden_layers, features)
+    assert torch.equal(logits_o, logits_ref.detach()) and torch.equal(loss_o, loss_ref.detach())
+    for k in grads_ref:
+        assert torch.equal(grads_o[k], grads_ref[k]), k
+    # the reference Trainer's loop body, driven without its DDP / dataloader plumbing
+    opt = torch.optim.Adam(ref.parameters(), lr=1e-3)           # ref :173
+    trainer = ref_mod.Trainer.__new__(ref_mod.Trainer)
+    trainer.model, trainer.optimizer, trainer.criterion = ref, opt, crit
+    losses = []
+    for k in range(steps):
+        trainer._run_batch(xs[k], ys[k])                         # ref :70-75 (returns nothing)
+        with torch.no_grad():
+            losses.append(crit(ref(xs[k]), ys[k]).detach())      # post-step loss, for the record only
+    losses_o, sd_o = mlp_oracle.train_steps(sd0, xs, ys, hidden_layers, features, "adam", lr=1e-3)
+    for k, v in ref.state_dict().items():
+        assert torch.equal(sd_o[k], v), k
+    fx = dict(state_dict0=sd0, xs=xs, ys=ys, logits=logits_ref.detach(), loss=loss_ref.detach(), grads=grads_ref,
+              losses=losses_o[:, 0], state_dict={k: v.detach().clone() for k, v in ref.state_dict().items()},
+              hidden_layers=hidden_layers, features=features, torch_version=torch.__version__)
+    torch.save(fx, os.path.join(OUT, f"mlp_{tag}.pt"))
+    print(f"mlp_{tag}: H={hidden_layers} F={features} {steps}x{batch} loss0={loss_ref.item():.6f}")
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if "--mlp-only" in sys.argv:
+        gen_mlp("h1_f128", 1, 128, steps=3, batch=32, seed=11)       # the class defaults (ref :137)
+        gen_mlp("h2_f64", 2, 64, steps=3, batch=24, seed=12)
+        return
     NetA = reference_net_class("horovod/mnist_horovod.py")
     NetB = reference_net_class("horovod/horovod_mnist_elastic.py")
     gen_forward_backward(NetA, "b8", 8, seed=1)
@@ -220,6 +260,8 @@ def main():
     gen_train(NetA, "adadelta", "adadelta", steps=4, batch=32, seed=9, lr=1.0)               # BASELINE north_star
     gen_ddp_w2()
     gen_sampler()
+    gen_mlp("h1_f128", 1, 128, steps=3, batch=32, seed=11)       # the class defaults (ref :137)
+    gen_mlp("h2_f64", 2, 64, steps=3, batch=24, seed=12)
 
 
 if __name__ == "__main__":

@@ -5,6 +5,7 @@ horovod_mnist_elastic.py), rebuilt B200-native: hand-written sm_100a kernels beh
 
 Drop-in surface:
     Net                      the MNIST CNN nn.Module                      (net.py)
+    Model                    the DDP script's MLP, tensor-core GEMMs      (mlp.py)
     DistributedSampler       shard indices, bit-exact with torch          (sampler.py)
     hvd                      horovod.torch-compatible module              (hvd.py, elastic.py)
     allreduce_hook / HookState   DDP register_comm_hook seam              (ddp_hook.py)
@@ -13,6 +14,7 @@ plus TrainStep (the graph-captured fast path), FusedOptimizer, SyntheticMNIST / 
 """
 from . import _native  # noqa: F401
 from .net import Net
+from .mlp import Model
 from .sampler import DistributedSampler
 from .optim import FusedOptimizer, FusedUpdater
 from .data import SyntheticMNIST, DeviceLoader
@@ -22,6 +24,6 @@ from .ddp_hook import HookState, allreduce_hook, FusedUpdateHook
 from . import hvd
 from . import elastic
 
-__all__ = ["Net", "DistributedSampler", "FusedOptimizer", "FusedUpdater", "SyntheticMNIST", "DeviceLoader",
+__all__ = ["Net", "Model", "DistributedSampler", "FusedOptimizer", "FusedUpdater", "SyntheticMNIST", "DeviceLoader",
            "TrainStep", "save_snapshot", "load_snapshot", "HookState", "allreduce_hook", "FusedUpdateHook",
            "hvd", "elastic"]

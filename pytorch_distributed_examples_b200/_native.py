@@ -30,6 +30,13 @@ class Hyper(ctypes.Structure):
                 ("nesterov", c_int), ("write_back_grad", c_int), ("bump_step_dev", c_int)]
 
 
+class MLPShape(ctypes.Structure):
+    """ddp_mlp_shape_t: Linear(in,F) -> ReLU -> hidden_layers x [Linear(F,F) -> ReLU] -> Linear(F,out)."""
+    _fields_ = [("in_features", c_int), ("features", c_int), ("hidden_layers", c_int), ("out_features", c_int)]
+
+
+DDP_EINVAL = -1000
+
 # name -> (restype, argtypes); also the list of symbols the not-gpu test checks against include/ddp_step.h
 SIGNATURES = {
     "ddp_abi_version": (c_int, []),
@@ -72,6 +79,13 @@ SIGNATURES = {
     "ddp_sym_flag_bytes": (c_int64, []),
     "ddp_sym_allreduce": (c_int, [POINTER(ctypes.c_uint64), ctypes.c_uint64, c_int64, c_int, c_int, c_int64, c_int64, c_int,
                                   c_float, c_int, c_int, c_void_p]),
+    "ddp_mlp_param_count": (c_int64, [c_void_p]),
+    "ddp_mlp_param_layout": (c_int, [c_void_p, POINTER(c_int64), POINTER(c_int64), c_int]),
+    "ddp_mlp_workspace_bytes": (c_int64, [c_void_p, c_int64]),
+    "ddp_mlp_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "ddp_mlp_backward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_int64, c_void_p, c_void_p, c_void_p]),
+    "ddp_split_tf32": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "ddp_gemm_tn_3xtf32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_int, c_void_p]),
     "ddp_state_snapshot": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "ddp_state_restore": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "ddp_prof_enable": (c_int, [c_int]),
@@ -299,6 +313,63 @@ class Native:
         rc = self.lib.ddp_sym_allreduce(arr, int(multicast or 0), int(flag_offset), int(world), int(rank), int(byte_offset),
                                         int(n), _DTYPES[dtype], float(scale), int(max_ctas), int(unroll), _stream())
         self._check(rc, "ddp_sym_allreduce")
+
+    # -- MLP of the DDP script (tensor-core 3xTF32 GEMMs) ---------------------------------------------
+    def mlp_param_layout(self, shape: "MLPShape"):
+        """[(offset, size)] in floats, reference state_dict order, and the padded arena length."""
+        n = 2 * (shape.hidden_layers + 2)
+        offs, sizes = (c_int64 * n)(), (c_int64 * n)()
+        rc = self.lib.ddp_mlp_param_layout(ctypes.byref(shape), offs, sizes, n)
+        if rc != n:
+            self._check(rc if rc < 0 else DDP_EINVAL, "ddp_mlp_param_layout")
+        total = int(self.lib.ddp_mlp_param_count(ctypes.byref(shape)))
+        return [(int(offs[i]), int(sizes[i])) for i in range(n)], total
+
+    def mlp_workspace_bytes(self, shape: "MLPShape", batch: int) -> int:
+        v = int(self.lib.ddp_mlp_workspace_bytes(ctypes.byref(shape), int(batch)))
+        if v < 0:
+            self._check(DDP_EINVAL, "ddp_mlp_workspace_bytes")
+        return v
+
+    def mlp_forward(self, shape, params, x, target, workspace, out_logits=None, out_loss=None):
+        batch = x.shape[0]
+        rc = self.lib.ddp_mlp_forward(ctypes.byref(shape), _ptr(params, "params", torch.float32), _ptr(x, "x", torch.float32),
+                                      _ptr(target, "target", torch.int64), batch, _ptr(workspace, "workspace"),
+                                      _ptr(out_logits, "out_logits", torch.float32), _ptr(out_loss, "out_loss", torch.float32),
+                                      _stream())
+        self._check(rc, "ddp_mlp_forward")
+
+    def mlp_backward(self, shape, params, dlogits, target, loss_scale, batch, workspace, grad_bucket):
+        rc = self.lib.ddp_mlp_backward(ctypes.byref(shape), _ptr(params, "params", torch.float32),
+                                       _ptr(dlogits, "dlogits", torch.float32), _ptr(target, "target", torch.int64),
+                                       float(loss_scale), int(batch), _ptr(workspace, "workspace"),
+                                       _ptr(grad_bucket, "grad_bucket", torch.float32), _stream())
+        self._check(rc, "ddp_mlp_backward")
+
+    def split_tf32(self, src, transposed=False):
+        """(hi, lo[, hiT, loT]) tf32-exact planes of a 2-D fp32 tensor."""
+        rows, cols = src.shape
+        hi, lo = torch.empty_like(src), torch.empty_like(src)
+        hiT = torch.empty(cols, rows, dtype=torch.float32, device=src.device) if transposed else None
+        loT = torch.empty_like(hiT) if transposed else None
+        rc = self.lib.ddp_split_tf32(_ptr(src, "src", torch.float32), rows, cols, _ptr(hi, "hi"), _ptr(lo, "lo"),
+                                     _ptr(hiT, "hiT"), _ptr(loT, "loT"), _stream())
+        self._check(rc, "ddp_split_tf32")
+        return (hi, lo, hiT, loT) if transposed else (hi, lo)
+
+    def gemm_tn_3xtf32(self, a_hi, a_lo, b_hi, b_lo, out=None, tile_n=0):
+        """out[M][N] = A[M][K] @ B[N][K]^T from tf32 hi/lo planes."""
+        M, K = a_hi.shape
+        N = b_hi.shape[0]
+        if out is None:
+            out = torch.empty(M, N, dtype=torch.float32, device=a_hi.device)
+        if not out.is_cuda or out.dtype != torch.float32 or out.stride(1) != 1:
+            raise RuntimeError("out must be a CUDA fp32 matrix with unit column stride (a row-strided view is fine)")
+        rc = self.lib.ddp_gemm_tn_3xtf32(_ptr(a_hi, "a_hi", torch.float32), _ptr(a_lo, "a_lo", torch.float32),
+                                         _ptr(b_hi, "b_hi", torch.float32), _ptr(b_lo, "b_lo", torch.float32), M, N, K,
+                                         ctypes.c_void_p(out.data_ptr()), out.stride(0), int(tile_n), _stream())
+        self._check(rc, "ddp_gemm_tn_3xtf32")
+        return out
 
     # -- elastic snapshot ---------------------------------------------------------------------------
     def state_snapshot(self, device_arena, pinned_host):

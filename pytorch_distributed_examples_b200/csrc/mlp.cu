@@ -1,0 +1,466 @@
+// Native forward/backward of the DDP script's own model:
+//   Model(hidden_layers=H, features=F): Linear(in,F) -> ReLU -> H x [Linear(F,F) -> ReLU] -> Linear(F,out)
+//   (ref: pytorch_elastic/mnist_ddp_elastic.py:133-159; built with H=5, F=1024 at :172) + nn.CrossEntropyLoss (:174).
+// The H+1 wide layers run on the tensor cores (mlp_gemm.cu, 3xTF32); the 10-wide classifier, the loss and the
+// bias gradients are small FFMA / reduction kernels here.  Data layout in the workspace: every activation X[l] and
+// every gradient D[l] is stored as tf32 hi/lo planes, row-major [B][F] (the K-contiguous operand of the next forward /
+// data-gradient GEMM) and transposed [F][B] (the K-contiguous operand of the weight-gradient GEMM, whose K is the
+// batch).  Weights are split (and transposed for the data-gradient GEMM) at the start of every forward.
+//   forward : X[l+1] = relu(X[l] W_l^T + b_l)                      GEMM M=B N=F K=in_l   epilogue bias+ReLU+split
+//   head    : z = X[G] W_G^T + b_G ; loss = mean_b(lse(z_b) - z_b[y_b])
+//   backward: D[G] = (dz W_G) * (X[G] > 0)
+//             D[l] = (D[l+1] W_l) * (X[l] > 0)      l = G-1..1      GEMM M=B N=F K=F      epilogue mask+split
+//             dW_l = D[l+1]^T X[l]                  l = 0..G-1      ONE grouped GEMM launch, M=F N=in_l K=B
+//             db_l = sum_b D[l+1]
+// All reductions run in a fixed order (no floating-point atomics): reruns and replicas are bit-identical.
+#include <math.h>
+#include <stdlib.h>
+#include "mlp_gemm.cuh"
+
+namespace ddp {
+namespace mlp {
+
+constexpr int MAXC = 16;            // classifier width supported by the head kernels
+constexpr int HEAD_CHUNK = 128;     // samples per partial sum of the classifier weight gradient
+
+struct Shape { int in, F, H, out, G; };     // G = H + 1 tensor-core layers
+static int check_shape(const ddp_mlp_shape_t* s, Shape* o) {
+  if (!s) { set_error("mlp: shape is NULL"); return DDP_EINVAL; }
+  o->in = s->in_features; o->F = s->features; o->H = s->hidden_layers; o->out = s->out_features; o->G = s->hidden_layers + 1;
+  if (o->in < 4 || (o->in & 3) || o->F < 4 || (o->F & 3) || o->H < 0 || o->H + 1 > MAX_PROBLEMS || o->out < 1 || o->out > MAXC) {
+    set_error("mlp: need in_features %% 4 == 0, features %% 4 == 0, 0 <= hidden_layers <= %d, 1 <= out_features <= %d",
+              MAX_PROBLEMS - 1, MAXC);
+    return DDP_EINVAL;
+  }
+  return 0;
+}
+static inline int64_t pad4(int64_t v) { return (v + 3) & ~int64_t(3); }
+// parameter arena, reference state_dict order: input_layer.{weight,bias}, hidden_layers.i.{weight,bias}, final_layer.{weight,bias}
+struct ParamLayout { int64_t w[MAX_PROBLEMS + 1], b[MAX_PROBLEMS + 1], total; };
+static ParamLayout param_layout(const Shape& s) {
+  ParamLayout L{};
+  int64_t off = 0;
+  for (int l = 0; l <= s.G; ++l) {
+    const int64_t rows = l == s.G ? s.out : s.F, cols = l == 0 ? s.in : s.F;
+    L.w[l] = off; off += pad4(rows * cols);
+    L.b[l] = off; off += pad4(rows);
+  }
+  L.total = off;
+  return L;
+}
+
+struct Planes { float *hi, *lo, *hiT, *loT; };
+struct Work {
+  Planes W[MAX_PROBLEMS];       // W[l].hi/lo: [F][in_l]; hiT/loT: [in_l][F] (l >= 1 only)
+  Planes X[MAX_PROBLEMS + 1];   // X[0]: [B][in]; X[l>=1]: [B][F]
+  Planes D[MAX_PROBLEMS + 1];   // D[1..G]: [B][F]
+  float* logits;                // [B][MAXC]
+  float* dz;                    // [B][MAXC]
+  float* loss_part;             // [B]
+  float* head_part;             // [B/HEAD_CHUNK][out][F]
+};
+static int64_t carve(const Shape& s, int64_t B, char* base, Work* w) {
+  int64_t off = 0;
+  auto take = [&](int64_t floats) { float* p = base ? reinterpret_cast<float*>(base + off) : nullptr; off += align256(floats * 4); return p; };
+  auto planes = [&](int64_t floats, bool transposed) {
+    Planes p{};
+    p.hi = take(floats); p.lo = take(floats);
+    if (transposed) { p.hiT = take(floats); p.loT = take(floats); }
+    return p;
+  };
+  Work tmp{};
+  for (int l = 0; l < s.G; ++l) tmp.W[l] = planes(int64_t(s.F) * (l == 0 ? s.in : s.F), l >= 1);
+  for (int l = 0; l <= s.G; ++l) tmp.X[l] = planes(B * (l == 0 ? s.in : s.F), true);
+  for (int l = 1; l <= s.G; ++l) tmp.D[l] = planes(B * s.F, true);
+  tmp.logits = take(B * MAXC);
+  tmp.dz = take(B * MAXC);
+  tmp.loss_part = take(B);
+  tmp.head_part = take(((B + HEAD_CHUNK - 1) / HEAD_CHUNK) * int64_t(s.out) * s.F);
+  if (w) *w = tmp;
+  return off;
+}
+
+__device__ __forceinline__ float tf32_rna(float v) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+  return __uint_as_float(r);
+}
+
+// ---- src[rows][cols] -> tf32 hi/lo planes, row-major and (optionally) transposed [cols][rows] ----------------
+__global__ void __launch_bounds__(256)
+split_kernel(const float* __restrict__ src, int rows, int cols, float* __restrict__ hi, float* __restrict__ lo,
+             float* __restrict__ hiT, float* __restrict__ loT) {
+  __shared__ float th[32][33], tl[32][33];
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const int c = blockIdx.x * 32 + tx;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int rr = ty + 8 * i, r = blockIdx.y * 32 + rr;
+    float h = 0.f, l = 0.f;
+    if (r < rows && c < cols) {
+      const float v = src[size_t(r) * cols + c];
+      h = tf32_rna(v); l = tf32_rna(v - h);
+      hi[size_t(r) * cols + c] = h; lo[size_t(r) * cols + c] = l;
+    }
+    th[rr][tx] = h; tl[rr][tx] = l;
+  }
+  if (!hiT) return;
+  __syncthreads();
+  const int r = blockIdx.y * 32 + tx;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int cc = ty + 8 * i, c2 = blockIdx.x * 32 + cc;
+    if (c2 < cols && r < rows) {
+      hiT[size_t(c2) * rows + r] = th[tx][cc];
+      loT[size_t(c2) * rows + r] = tl[tx][cc];
+    }
+  }
+}
+static void launch_split(const float* src, int rows, int cols, const Planes& p, bool transposed, cudaStream_t st) {
+  dim3 grid((cols + 31) / 32, (rows + 31) / 32), block(32, 8);
+  split_kernel<<<grid, block, 0, st>>>(src, rows, cols, p.hi, p.lo, transposed ? p.hiT : nullptr, transposed ? p.loT : nullptr);
+}
+
+// ---- classifier forward: one warp per sample -----------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+head_fwd_kernel(const float* __restrict__ xh, const float* __restrict__ xl, const float* __restrict__ w, const float* __restrict__ bias,
+                const int64_t* __restrict__ target, int B, int F, int out, float* __restrict__ logits_ws,
+                float* __restrict__ out_logits, float* __restrict__ loss_part) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= B) return;
+  float acc[MAXC];
+#pragma unroll
+  for (int c = 0; c < MAXC; ++c) acc[c] = 0.f;
+  const float* h = xh + size_t(warp) * F;
+  const float* l = xl + size_t(warp) * F;
+  for (int k = lane; k < F; k += 32) {
+    const float v = h[k] + l[k];
+#pragma unroll
+    for (int c = 0; c < MAXC; ++c)
+      if (c < out) acc[c] = fmaf(v, __ldg(w + size_t(c) * F + k), acc[c]);
+  }
+#pragma unroll
+  for (int c = 0; c < MAXC; ++c)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], o);
+  float z = -INFINITY;
+#pragma unroll
+  for (int c = 0; c < MAXC; ++c)
+    if (lane == c && c < out) z = acc[c] + bias[c];
+  if (lane < MAXC) logits_ws[size_t(warp) * MAXC + lane] = lane < out ? z : 0.f;
+  if (out_logits && lane < out) out_logits[size_t(warp) * out + lane] = z;
+  if (target && loss_part) {
+    float mx = z;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float e = lane < out ? expf(z - mx) : 0.f;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) e += __shfl_xor_sync(0xffffffffu, e, o);
+    const int y = int(target[warp]);
+    const float zy = __shfl_sync(0xffffffffu, z, y);
+    if (lane == 0) loss_part[warp] = (mx + logf(e)) - zy;
+  }
+}
+// mean of loss_part in a fixed order (one block)
+__global__ void __launch_bounds__(1024)
+loss_mean_kernel(const float* __restrict__ part, int B, float* __restrict__ out) {
+  __shared__ float s[1024];
+  float a = 0.f;
+  for (int i = threadIdx.x; i < B; i += 1024) a += part[i];
+  s[threadIdx.x] = a;
+  __syncthreads();
+  for (int w = 512; w > 0; w >>= 1) {
+    if (threadIdx.x < w) s[threadIdx.x] += s[threadIdx.x + w];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) out[0] = s[0] / float(B);
+}
+
+// ---- classifier backward ---------------------------------------------------------------------------------------
+// dz = (softmax(z) - onehot(y)) * scale / B   when the loss is ours;  dz = dlogits * scale   when autograd hands it in
+__global__ void __launch_bounds__(256)
+head_dz_kernel(const float* __restrict__ logits_ws, const int64_t* __restrict__ target, const float* __restrict__ dlogits,
+               float scale, int B, int out, float* __restrict__ dz) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  float v[MAXC];
+  if (dlogits) {
+#pragma unroll
+    for (int c = 0; c < MAXC; ++c) v[c] = c < out ? dlogits[size_t(b) * out + c] * scale : 0.f;
+  } else {
+    float mx = -INFINITY;
+#pragma unroll
+    for (int c = 0; c < MAXC; ++c) { v[c] = c < out ? logits_ws[size_t(b) * MAXC + c] : -INFINITY; mx = fmaxf(mx, v[c]); }
+    float sum = 0.f;
+#pragma unroll
+    for (int c = 0; c < MAXC; ++c) { v[c] = c < out ? expf(v[c] - mx) : 0.f; sum += v[c]; }
+    const int y = int(target[b]);
+    const float inv = 1.f / sum, k = scale / float(B);
+#pragma unroll
+    for (int c = 0; c < MAXC; ++c) v[c] = c < out ? (v[c] * inv - (c == y ? 1.f : 0.f)) * k : 0.f;
+  }
+#pragma unroll
+  for (int c = 0; c < MAXC; c += 4)
+    *reinterpret_cast<float4*>(dz + size_t(b) * MAXC + c) = make_float4(v[c], v[c + 1], v[c + 2], v[c + 3]);
+}
+// D[G][b][k] = (sum_c dz[b][c] W[c][k]) * (X[G][b][k] > 0), written as hi/lo planes row-major and transposed
+__global__ void __launch_bounds__(256)
+head_dx_kernel(const float* __restrict__ dz, const float* __restrict__ w, const float* __restrict__ xh, int B, int F, int out,
+               float* __restrict__ hi, float* __restrict__ lo, float* __restrict__ hiT, float* __restrict__ loT) {
+  __shared__ float th[32][33], tl[32][33];
+  __shared__ float dzs[32][MAXC];
+  const int tx = threadIdx.x, ty = threadIdx.y, t = ty * 32 + tx;
+  const int b0 = blockIdx.y * 32, k = blockIdx.x * 32 + tx;
+  for (int i = t; i < 32 * MAXC; i += 256) {
+    const int bb = b0 + i / MAXC;
+    dzs[i / MAXC][i % MAXC] = bb < B ? dz[size_t(bb) * MAXC + i % MAXC] : 0.f;
+  }
+  __syncthreads();
+  float wv[MAXC];
+#pragma unroll
+  for (int c = 0; c < MAXC; ++c) wv[c] = (c < out && k < F) ? __ldg(w + size_t(c) * F + k) : 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int rr = ty + 8 * i, b = b0 + rr;
+    float h = 0.f, l = 0.f;
+    if (b < B && k < F) {
+      float a = 0.f;
+#pragma unroll
+      for (int c = 0; c < MAXC; ++c) a = fmaf(dzs[rr][c], wv[c], a);
+      const float v = xh[size_t(b) * F + k] > 0.f ? a : 0.f;
+      h = tf32_rna(v); l = tf32_rna(v - h);
+      hi[size_t(b) * F + k] = h; lo[size_t(b) * F + k] = l;
+    }
+    th[rr][tx] = h; tl[rr][tx] = l;
+  }
+  __syncthreads();
+  const int b = b0 + tx;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int cc = ty + 8 * i, k2 = blockIdx.x * 32 + cc;
+    if (k2 < F && b < B) { hiT[size_t(k2) * B + b] = th[tx][cc]; loT[size_t(k2) * B + b] = tl[tx][cc]; }
+  }
+}
+// partial[chunk][c][k] = sum_{b in chunk} dz[b][c] * X[G][b][k]
+__global__ void __launch_bounds__(128)
+head_dw_partial_kernel(const float* __restrict__ dz, const float* __restrict__ xh, const float* __restrict__ xl, int B, int F, int out,
+                       float* __restrict__ part) {
+  __shared__ float dzs[HEAD_CHUNK][MAXC];
+  const int k = blockIdx.x * 128 + threadIdx.x, b0 = blockIdx.y * HEAD_CHUNK;
+  for (int i = threadIdx.x; i < HEAD_CHUNK * MAXC; i += 128) {
+    const int bb = b0 + i / MAXC;
+    dzs[i / MAXC][i % MAXC] = bb < B ? dz[size_t(bb) * MAXC + i % MAXC] : 0.f;
+  }
+  __syncthreads();
+  if (k >= F) return;
+  float acc[MAXC];
+#pragma unroll
+  for (int c = 0; c < MAXC; ++c) acc[c] = 0.f;
+  const int nb = min(HEAD_CHUNK, B - b0);
+  for (int i = 0; i < nb; ++i) {
+    const size_t o = size_t(b0 + i) * F + k;
+    const float v = xh[o] + xl[o];
+#pragma unroll
+    for (int c = 0; c < MAXC; ++c) acc[c] = fmaf(dzs[i][c], v, acc[c]);
+  }
+#pragma unroll
+  for (int c = 0; c < MAXC; ++c)
+    if (c < out) part[(size_t(blockIdx.y) * out + c) * F + k] = acc[c];
+}
+__global__ void __launch_bounds__(256)
+head_dw_reduce_kernel(const float* __restrict__ part, int chunks, int n /* out*F */, float* __restrict__ dw) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= n) return;
+  float a = 0.f;
+  for (int c = 0; c < chunks; ++c) a += part[size_t(c) * n + i];
+  dw[i] = a;
+}
+// db[c] = sum_b dz[b][c]  (one block, fixed order)
+__global__ void __launch_bounds__(1024)
+head_db_kernel(const float* __restrict__ dz, int B, int out, float* __restrict__ db) {
+  __shared__ float s[1024];
+  const int c = threadIdx.x % MAXC, lane_b = threadIdx.x / MAXC;        // 64 sample lanes x 16 classes
+  float a = 0.f;
+  for (int b = lane_b; b < B; b += 1024 / MAXC) a += dz[size_t(b) * MAXC + c];
+  s[threadIdx.x] = a;
+  __syncthreads();
+  for (int w = 512; w >= MAXC; w >>= 1) {
+    if (threadIdx.x < w) s[threadIdx.x] += s[threadIdx.x + w];
+    __syncthreads();
+  }
+  if (threadIdx.x < out) db[threadIdx.x] = s[threadIdx.x];
+}
+// db[n] = sum_b (DT_hi[n][b] + DT_lo[n][b]): one warp per output feature
+__global__ void __launch_bounds__(256)
+bias_grad_kernel(const float* __restrict__ dth, const float* __restrict__ dtl, int F, int B, float* __restrict__ db) {
+  const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (n >= F) return;
+  const float* h = dth + size_t(n) * B;
+  const float* l = dtl + size_t(n) * B;
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+  int b = lane * 4;
+  for (; b + 3 < B; b += 128) {
+    const float4 x = *reinterpret_cast<const float4*>(h + b), y = *reinterpret_cast<const float4*>(l + b);
+    a0 += x.x + y.x; a1 += x.y + y.y; a2 += x.z + y.z; a3 += x.w + y.w;
+  }
+  float a = (a0 + a1) + (a2 + a3);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+  if (lane == 0) db[n] = a;
+}
+
+static int tile_width() { return 128; }   // N tile of every GEMM (the epilogue keeps one fp32 running sum per column)
+
+}  // namespace mlp
+}  // namespace ddp
+
+using namespace ddp;
+using namespace ddp::mlp;
+
+extern "C" int64_t ddp_mlp_param_count(const ddp_mlp_shape_t* shape) {
+  Shape s;
+  if (check_shape(shape, &s)) return -1;
+  return param_layout(s).total;
+}
+
+extern "C" int ddp_mlp_param_layout(const ddp_mlp_shape_t* shape, int64_t* offsets, int64_t* sizes, int max_tensors) {
+  Shape s;
+  if (int rc = check_shape(shape, &s)) return rc;
+  const int n = 2 * (s.G + 1);
+  DDP_REQUIRE(offsets && sizes && max_tensors >= n, "offsets/sizes must hold 2 * (hidden_layers + 2) entries");
+  const ParamLayout L = param_layout(s);
+  for (int l = 0; l <= s.G; ++l) {
+    const int64_t rows = l == s.G ? s.out : s.F, cols = l == 0 ? s.in : s.F;
+    offsets[2 * l] = L.w[l]; sizes[2 * l] = rows * cols;
+    offsets[2 * l + 1] = L.b[l]; sizes[2 * l + 1] = rows;
+  }
+  return n;
+}
+
+extern "C" int64_t ddp_mlp_workspace_bytes(const ddp_mlp_shape_t* shape, int64_t batch) {
+  Shape s;
+  if (check_shape(shape, &s)) return -1;
+  if (batch < 4 || (batch & 3)) { set_error("ddp_mlp_workspace_bytes: batch must be a positive multiple of 4"); return -1; }
+  return carve(s, batch, nullptr, nullptr);
+}
+
+extern "C" int ddp_mlp_forward(const ddp_mlp_shape_t* shape, const float* params, const float* x, const int64_t* target,
+                               int64_t batch, void* workspace, float* out_logits, float* out_loss, void* stream_) {
+  Shape s;
+  if (int rc = check_shape(shape, &s)) return rc;
+  DDP_REQUIRE(params && x && workspace, "params, x and workspace are required");
+  DDP_REQUIRE(batch >= 4 && (batch & 3) == 0 && batch <= (int64_t(1) << 20), "batch must be a multiple of 4 (<= 2^20)");
+  DDP_REQUIRE(aligned16(params) && aligned16(x) && (reinterpret_cast<uintptr_t>(workspace) & 255) == 0,
+              "params/x must be 16-byte aligned, workspace 256-byte aligned");
+  DDP_REQUIRE(!out_loss || target, "out_loss needs target");
+  cudaStream_t st = static_cast<cudaStream_t>(stream_);
+  const int B = int(batch);
+  Work w;
+  carve(s, batch, static_cast<char*>(workspace), &w);
+  const ParamLayout L = param_layout(s);
+  // operands: weights and the input batch as tf32 hi/lo planes
+  for (int l = 0; l < s.G; ++l) launch_split(params + L.w[l], s.F, l == 0 ? s.in : s.F, w.W[l], l >= 1, st);
+  launch_split(x, B, s.in, w.X[0], true, st);
+  DDP_CUDA(cudaGetLastError());
+  const int bn = tile_width();
+  for (int l = 0; l < s.G; ++l) {
+    GemmBatch gb{};
+    GemmProblem& p = gb.p[0];
+    const int K = l == 0 ? s.in : s.F;
+    if (int rc = make_operand_maps(&p, w.X[l].hi, w.X[l].lo, w.W[l].hi, w.W[l].lo, B, s.F, K, bn)) return rc;
+    p.bias = params + L.b[l];
+    p.out_hi = w.X[l + 1].hi; p.out_lo = w.X[l + 1].lo; p.outT_hi = w.X[l + 1].hiT; p.outT_lo = w.X[l + 1].loT;
+    p.ldo = s.F; p.ldt = B;
+    gb.count = 1; gb.tile_start[0] = 0; gb.tile_start[1] = p.mtiles * p.ntiles;
+    if (int rc = launch_gemm(gb, EPI_BIAS_RELU_SPLIT, bn, st)) return rc;
+  }
+  const int wpb = 8;
+  head_fwd_kernel<<<(B + wpb - 1) / wpb, wpb * 32, 0, st>>>(w.X[s.G].hi, w.X[s.G].lo, params + L.w[s.G], params + L.b[s.G], target, B, s.F,
+                                                         s.out, w.logits, out_logits, out_loss ? w.loss_part : nullptr);
+  if (out_loss) loss_mean_kernel<<<1, 1024, 0, st>>>(w.loss_part, B, out_loss);
+  DDP_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ddp_mlp_backward(const ddp_mlp_shape_t* shape, const float* params, const float* dlogits, const int64_t* target,
+                                float loss_scale, int64_t batch, void* workspace, float* grad_bucket, void* stream_) {
+  Shape s;
+  if (int rc = check_shape(shape, &s)) return rc;
+  DDP_REQUIRE(params && workspace && grad_bucket, "params, workspace and grad_bucket are required");
+  DDP_REQUIRE(dlogits || target, "either dlogits (from autograd) or target (fused cross-entropy) is required");
+  DDP_REQUIRE(batch >= 4 && (batch & 3) == 0 && batch <= (int64_t(1) << 20), "batch must be a multiple of 4 (<= 2^20)");
+  DDP_REQUIRE(aligned16(params) && aligned16(grad_bucket) && (reinterpret_cast<uintptr_t>(workspace) & 255) == 0,
+              "params/grad_bucket must be 16-byte aligned, workspace 256-byte aligned");
+  cudaStream_t st = static_cast<cudaStream_t>(stream_);
+  const int B = int(batch);
+  Work w;
+  carve(s, batch, static_cast<char*>(workspace), &w);
+  const ParamLayout L = param_layout(s);
+  const int G = s.G;
+  // classifier
+  head_dz_kernel<<<(B + 255) / 256, 256, 0, st>>>(w.logits, target, dlogits, loss_scale, B, s.out, w.dz);
+  head_dx_kernel<<<dim3((s.F + 31) / 32, (B + 31) / 32), dim3(32, 8), 0, st>>>(w.dz, params + L.w[G], w.X[G].hi, B, s.F, s.out,
+                                                                              w.D[G].hi, w.D[G].lo, w.D[G].hiT, w.D[G].loT);
+  const int chunks = (B + HEAD_CHUNK - 1) / HEAD_CHUNK;
+  head_dw_partial_kernel<<<dim3((s.F + 127) / 128, chunks), 128, 0, st>>>(w.dz, w.X[G].hi, w.X[G].lo, B, s.F, s.out, w.head_part);
+  head_dw_reduce_kernel<<<(s.out * s.F + 255) / 256, 256, 0, st>>>(w.head_part, chunks, s.out * s.F, grad_bucket + L.w[G]);
+  head_db_kernel<<<1, 1024, 0, st>>>(w.dz, B, s.out, grad_bucket + L.b[G]);
+  DDP_CUDA(cudaGetLastError());
+  // data gradients through the wide layers
+  const int bn = tile_width();
+  for (int l = G - 1; l >= 1; --l) {
+    GemmBatch gb{};
+    GemmProblem& p = gb.p[0];
+    if (int rc = make_operand_maps(&p, w.D[l + 1].hi, w.D[l + 1].lo, w.W[l].hiT, w.W[l].loT, B, s.F, s.F, bn)) return rc;
+    p.mask = w.X[l].hi;
+    p.out_hi = w.D[l].hi; p.out_lo = w.D[l].lo; p.outT_hi = w.D[l].hiT; p.outT_lo = w.D[l].loT;
+    p.ldo = s.F; p.ldt = B;
+    gb.count = 1; gb.tile_start[0] = 0; gb.tile_start[1] = p.mtiles * p.ntiles;
+    if (int rc = launch_gemm(gb, EPI_MASK_SPLIT, bn, st)) return rc;
+  }
+  // all weight gradients in one grouped launch; bias gradients beside it
+  {
+    GemmBatch gb{};
+    gb.count = G;
+    gb.tile_start[0] = 0;
+    for (int l = 0; l < G; ++l) {
+      GemmProblem& p = gb.p[l];
+      const int K_l = l == 0 ? s.in : s.F;
+      if (int rc = make_operand_maps(&p, w.D[l + 1].hiT, w.D[l + 1].loT, w.X[l].hiT, w.X[l].loT, s.F, K_l, B, 128)) return rc;
+      p.out = grad_bucket + L.w[l];
+      p.ldo = K_l;
+      gb.tile_start[l + 1] = gb.tile_start[l] + p.mtiles * p.ntiles;
+    }
+    if (int rc = launch_gemm(gb, EPI_PLAIN, 128, st)) return rc;
+  }
+  for (int l = 0; l < G; ++l)
+    bias_grad_kernel<<<(s.F + 7) / 8, 256, 0, st>>>(w.D[l + 1].hiT, w.D[l + 1].loT, s.F, B, grad_bucket + L.b[l]);
+  DDP_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ---- building blocks, exported for tests and reuse ----------------------------------------------------------------
+extern "C" int ddp_split_tf32(const float* src, int64_t rows, int64_t cols, float* hi, float* lo, float* hiT, float* loT,
+                              void* stream) {
+  DDP_REQUIRE(src && hi && lo, "src, hi and lo are required");
+  DDP_REQUIRE((hiT == nullptr) == (loT == nullptr), "give both transposed planes or neither");
+  DDP_REQUIRE(rows >= 1 && cols >= 1 && rows <= (1 << 24) && cols <= (1 << 24), "rows/cols out of range");
+  Planes p{hi, lo, hiT, loT};
+  launch_split(src, int(rows), int(cols), p, hiT != nullptr, static_cast<cudaStream_t>(stream));
+  DDP_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ddp_gemm_tn_3xtf32(const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, int M, int N, int K,
+                                  float* c, int ldc, int tile_n, void* stream) {
+  DDP_REQUIRE(a_hi && a_lo && b_hi && b_lo && c, "null operand");
+  DDP_REQUIRE(M >= 1 && N >= 1 && K >= 4 && (K & 3) == 0 && ldc >= N, "need K %% 4 == 0 and ldc >= N");
+  DDP_REQUIRE(tile_n == 0 || tile_n == 128, "tile_n must be 0 (default) or 128");
+  const int bn = tile_n ? tile_n : 128;
+  GemmBatch gb{};
+  GemmProblem& p = gb.p[0];
+  if (int rc = make_operand_maps(&p, a_hi, a_lo, b_hi, b_lo, M, N, K, bn)) return rc;
+  p.out = c; p.ldo = ldc;
+  gb.count = 1; gb.tile_start[0] = 0; gb.tile_start[1] = p.mtiles * p.ntiles;
+  return launch_gemm(gb, EPI_PLAIN, bn, static_cast<cudaStream_t>(stream));
+}

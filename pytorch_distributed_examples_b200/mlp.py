@@ -1,0 +1,144 @@
+"""``Model`` — drop-in for the DDP script's own network (ref: pytorch_elastic/mnist_ddp_elastic.py:133-159; the
+script builds ``Model(hidden_layers=5, features=1024)`` at :172 and trains it with Adam + nn.CrossEntropyLoss).
+
+Same constructor, same attribute names (input_layer, hidden_layers, final_layer, relu) and therefore the same
+``state_dict()`` keys and default initialisation.  ``model(x)`` returns the [B,10] logits wired into autograd,
+so the reference loop body (ref :70-75)
+    output = model(source); loss = criterion(output, targets); loss.backward(); optimizer.step()
+runs unchanged, under stock DDP as well (the gradients appear in ``p.grad`` like any module's).
+On a CUDA device the parameters are views of one flat fp32 arena (ddp_mlp_param_layout) and the backward
+kernels write the gradients into a flat bucket of the same layout.  The wide layers are 3xTF32 tensor-core GEMMs
+(csrc/mlp_gemm.cu), fp32-accurate.  The batch must be a multiple of 4 (the weight-gradient GEMM's K is the
+batch and TMA rows are 16-byte aligned).  No CPU implementation: calling it with CPU tensors raises.
+``loss_and_grads`` is the fused path: cross-entropy and its gradient computed by the head kernels.
+"""
+import torch
+import torch.nn as nn
+
+from . import _native
+
+
+class _MLPFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, net, *params):
+        nat = _native.get()
+        batch = x.shape[0]
+        logits = torch.empty(batch, net._shape.out_features, dtype=torch.float32, device=x.device)
+        ws = net._get_workspace(batch)
+        nat.mlp_forward(net._shape, net._arena, x, None, ws, out_logits=logits)
+        ctx.net, ctx.batch = net, batch
+        ctx.ws_version = net._ws_version = net._ws_version + 1
+        return logits
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        nat = _native.get()
+        net = ctx.net
+        if ctx.ws_version != net._ws_version:
+            raise RuntimeError("Model keeps ONE activation workspace: backward must follow its own forward "
+                               "(two forwards before a backward are not supported)")
+        fresh = all(p.grad is None for p in net._param_list)
+        bucket = net._grad_arena if fresh else torch.empty_like(net._grad_arena)
+        nat.mlp_backward(net._shape, net._arena, dlogits.contiguous(), None, 1.0, ctx.batch, net._workspace, bucket)
+        grads = [bucket[o:o + n].view(p.shape) for p, (o, n) in zip(net._param_list, net._layout)]
+        return (None, None, *grads)
+
+
+class Model(nn.Module):
+    def __init__(self, hidden_layers=1, features=128):
+        super().__init__()
+        self.input_layer = nn.Linear(784, features)
+        self.hidden_layers = nn.ModuleList([nn.Linear(features, features) for _ in range(hidden_layers)])
+        self.final_layer = nn.Linear(features, out_features=10)
+        self.relu = nn.ReLU()
+        self._shape = _native.MLPShape(784, features, hidden_layers, 10)
+        self._arena = self._grad_arena = self._workspace = None
+        self._workspace_batch = 0
+        self._ws_version = 0
+        self._layout = None
+
+    @property
+    def _param_list(self):
+        out = [self.input_layer.weight, self.input_layer.bias]
+        for layer in self.hidden_layers:
+            out += [layer.weight, layer.bias]
+        return out + [self.final_layer.weight, self.final_layer.bias]
+
+    def _apply(self, fn, *args, **kwargs):
+        out = super()._apply(fn, *args, **kwargs)
+        self._flatten()
+        return out
+
+    def _flatten(self):
+        dev = self.input_layer.weight.device
+        if dev.type != "cuda":
+            self._arena = self._grad_arena = self._workspace = None
+            return
+        nat = _native.get()
+        self._layout, total = nat.mlp_param_layout(self._shape)
+        arena = torch.zeros(total, dtype=torch.float32, device=dev)
+        with torch.no_grad():
+            for p, (o, n) in zip(self._param_list, self._layout):
+                arena[o:o + n].copy_(p.detach().reshape(-1).to(torch.float32))
+                p.data = arena[o:o + n].view(p.shape)
+                p.grad = None
+        self._arena = arena
+        self._grad_arena = torch.zeros_like(arena)
+        self._workspace, self._workspace_batch = None, 0
+
+    def _check_arena(self):
+        if self._arena is None:
+            raise RuntimeError("Model runs only on a CUDA device (sm_100a kernels, no CPU fallback): call .cuda() first")
+        base = self._arena.data_ptr()
+        for p, (o, _) in zip(self._param_list, self._layout):
+            if p.data_ptr() != base + 4 * o:
+                self._flatten()
+                break
+
+    def _get_workspace(self, batch: int):
+        if batch % 4:
+            raise RuntimeError(f"Model needs a batch that is a multiple of 4, got {batch}")
+        if self._workspace is None or self._workspace_batch != batch:
+            nat = _native.get()
+            self._workspace = torch.empty(nat.mlp_workspace_bytes(self._shape, batch), dtype=torch.uint8,
+                                          device=self._arena.device)
+            self._workspace_batch = batch
+        return self._workspace
+
+    @property
+    def flat_params(self) -> torch.Tensor:
+        self._check_arena()
+        return self._arena
+
+    @property
+    def flat_grads(self) -> torch.Tensor:
+        self._check_arena()
+        return self._grad_arena
+
+    def forward(self, x):
+        self._check_arena()
+        if not x.is_cuda:
+            raise RuntimeError("Model.forward needs a CUDA tensor (no CPU fallback)")
+        x = x.reshape(x.size(0), -1).to(torch.float32).contiguous()          # ref :151 x.view(x.size(0), -1)
+        if not torch.is_grad_enabled():
+            logits = torch.empty(x.shape[0], 10, dtype=torch.float32, device=x.device)
+            _native.get().mlp_forward(self._shape, self._arena, x, None, self._get_workspace(x.shape[0]), out_logits=logits)
+            self._ws_version += 1
+            return logits
+        return _MLPFunction.apply(x, self, *self._param_list)
+
+    def loss_and_grads(self, x, target, loss_scale: float = 1.0):
+        """Fused step body without autograd: mean cross-entropy of ``model(x)`` vs ``target`` (device scalar) and
+        its gradients written into ``flat_grads`` (= every ``p.grad``).  Same arithmetic as
+        ``criterion(model(x), target).backward()`` (ref :72-74)."""
+        self._check_arena()
+        nat = _native.get()
+        x = x.reshape(x.size(0), -1).to(torch.float32).contiguous()
+        ws = self._get_workspace(x.shape[0])
+        loss = torch.empty(1, dtype=torch.float32, device=x.device)
+        nat.mlp_forward(self._shape, self._arena, x, target, ws, out_loss=loss)
+        nat.mlp_backward(self._shape, self._arena, None, target, loss_scale, x.shape[0], ws, self._grad_arena)
+        self._ws_version += 1
+        for p, (o, n) in zip(self._param_list, self._layout):
+            p.grad = self._grad_arena[o:o + n].view(p.shape)
+        return loss
