@@ -266,14 +266,16 @@ int ddp_mlp_backward(const ddp_mlp_shape_t* shape, const float* params, const fl
                      float loss_scale, int64_t batch, void* workspace, float* grad_bucket, void* stream);
 /* Building blocks of the above (no counterpart in the reference).  ddp_split_tf32: src [rows][cols] -> two
  * tf32-exact planes hi = rna_tf32(v), lo = rna_tf32(v - hi), row-major and (when hiT/loT are given)
- * transposed [cols][rows].  ddp_gemm_tn_3xtf32: c[M][N] (ldc) = A[M][K] . B[N][K]^T from such planes with three
+ * transposed [cols][rows].  ddp_gemm_3xtf32: c[M][N] (row pitch ldc) = A . B^T from such planes with three
  * tensor-core products per k-step (lo*hi + hi*lo + hi*hi); the tensor-core accumulator is drained into
- * round-to-nearest fp32 sums every 128 k values; K % 4 == 0, operands 16-byte aligned; tile_n = 0 (default)
- * or 128 selects the N tile.                                                                             */
+ * round-to-nearest fp32 sums every 128 k values.  Operand layouts: a_mn_major = 0: A is [M][K] (K contiguous),
+ * 1: A is [K][M]; b_mn_major = 0: B is [N][K], 1: B is [K][N].  The contiguous dimension of each operand and
+ * ldc must be multiples of 4, all bases 16-byte aligned.  With an MN-major operand whose row count is not a
+ * multiple of 32 the kernel may read (never use) up to 124 bytes past the end of that operand's last row.   */
 int ddp_split_tf32(const float* src, int64_t rows, int64_t cols, float* hi, float* lo, float* hiT, float* loT,
                    void* stream);
-int ddp_gemm_tn_3xtf32(const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, int M, int N, int K,
-                       float* c, int ldc, int tile_n, void* stream);
+int ddp_gemm_3xtf32(const float* a_hi, const float* a_lo, int a_mn_major, const float* b_hi, const float* b_lo,
+                    int b_mn_major, int M, int N, int K, float* c, int ldc, void* stream);
 
 /* ---- elastic state snapshot -------------------------------------------------
  * ref: horovod_mnist_elastic.py:71-72 (state.commit), :104 (TorchState);

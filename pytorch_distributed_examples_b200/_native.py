@@ -85,7 +85,7 @@ SIGNATURES = {
     "ddp_mlp_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),
     "ddp_mlp_backward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_int64, c_void_p, c_void_p, c_void_p]),
     "ddp_split_tf32": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
-    "ddp_gemm_tn_3xtf32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_int, c_void_p]),
+    "ddp_gemm_3xtf32": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int, c_void_p]),
     "ddp_state_snapshot": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "ddp_state_restore": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "ddp_prof_enable": (c_int, [c_int]),
@@ -357,18 +357,21 @@ class Native:
         self._check(rc, "ddp_split_tf32")
         return (hi, lo, hiT, loT) if transposed else (hi, lo)
 
-    def gemm_tn_3xtf32(self, a_hi, a_lo, b_hi, b_lo, out=None, tile_n=0):
-        """out[M][N] = A[M][K] @ B[N][K]^T from tf32 hi/lo planes."""
-        M, K = a_hi.shape
-        N = b_hi.shape[0]
+    def gemm_3xtf32(self, a_hi, a_lo, b_hi, b_lo, out=None, a_mn_major=False, b_mn_major=False):
+        """out[M][N] = A @ B^T from tf32 hi/lo planes.  A is [M][K] (or [K][M] with a_mn_major), B is [N][K]
+        (or [K][N] with b_mn_major)."""
+        (K, M) = a_hi.shape if a_mn_major else a_hi.shape[::-1]
+        N = b_hi.shape[1] if b_mn_major else b_hi.shape[0]
+        if (b_hi.shape[0] if b_mn_major else b_hi.shape[1]) != K:
+            raise RuntimeError("gemm_3xtf32: K of A and B differ")
         if out is None:
             out = torch.empty(M, N, dtype=torch.float32, device=a_hi.device)
         if not out.is_cuda or out.dtype != torch.float32 or out.stride(1) != 1:
             raise RuntimeError("out must be a CUDA fp32 matrix with unit column stride (a row-strided view is fine)")
-        rc = self.lib.ddp_gemm_tn_3xtf32(_ptr(a_hi, "a_hi", torch.float32), _ptr(a_lo, "a_lo", torch.float32),
-                                         _ptr(b_hi, "b_hi", torch.float32), _ptr(b_lo, "b_lo", torch.float32), M, N, K,
-                                         ctypes.c_void_p(out.data_ptr()), out.stride(0), int(tile_n), _stream())
-        self._check(rc, "ddp_gemm_tn_3xtf32")
+        rc = self.lib.ddp_gemm_3xtf32(_ptr(a_hi, "a_hi", torch.float32), _ptr(a_lo, "a_lo", torch.float32), int(a_mn_major),
+                                      _ptr(b_hi, "b_hi", torch.float32), _ptr(b_lo, "b_lo", torch.float32), int(b_mn_major),
+                                      M, N, K, ctypes.c_void_p(out.data_ptr()), out.stride(0), _stream())
+        self._check(rc, "ddp_gemm_3xtf32")
         return out
 
     # -- elastic snapshot ---------------------------------------------------------------------------

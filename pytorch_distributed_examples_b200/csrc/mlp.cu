@@ -2,10 +2,10 @@
 //   Model(hidden_layers=H, features=F): Linear(in,F) -> ReLU -> H x [Linear(F,F) -> ReLU] -> Linear(F,out)
 //   (ref: pytorch_elastic/mnist_ddp_elastic.py:133-159; built with H=5, F=1024 at :172) + nn.CrossEntropyLoss (:174).
 // The H+1 wide layers run on the tensor cores (mlp_gemm.cu, 3xTF32); the 10-wide classifier, the loss and the
-// bias gradients are small FFMA / reduction kernels here.  Data layout in the workspace: every activation X[l] and
-// every gradient D[l] is stored as tf32 hi/lo planes, row-major [B][F] (the K-contiguous operand of the next forward /
-// data-gradient GEMM) and transposed [F][B] (the K-contiguous operand of the weight-gradient GEMM, whose K is the
-// batch).  Weights are split (and transposed for the data-gradient GEMM) at the start of every forward.
+// bias gradients are small FFMA / reduction kernels here.  Data layout in the workspace: every activation X[l], every
+// gradient D[l] and every weight matrix is ONE pair of row-major tf32 hi/lo planes; the GEMM reads them K-major or
+// MN-major as each product needs, so nothing is ever transposed.  The ReLU masks travel as one bit per element.
+// Weights are split into their planes at the start of every forward.
 //   forward : X[l+1] = relu(X[l] W_l^T + b_l)                      GEMM M=B N=F K=in_l   epilogue bias+ReLU+split
 //   head    : z = X[G] W_G^T + b_G ; loss = mean_b(lse(z_b) - z_b[y_b])
 //   backward: D[G] = (dz W_G) * (X[G] > 0)
@@ -51,9 +51,10 @@ static ParamLayout param_layout(const Shape& s) {
 
 struct Planes { float *hi, *lo, *hiT, *loT; };
 struct Work {
-  Planes W[MAX_PROBLEMS];       // W[l].hi/lo: [F][in_l]; hiT/loT: [in_l][F] (l >= 1 only)
+  Planes W[MAX_PROBLEMS];       // W[l].hi/lo: [F][in_l]
   Planes X[MAX_PROBLEMS + 1];   // X[0]: [B][in]; X[l>=1]: [B][F]
   Planes D[MAX_PROBLEMS + 1];   // D[1..G]: [B][F]
+  uint32_t* bits[MAX_PROBLEMS + 1];   // bits[l], l = 1..G: ReLU mask of X[l], [B][ceil(F/32)]
   float* logits;                // [B][MAXC]
   float* dz;                    // [B][MAXC]
   float* loss_part;             // [B]
@@ -69,9 +70,10 @@ static int64_t carve(const Shape& s, int64_t B, char* base, Work* w) {
     return p;
   };
   Work tmp{};
-  for (int l = 0; l < s.G; ++l) tmp.W[l] = planes(int64_t(s.F) * (l == 0 ? s.in : s.F), l >= 1);
-  for (int l = 0; l <= s.G; ++l) tmp.X[l] = planes(B * (l == 0 ? s.in : s.F), true);
-  for (int l = 1; l <= s.G; ++l) tmp.D[l] = planes(B * s.F, true);
+  for (int l = 0; l < s.G; ++l) tmp.W[l] = planes(int64_t(s.F) * (l == 0 ? s.in : s.F), false);
+  for (int l = 0; l <= s.G; ++l) tmp.X[l] = planes(B * (l == 0 ? s.in : s.F), false);
+  for (int l = 1; l <= s.G; ++l) tmp.D[l] = planes(B * s.F, false);
+  for (int l = 1; l <= s.G; ++l) tmp.bits[l] = reinterpret_cast<uint32_t*>(take(B * ((s.F + 31) / 32)));
   tmp.logits = take(B * MAXC);
   tmp.dz = take(B * MAXC);
   tmp.loss_part = take(B);
@@ -121,44 +123,60 @@ static void launch_split(const float* src, int rows, int cols, const Planes& p, 
   split_kernel<<<grid, block, 0, st>>>(src, rows, cols, p.hi, p.lo, transposed ? p.hiT : nullptr, transposed ? p.loT : nullptr);
 }
 
-// ---- classifier forward: one warp per sample -----------------------------------------------------------------
+// ---- classifier forward: one warp per HEAD_SPW samples (the classifier rows are loaded once for all of them) -----
+constexpr int HEAD_SPW = 4;
 __global__ void __launch_bounds__(256)
 head_fwd_kernel(const float* __restrict__ xh, const float* __restrict__ xl, const float* __restrict__ w, const float* __restrict__ bias,
                 const int64_t* __restrict__ target, int B, int F, int out, float* __restrict__ logits_ws,
                 float* __restrict__ out_logits, float* __restrict__ loss_part) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (warp >= B) return;
-  float acc[MAXC];
+  const int b0 = warp * HEAD_SPW;
+  if (b0 >= B) return;
+  float acc[HEAD_SPW][MAXC];
 #pragma unroll
-  for (int c = 0; c < MAXC; ++c) acc[c] = 0.f;
-  const float* h = xh + size_t(warp) * F;
-  const float* l = xl + size_t(warp) * F;
+  for (int s = 0; s < HEAD_SPW; ++s)
+#pragma unroll
+    for (int c = 0; c < MAXC; ++c) acc[s][c] = 0.f;
   for (int k = lane; k < F; k += 32) {
-    const float v = h[k] + l[k];
+    float v[HEAD_SPW];
+#pragma unroll
+    for (int s = 0; s < HEAD_SPW; ++s) {
+      const size_t o = size_t(min(b0 + s, B - 1)) * F + k;
+      v[s] = xh[o] + xl[o];
+    }
 #pragma unroll
     for (int c = 0; c < MAXC; ++c)
-      if (c < out) acc[c] = fmaf(v, __ldg(w + size_t(c) * F + k), acc[c]);
+      if (c < out) {
+        const float wv = __ldg(w + size_t(c) * F + k);
+#pragma unroll
+        for (int s = 0; s < HEAD_SPW; ++s) acc[s][c] = fmaf(v[s], wv, acc[s][c]);
+      }
   }
 #pragma unroll
-  for (int c = 0; c < MAXC; ++c)
+  for (int s = 0; s < HEAD_SPW; ++s) {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], o);
-  float z = -INFINITY;
+    for (int c = 0; c < MAXC; ++c)
 #pragma unroll
-  for (int c = 0; c < MAXC; ++c)
-    if (lane == c && c < out) z = acc[c] + bias[c];
-  if (lane < MAXC) logits_ws[size_t(warp) * MAXC + lane] = lane < out ? z : 0.f;
-  if (out_logits && lane < out) out_logits[size_t(warp) * out + lane] = z;
-  if (target && loss_part) {
-    float mx = z;
+      for (int o = 16; o > 0; o >>= 1) acc[s][c] += __shfl_xor_sync(0xffffffffu, acc[s][c], o);
+    const int b = b0 + s;
+    if (b >= B) break;                                         // warp-uniform
+    float z = -INFINITY;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    float e = lane < out ? expf(z - mx) : 0.f;
+    for (int c = 0; c < MAXC; ++c)
+      if (lane == c && c < out) z = acc[s][c] + bias[c];
+    if (lane < MAXC) logits_ws[size_t(b) * MAXC + lane] = lane < out ? z : 0.f;
+    if (out_logits && lane < out) out_logits[size_t(b) * out + lane] = z;
+    if (target && loss_part) {
+      float mx = z;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) e += __shfl_xor_sync(0xffffffffu, e, o);
-    const int y = int(target[warp]);
-    const float zy = __shfl_sync(0xffffffffu, z, y);
-    if (lane == 0) loss_part[warp] = (mx + logf(e)) - zy;
+      for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      float e = lane < out ? expf(z - mx) : 0.f;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) e += __shfl_xor_sync(0xffffffffu, e, o);
+      const int y = int(target[b]);
+      const float zy = __shfl_sync(0xffffffffu, z, y);
+      if (lane == 0) loss_part[b] = (mx + logf(e)) - zy;
+    }
   }
 }
 // mean of loss_part in a fixed order (one block)
@@ -203,11 +221,10 @@ head_dz_kernel(const float* __restrict__ logits_ws, const int64_t* __restrict__ 
   for (int c = 0; c < MAXC; c += 4)
     *reinterpret_cast<float4*>(dz + size_t(b) * MAXC + c) = make_float4(v[c], v[c + 1], v[c + 2], v[c + 3]);
 }
-// D[G][b][k] = (sum_c dz[b][c] W[c][k]) * (X[G][b][k] > 0), written as hi/lo planes row-major and transposed
+// D[G][b][k] = (sum_c dz[b][c] W[c][k]) * (X[G][b][k] > 0), written as tf32 hi/lo planes
 __global__ void __launch_bounds__(256)
 head_dx_kernel(const float* __restrict__ dz, const float* __restrict__ w, const float* __restrict__ xh, int B, int F, int out,
-               float* __restrict__ hi, float* __restrict__ lo, float* __restrict__ hiT, float* __restrict__ loT) {
-  __shared__ float th[32][33], tl[32][33];
+               float* __restrict__ hi, float* __restrict__ lo) {
   __shared__ float dzs[32][MAXC];
   const int tx = threadIdx.x, ty = threadIdx.y, t = ty * 32 + tx;
   const int b0 = blockIdx.y * 32, k = blockIdx.x * 32 + tx;
@@ -222,23 +239,14 @@ head_dx_kernel(const float* __restrict__ dz, const float* __restrict__ w, const 
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int rr = ty + 8 * i, b = b0 + rr;
-    float h = 0.f, l = 0.f;
     if (b < B && k < F) {
       float a = 0.f;
 #pragma unroll
       for (int c = 0; c < MAXC; ++c) a = fmaf(dzs[rr][c], wv[c], a);
       const float v = xh[size_t(b) * F + k] > 0.f ? a : 0.f;
-      h = tf32_rna(v); l = tf32_rna(v - h);
-      hi[size_t(b) * F + k] = h; lo[size_t(b) * F + k] = l;
+      const float h = tf32_rna(v);
+      hi[size_t(b) * F + k] = h; lo[size_t(b) * F + k] = tf32_rna(v - h);
     }
-    th[rr][tx] = h; tl[rr][tx] = l;
-  }
-  __syncthreads();
-  const int b = b0 + tx;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int cc = ty + 8 * i, k2 = blockIdx.x * 32 + cc;
-    if (k2 < F && b < B) { hiT[size_t(k2) * B + b] = th[tx][cc]; loT[size_t(k2) * B + b] = tl[tx][cc]; }
   }
 }
 // partial[chunk][c][k] = sum_{b in chunk} dz[b][c] * X[G][b][k]
@@ -290,26 +298,27 @@ head_db_kernel(const float* __restrict__ dz, int B, int out, float* __restrict__
   }
   if (threadIdx.x < out) db[threadIdx.x] = s[threadIdx.x];
 }
-// db[n] = sum_b (DT_hi[n][b] + DT_lo[n][b]): one warp per output feature
-__global__ void __launch_bounds__(256)
-bias_grad_kernel(const float* __restrict__ dth, const float* __restrict__ dtl, int F, int B, float* __restrict__ db) {
-  const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (n >= F) return;
-  const float* h = dth + size_t(n) * B;
-  const float* l = dtl + size_t(n) * B;
-  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-  int b = lane * 4;
-  for (; b + 3 < B; b += 128) {
-    const float4 x = *reinterpret_cast<const float4*>(h + b), y = *reinterpret_cast<const float4*>(l + b);
-    a0 += x.x + y.x; a1 += x.y + y.y; a2 += x.z + y.z; a3 += x.w + y.w;
-  }
-  float a = (a0 + a1) + (a2 + a3);
+// db_l[n] = sum_b (D_hi[b][n] + D_lo[b][n]): a 32 x 32 thread block per 32 columns (rows strided by 32, then a fixed-order
+// reduction over the 32 row lanes), blockIdx.y = layer
+struct BiasGradArgs { const float* dh[MAX_PROBLEMS]; const float* dl[MAX_PROBLEMS]; float* db[MAX_PROBLEMS]; };
+__global__ void __launch_bounds__(1024)
+bias_grad_kernel(BiasGradArgs args, int F, int B) {
+  __shared__ float s[32][33];
+  const int tx = threadIdx.x, ty = threadIdx.y, n = blockIdx.x * 32 + tx;
+  const float* h = args.dh[blockIdx.y];
+  const float* l = args.dl[blockIdx.y];
+  float a = 0.f;
+  if (n < F)
+    for (int b = ty; b < B; b += 32) a += h[size_t(b) * F + n] + l[size_t(b) * F + n];
+  s[ty][tx] = a;
+  __syncthreads();
+  if (ty == 0 && n < F) {
+    float t = 0.f;
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
-  if (lane == 0) db[n] = a;
+    for (int i = 0; i < 32; ++i) t += s[i][tx];
+    args.db[blockIdx.y][n] = t;
+  }
 }
-
-static int tile_width() { return 128; }   // N tile of every GEMM (the epilogue keeps one fp32 running sum per column)
 
 }  // namespace mlp
 }  // namespace ddp
@@ -359,23 +368,22 @@ extern "C" int ddp_mlp_forward(const ddp_mlp_shape_t* shape, const float* params
   carve(s, batch, static_cast<char*>(workspace), &w);
   const ParamLayout L = param_layout(s);
   // operands: weights and the input batch as tf32 hi/lo planes
-  for (int l = 0; l < s.G; ++l) launch_split(params + L.w[l], s.F, l == 0 ? s.in : s.F, w.W[l], l >= 1, st);
-  launch_split(x, B, s.in, w.X[0], true, st);
+  for (int l = 0; l < s.G; ++l) launch_split(params + L.w[l], s.F, l == 0 ? s.in : s.F, w.W[l], false, st);
+  launch_split(x, B, s.in, w.X[0], false, st);
   DDP_CUDA(cudaGetLastError());
-  const int bn = tile_width();
   for (int l = 0; l < s.G; ++l) {
     GemmBatch gb{};
     GemmProblem& p = gb.p[0];
     const int K = l == 0 ? s.in : s.F;
-    if (int rc = make_operand_maps(&p, w.X[l].hi, w.X[l].lo, w.W[l].hi, w.W[l].lo, B, s.F, K, bn)) return rc;
+    if (int rc = make_operand_maps(&p, w.X[l].hi, w.X[l].lo, false, K, w.W[l].hi, w.W[l].lo, false, K, B, s.F, K)) return rc;
     p.bias = params + L.b[l];
-    p.out_hi = w.X[l + 1].hi; p.out_lo = w.X[l + 1].lo; p.outT_hi = w.X[l + 1].hiT; p.outT_lo = w.X[l + 1].loT;
-    p.ldo = s.F; p.ldt = B;
+    if (int rc = make_output_maps(&p, w.X[l + 1].hi, w.X[l + 1].lo, B, s.F, s.F)) return rc;
+    p.bits_out = w.bits[l + 1]; p.bits_ld = (s.F + 31) / 32;
     gb.count = 1; gb.tile_start[0] = 0; gb.tile_start[1] = p.mtiles * p.ntiles;
-    if (int rc = launch_gemm(gb, EPI_BIAS_RELU_SPLIT, bn, st)) return rc;
+    if (int rc = launch_gemm(gb, EPI_BIAS_RELU_SPLIT, false, false, st)) return rc;
   }
-  const int wpb = 8;
-  head_fwd_kernel<<<(B + wpb - 1) / wpb, wpb * 32, 0, st>>>(w.X[s.G].hi, w.X[s.G].lo, params + L.w[s.G], params + L.b[s.G], target, B, s.F,
+  const int spb = 8 * HEAD_SPW;                               // samples per 256-thread block
+  head_fwd_kernel<<<(B + spb - 1) / spb, 256, 0, st>>>(w.X[s.G].hi, w.X[s.G].lo, params + L.w[s.G], params + L.b[s.G], target, B, s.F,
                                                          s.out, w.logits, out_logits, out_loss ? w.loss_part : nullptr);
   if (out_loss) loss_mean_kernel<<<1, 1024, 0, st>>>(w.loss_part, B, out_loss);
   DDP_CUDA(cudaGetLastError());
@@ -400,23 +408,22 @@ extern "C" int ddp_mlp_backward(const ddp_mlp_shape_t* shape, const float* param
   // classifier
   head_dz_kernel<<<(B + 255) / 256, 256, 0, st>>>(w.logits, target, dlogits, loss_scale, B, s.out, w.dz);
   head_dx_kernel<<<dim3((s.F + 31) / 32, (B + 31) / 32), dim3(32, 8), 0, st>>>(w.dz, params + L.w[G], w.X[G].hi, B, s.F, s.out,
-                                                                              w.D[G].hi, w.D[G].lo, w.D[G].hiT, w.D[G].loT);
+                                                                              w.D[G].hi, w.D[G].lo);
   const int chunks = (B + HEAD_CHUNK - 1) / HEAD_CHUNK;
   head_dw_partial_kernel<<<dim3((s.F + 127) / 128, chunks), 128, 0, st>>>(w.dz, w.X[G].hi, w.X[G].lo, B, s.F, s.out, w.head_part);
   head_dw_reduce_kernel<<<(s.out * s.F + 255) / 256, 256, 0, st>>>(w.head_part, chunks, s.out * s.F, grad_bucket + L.w[G]);
   head_db_kernel<<<1, 1024, 0, st>>>(w.dz, B, s.out, grad_bucket + L.b[G]);
   DDP_CUDA(cudaGetLastError());
   // data gradients through the wide layers
-  const int bn = tile_width();
   for (int l = G - 1; l >= 1; --l) {
     GemmBatch gb{};
     GemmProblem& p = gb.p[0];
-    if (int rc = make_operand_maps(&p, w.D[l + 1].hi, w.D[l + 1].lo, w.W[l].hiT, w.W[l].loT, B, s.F, s.F, bn)) return rc;
-    p.mask = w.X[l].hi;
-    p.out_hi = w.D[l].hi; p.out_lo = w.D[l].lo; p.outT_hi = w.D[l].hiT; p.outT_lo = w.D[l].loT;
-    p.ldo = s.F; p.ldt = B;
+    // D[l] = D[l+1] @ W_l: B operand (n = in, k = out) is W_l's row-major plane read MN-major
+    if (int rc = make_operand_maps(&p, w.D[l + 1].hi, w.D[l + 1].lo, false, s.F, w.W[l].hi, w.W[l].lo, true, s.F, B, s.F, s.F)) return rc;
+    p.bits_in = w.bits[l]; p.bits_ld = (s.F + 31) / 32;
+    if (int rc = make_output_maps(&p, w.D[l].hi, w.D[l].lo, B, s.F, s.F)) return rc;
     gb.count = 1; gb.tile_start[0] = 0; gb.tile_start[1] = p.mtiles * p.ntiles;
-    if (int rc = launch_gemm(gb, EPI_MASK_SPLIT, bn, st)) return rc;
+    if (int rc = launch_gemm(gb, EPI_MASK_SPLIT, false, true, st)) return rc;
   }
   // all weight gradients in one grouped launch; bias gradients beside it
   {
@@ -426,15 +433,18 @@ extern "C" int ddp_mlp_backward(const ddp_mlp_shape_t* shape, const float* param
     for (int l = 0; l < G; ++l) {
       GemmProblem& p = gb.p[l];
       const int K_l = l == 0 ? s.in : s.F;
-      if (int rc = make_operand_maps(&p, w.D[l + 1].hiT, w.D[l + 1].loT, w.X[l].hiT, w.X[l].loT, s.F, K_l, B, 128)) return rc;
-      p.out = grad_bucket + L.w[l];
-      p.ldo = K_l;
+      // dW_l = D[l+1]^T @ X[l]: both operands are the row-major planes read MN-major (k = batch)
+      if (int rc = make_operand_maps(&p, w.D[l + 1].hi, w.D[l + 1].lo, true, s.F, w.X[l].hi, w.X[l].lo, true, K_l, s.F, K_l, B)) return rc;
+      if (int rc = make_output_maps(&p, grad_bucket + L.w[l], nullptr, s.F, K_l, K_l)) return rc;
       gb.tile_start[l + 1] = gb.tile_start[l] + p.mtiles * p.ntiles;
     }
-    if (int rc = launch_gemm(gb, EPI_PLAIN, 128, st)) return rc;
+    if (int rc = launch_gemm(gb, EPI_PLAIN, true, true, st)) return rc;
   }
-  for (int l = 0; l < G; ++l)
-    bias_grad_kernel<<<(s.F + 7) / 8, 256, 0, st>>>(w.D[l + 1].hiT, w.D[l + 1].loT, s.F, B, grad_bucket + L.b[l]);
+  {
+    BiasGradArgs ba{};
+    for (int l = 0; l < G; ++l) { ba.dh[l] = w.D[l + 1].hi; ba.dl[l] = w.D[l + 1].lo; ba.db[l] = grad_bucket + L.b[l]; }
+    bias_grad_kernel<<<dim3((s.F + 31) / 32, G), dim3(32, 32), 0, st>>>(ba, s.F, B);
+  }
   DDP_CUDA(cudaGetLastError());
   return 0;
 }
@@ -451,16 +461,17 @@ extern "C" int ddp_split_tf32(const float* src, int64_t rows, int64_t cols, floa
   return 0;
 }
 
-extern "C" int ddp_gemm_tn_3xtf32(const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, int M, int N, int K,
-                                  float* c, int ldc, int tile_n, void* stream) {
+extern "C" int ddp_gemm_3xtf32(const float* a_hi, const float* a_lo, int a_mn_major, const float* b_hi, const float* b_lo,
+                               int b_mn_major, int M, int N, int K, float* c, int ldc, void* stream) {
   DDP_REQUIRE(a_hi && a_lo && b_hi && b_lo && c, "null operand");
-  DDP_REQUIRE(M >= 1 && N >= 1 && K >= 4 && (K & 3) == 0 && ldc >= N, "need K %% 4 == 0 and ldc >= N");
-  DDP_REQUIRE(tile_n == 0 || tile_n == 128, "tile_n must be 0 (default) or 128");
-  const int bn = tile_n ? tile_n : 128;
+  DDP_REQUIRE(M >= 1 && N >= 1 && K >= 1 && ldc >= N, "need positive sizes and ldc >= N");
+  DDP_REQUIRE((ldc & 3) == 0 && aligned16(c), "c must be 16-byte aligned with ldc %% 4 == 0");
+  const int lda = a_mn_major ? M : K, ldb = b_mn_major ? N : K;
+  DDP_REQUIRE((lda & 3) == 0 && (ldb & 3) == 0, "the contiguous dimension of each operand must be a multiple of 4");
   GemmBatch gb{};
   GemmProblem& p = gb.p[0];
-  if (int rc = make_operand_maps(&p, a_hi, a_lo, b_hi, b_lo, M, N, K, bn)) return rc;
-  p.out = c; p.ldo = ldc;
+  if (int rc = make_operand_maps(&p, a_hi, a_lo, a_mn_major != 0, lda, b_hi, b_lo, b_mn_major != 0, ldb, M, N, K)) return rc;
+  if (int rc = make_output_maps(&p, c, nullptr, M, N, ldc)) return rc;
   gb.count = 1; gb.tile_start[0] = 0; gb.tile_start[1] = p.mtiles * p.ntiles;
-  return launch_gemm(gb, EPI_PLAIN, bn, static_cast<cudaStream_t>(stream));
+  return launch_gemm(gb, EPI_PLAIN, a_mn_major != 0, b_mn_major != 0, static_cast<cudaStream_t>(stream));
 }

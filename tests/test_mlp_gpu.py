@@ -17,23 +17,34 @@ def test_split_tf32_planes(native):
     assert torch.equal(hiT, hi.t().contiguous()) and torch.equal(loT, lo.t().contiguous())
 
 
-@pytest.mark.parametrize("M,N,K,tile_n", [(128, 128, 32, 128), (256, 256, 64, 0), (200, 136, 100, 128), (200, 136, 1000, 0),
-                                          (1000, 784, 512, 128), (2048, 1024, 784, 0), (1024, 1024, 4096, 128), (4, 12, 8, 128)])
-def test_gemm_3xtf32_matches_fp64(native, M, N, K, tile_n):
+@pytest.mark.parametrize("M,N,K", [(128, 128, 32), (256, 256, 64), (200, 136, 100), (200, 136, 1000), (1000, 784, 512),
+                                   (2048, 1024, 784), (1024, 1024, 4096), (4, 12, 8), (1024, 784, 260)])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
+def test_gemm_3xtf32_matches_fp64(native, M, N, K, a_mn, b_mn):
+    """Every operand-layout combination the step uses (forward K/K, data gradient K/MN, weight gradient MN/MN)."""
+    if (a_mn and M % 4) or (b_mn and N % 4):
+        pytest.skip("MN-major operands need a contiguous dimension that is a multiple of 4")
     torch.manual_seed(M + N + K)
     a = torch.randn(M, K, device="cuda")
     b = torch.randn(N, K, device="cuda")
-    a_hi, a_lo = native.split_tf32(a)
-    b_hi, b_lo = native.split_tf32(b)
+    a_st = a.t().contiguous() if a_mn else a            # [K][M] when MN-major
+    b_st = b.t().contiguous() if b_mn else b
+    # MN-major tiles may read (never use) a few bytes past the last row: keep the planes inside a larger allocation
+    def planes(t):
+        hi, lo = native.split_tf32(t)
+        pad_hi = torch.zeros(t.numel() + 64, device="cuda"); pad_lo = torch.zeros(t.numel() + 64, device="cuda")
+        pad_hi[:t.numel()].copy_(hi.reshape(-1)); pad_lo[:t.numel()].copy_(lo.reshape(-1))
+        return pad_hi[:t.numel()].view(t.shape), pad_lo[:t.numel()].view(t.shape)
+    a_hi, a_lo = planes(a_st)
+    b_hi, b_lo = planes(b_st)
     full = torch.full((M, N + 4), 7.0, device="cuda")                  # ldc > N: padding columns must stay untouched
     out = full[:, :N]
-    native.gemm_tn_3xtf32(a_hi, a_lo, b_hi, b_lo, out=out, tile_n=tile_n)
+    native.gemm_3xtf32(a_hi, a_lo, b_hi, b_lo, out=out, a_mn_major=a_mn, b_mn_major=b_mn)
     ref64 = a.double() @ b.double().t()
     scale = (a.double().abs() @ b.double().abs().t())                  # per-element magnitude of the summed products
     err = (out.double() - ref64).abs()
     assert torch.all(err <= 1e-6 * scale + 1e-30), f"max err/scale {float((err / scale).max()):.3e}"
     err32 = ((a @ b.t()).double() - ref64).abs().max().item()         # cuBLAS fp32 on the same inputs, for scale
-    print(f"M{M} N{N} K{K}: max err {err.max().item():.3e} (cuBLAS fp32 {err32:.3e}), err/scale {float((err / scale).max()):.3e}")
     assert err.max().item() <= 4 * err32 + 1e-6 * ref64.abs().max().item()
     assert torch.all(full[:, N:] == 7.0)
 
@@ -127,7 +138,7 @@ def test_mlp_full_size_against_oracle(native):
     for name in layers:
         a_hi, a_lo = native.split_tf32(h)
         b_hi, b_lo = native.split_tf32(sd[name + ".weight"].cuda())
-        h = torch.relu(native.gemm_tn_3xtf32(a_hi, a_lo, b_hi, b_lo) + sd[name + ".bias"].cuda())
+        h = torch.relu(native.gemm_3xtf32(a_hi, a_lo, b_hi, b_lo) + sd[name + ".bias"].cuda())
         hh, hl = native.split_tf32(h)
         h = hh + hl                                   # activations travel as tf32 hi/lo planes
         masks.append((h > 0).double())
