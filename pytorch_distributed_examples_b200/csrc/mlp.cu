@@ -21,7 +21,7 @@ namespace ddp {
 namespace mlp {
 
 constexpr int MAXC = 16;            // classifier width supported by the head kernels
-constexpr int HEAD_CHUNK = 128;     // samples per partial sum of the classifier weight gradient
+constexpr int HEAD_CHUNK = 32;      // samples per partial sum of the classifier weight gradient
 
 struct Shape { int in, F, H, out, G; };     // G = H + 1 tensor-core layers
 static int check_shape(const ddp_mlp_shape_t* s, Shape* o) {
@@ -59,6 +59,7 @@ struct Work {
   float* dz;                    // [B][MAXC]
   float* loss_part;             // [B]
   float* head_part;             // [B/HEAD_CHUNK][out][F]
+  float* bias_part;             // [BIAS_RC][G][F]
 };
 static int64_t carve(const Shape& s, int64_t B, char* base, Work* w) {
   int64_t off = 0;
@@ -78,6 +79,7 @@ static int64_t carve(const Shape& s, int64_t B, char* base, Work* w) {
   tmp.dz = take(B * MAXC);
   tmp.loss_part = take(B);
   tmp.head_part = take(((B + HEAD_CHUNK - 1) / HEAD_CHUNK) * int64_t(s.out) * s.F);
+  tmp.bias_part = take(int64_t(16) * s.G * s.F);
   if (w) *w = tmp;
   return off;
 }
@@ -124,7 +126,7 @@ static void launch_split(const float* src, int rows, int cols, const Planes& p, 
 }
 
 // ---- classifier forward: one warp per HEAD_SPW samples (the classifier rows are loaded once for all of them) -----
-constexpr int HEAD_SPW = 4;
+constexpr int HEAD_SPW = 1;
 __global__ void __launch_bounds__(256)
 head_fwd_kernel(const float* __restrict__ xh, const float* __restrict__ xl, const float* __restrict__ w, const float* __restrict__ bias,
                 const int64_t* __restrict__ target, int B, int F, int out, float* __restrict__ logits_ws,
@@ -137,6 +139,7 @@ head_fwd_kernel(const float* __restrict__ xh, const float* __restrict__ xl, cons
   for (int s = 0; s < HEAD_SPW; ++s)
 #pragma unroll
     for (int c = 0; c < MAXC; ++c) acc[s][c] = 0.f;
+#pragma unroll 4
   for (int k = lane; k < F; k += 32) {
     float v[HEAD_SPW];
 #pragma unroll
@@ -265,7 +268,8 @@ head_dw_partial_kernel(const float* __restrict__ dz, const float* __restrict__ x
 #pragma unroll
   for (int c = 0; c < MAXC; ++c) acc[c] = 0.f;
   const int nb = min(HEAD_CHUNK, B - b0);
-  for (int i = 0; i < nb; ++i) {
+#pragma unroll 8
+  for (int i = 0; i < nb; ++i) {                               // rows past B have dz = 0 in smem, but are not read
     const size_t o = size_t(b0 + i) * F + k;
     const float v = xh[o] + xl[o];
 #pragma unroll
@@ -298,25 +302,63 @@ head_db_kernel(const float* __restrict__ dz, int B, int out, float* __restrict__
   }
   if (threadIdx.x < out) db[threadIdx.x] = s[threadIdx.x];
 }
-// db_l[n] = sum_b (D_hi[b][n] + D_lo[b][n]): a 32 x 32 thread block per 32 columns (rows strided by 32, then a fixed-order
-// reduction over the 32 row lanes), blockIdx.y = layer
+// db_l[n] = sum_b (D_hi[b][n] + D_lo[b][n]) in two fixed-order stages.  Stage 1: block (x = 128-column group, y = layer,
+// z = row chunk), 8 warps; a lane owns 4 columns (float4 loads, a warp covers 512 contiguous bytes of a row), warp w
+// takes rows w, w+8, ... of the chunk, the 8 warp sums are added in warp order -> part[z][layer][n].  Stage 2 adds
+// the BIAS_RC chunk sums in order.
+constexpr int BIAS_RC = 16;
 struct BiasGradArgs { const float* dh[MAX_PROBLEMS]; const float* dl[MAX_PROBLEMS]; float* db[MAX_PROBLEMS]; };
-__global__ void __launch_bounds__(1024)
-bias_grad_kernel(BiasGradArgs args, int F, int B) {
-  __shared__ float s[32][33];
-  const int tx = threadIdx.x, ty = threadIdx.y, n = blockIdx.x * 32 + tx;
+__global__ void __launch_bounds__(256)
+bias_grad_partial_kernel(BiasGradArgs args, int F, int B, float* __restrict__ part) {
+  __shared__ float4 s[8][32];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n = blockIdx.x * 128 + lane * 4;
+  const int rows_per = (B + BIAS_RC - 1) / BIAS_RC;
+  const int r0 = blockIdx.z * rows_per, r1 = min(B, r0 + rows_per);
   const float* h = args.dh[blockIdx.y];
   const float* l = args.dl[blockIdx.y];
-  float a = 0.f;
-  if (n < F)
-    for (int b = ty; b < B; b += 32) a += h[size_t(b) * F + n] + l[size_t(b) * F + n];
-  s[ty][tx] = a;
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (n < F) {                                                 // F % 4 == 0: a float4 is all in or all out
+#pragma unroll 4
+    for (int b = r0 + warp; b < r1; b += 8) {
+      const float4 x = *reinterpret_cast<const float4*>(h + size_t(b) * F + n);
+      const float4 y = *reinterpret_cast<const float4*>(l + size_t(b) * F + n);
+      a.x += x.x + y.x; a.y += x.y + y.y; a.z += x.z + y.z; a.w += x.w + y.w;
+    }
+  }
+  s[warp][lane] = a;
   __syncthreads();
-  if (ty == 0 && n < F) {
-    float t = 0.f;
+  if (warp == 0 && n < F) {
+    float4 t = s[0][lane];
 #pragma unroll
-    for (int i = 0; i < 32; ++i) t += s[i][tx];
-    args.db[blockIdx.y][n] = t;
+    for (int i = 1; i < 8; ++i) { const float4 v = s[i][lane]; t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w; }
+    *reinterpret_cast<float4*>(part + (size_t(blockIdx.z) * gridDim.y + blockIdx.y) * F + n) = t;
+  }
+}
+__global__ void __launch_bounds__(256)
+bias_grad_reduce_kernel(BiasGradArgs args, int F, int layers, const float* __restrict__ part) {
+  const int n = blockIdx.x * 256 + threadIdx.x;
+  if (n >= F) return;
+  float t = 0.f;
+#pragma unroll
+  for (int z = 0; z < BIAS_RC; ++z) t += part[(size_t(z) * layers + blockIdx.y) * F + n];
+  args.db[blockIdx.y][n] = t;
+}
+
+// ---- all weight matrices -> tf32 hi/lo planes in one launch (blockIdx.z = layer) ------------------------------------
+struct SplitArgs { const float* src[MAX_PROBLEMS]; float* hi[MAX_PROBLEMS]; float* lo[MAX_PROBLEMS]; int64_t n[MAX_PROBLEMS]; };
+__global__ void __launch_bounds__(256)
+split_flat_kernel(SplitArgs args) {
+  const int64_t n4 = args.n[blockIdx.z] >> 2;                  // every tensor is a multiple of 4 floats (F % 4 == in % 4 == 0)
+  const float4* src = reinterpret_cast<const float4*>(args.src[blockIdx.z]);
+  float4* hi = reinterpret_cast<float4*>(args.hi[blockIdx.z]);
+  float4* lo = reinterpret_cast<float4*>(args.lo[blockIdx.z]);
+  for (int64_t i = int64_t(blockIdx.x) * 256 + threadIdx.x; i < n4; i += int64_t(gridDim.x) * 256) {
+    const float4 v = src[i];
+    float4 h, l;
+    h.x = tf32_rna(v.x); h.y = tf32_rna(v.y); h.z = tf32_rna(v.z); h.w = tf32_rna(v.w);
+    l.x = tf32_rna(v.x - h.x); l.y = tf32_rna(v.y - h.y); l.z = tf32_rna(v.z - h.z); l.w = tf32_rna(v.w - h.w);
+    hi[i] = h; lo[i] = l;
   }
 }
 
@@ -368,8 +410,17 @@ extern "C" int ddp_mlp_forward(const ddp_mlp_shape_t* shape, const float* params
   carve(s, batch, static_cast<char*>(workspace), &w);
   const ParamLayout L = param_layout(s);
   // operands: weights and the input batch as tf32 hi/lo planes
-  for (int l = 0; l < s.G; ++l) launch_split(params + L.w[l], s.F, l == 0 ? s.in : s.F, w.W[l], false, st);
-  launch_split(x, B, s.in, w.X[0], false, st);
+  {
+    SplitArgs sa{};
+    for (int l = 0; l < s.G; ++l) {
+      sa.src[l] = params + L.w[l]; sa.hi[l] = w.W[l].hi; sa.lo[l] = w.W[l].lo;
+      sa.n[l] = int64_t(s.F) * (l == 0 ? s.in : s.F);
+    }
+    split_flat_kernel<<<dim3(128, 1, s.G), 256, 0, st>>>(sa);
+    SplitArgs sx{};
+    sx.src[0] = x; sx.hi[0] = w.X[0].hi; sx.lo[0] = w.X[0].lo; sx.n[0] = int64_t(B) * s.in;
+    split_flat_kernel<<<dim3(256, 1, 1), 256, 0, st>>>(sx);
+  }
   DDP_CUDA(cudaGetLastError());
   for (int l = 0; l < s.G; ++l) {
     GemmBatch gb{};
@@ -443,7 +494,9 @@ extern "C" int ddp_mlp_backward(const ddp_mlp_shape_t* shape, const float* param
   {
     BiasGradArgs ba{};
     for (int l = 0; l < G; ++l) { ba.dh[l] = w.D[l + 1].hi; ba.dl[l] = w.D[l + 1].lo; ba.db[l] = grad_bucket + L.b[l]; }
-    bias_grad_kernel<<<dim3((s.F + 31) / 32, G), dim3(32, 32), 0, st>>>(ba, s.F, B);
+    static_assert(BIAS_RC == 16, "carve() reserves 16 row chunks");
+    bias_grad_partial_kernel<<<dim3((s.F + 127) / 128, G, BIAS_RC), 256, 0, st>>>(ba, s.F, B, w.bias_part);
+    bias_grad_reduce_kernel<<<dim3((s.F + 255) / 256, G), 256, 0, st>>>(ba, s.F, G, w.bias_part);
   }
   DDP_CUDA(cudaGetLastError());
   return 0;

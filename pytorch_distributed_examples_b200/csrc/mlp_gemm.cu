@@ -38,10 +38,14 @@ namespace mlp {
 #ifdef DDP_MLP_TIMING
 __device__ unsigned long long g_mlp_dbg[160 * 16];
 #define MT_T0(var) const long long var = clock64()
-#define MT_ACC(slot, t0) do { g_mlp_dbg[blockIdx.x * 16 + (slot)] += (unsigned long long)(clock64() - (t0)); } while (0)
+#define MT_LOCALS long long mt_loc[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}
+#define MT_ACC(slot, t0) do { mt_loc[slot] += clock64() - (t0); } while (0)          // registers: no memory traffic in the loops
+#define MT_FLUSH(slot) do { g_mlp_dbg[blockIdx.x * 16 + (slot)] += (unsigned long long)mt_loc[slot]; } while (0)
 #else
 #define MT_T0(var)
+#define MT_LOCALS
 #define MT_ACC(slot, t0)
+#define MT_FLUSH(slot)
 #endif
 
 constexpr int BM = 128;
@@ -159,6 +163,7 @@ gemm3x_kernel(const __grid_constant__ GemmBatch batch) {
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   MT_T0(t_kernel);
+  MT_LOCALS;
   if (tid == 0) {
     for (int s = 0; s < C::STAGES; ++s) { bar_init(full(s), 1); bar_init(empty(s), 1); }
     for (int b = 0; b < 2; ++b) { bar_init(tfull(b), 1); bar_init(tempty(b), 128); }
@@ -203,6 +208,7 @@ gemm3x_kernel(const __grid_constant__ GemmBatch batch) {
           }
         }
       }
+      MT_FLUSH(1);
     }
   } else if (warp == 1) {
     // ======================= MMA issuer =======================
@@ -222,6 +228,7 @@ gemm3x_kernel(const __grid_constant__ GemmBatch batch) {
           for (int kb = kb0; kb < kend; ++kb, ++it) {
             const int slot = it % C::STAGES;
             { MT_T0(tw); bar_wait(full(slot), (it / C::STAGES) & 1); MT_ACC(3, tw); }                               // 3: MMA waits full
+            if (it == 0) MT_ACC(8, t_kernel);                                                                     // 8: kernel start -> first operands landed
             MT_T0(ti);
             asm volatile("tcgen05.fence::after_thread_sync;");
             const uint32_t st = ring + slot * C::STAGE_BYTES;
@@ -243,6 +250,8 @@ gemm3x_kernel(const __grid_constant__ GemmBatch batch) {
           umma_commit_to(tfull(buf));
         }
       }
+      MT_ACC(9, t_kernel);                                                                                        // 9: kernel start -> last MMA issued
+      MT_FLUSH(2); MT_FLUSH(3); MT_FLUSH(4); MT_FLUSH(8); MT_FLUSH(9);
     }
   } else {
     // ======================= epilogue: warp w reads TMEM lanes 32*(w%4).. =======================
@@ -257,7 +266,7 @@ gemm3x_kernel(const __grid_constant__ GemmBatch batch) {
       for (int j = 0; j < BN; ++j) sum[j] = 0.f;
       for (int kb0 = 0; kb0 < kblocks; kb0 += KCHUNK, ++sub) {
         const int buf = sub & 1;
-        { MT_T0(tw); bar_wait(tfull(buf), (sub >> 1) & 1); if (tid == 64) MT_ACC(5, tw); }                          // 5: epilogue waits accumulators
+        { MT_T0(tw); bar_wait(tfull(buf), (sub >> 1) & 1); MT_ACC(5, tw); }                          // 5: epilogue waits accumulators
         MT_T0(td);
         asm volatile("tcgen05.fence::after_thread_sync;");
 #pragma unroll
@@ -269,7 +278,7 @@ gemm3x_kernel(const __grid_constant__ GemmBatch batch) {
         }
         asm volatile("tcgen05.fence::before_thread_sync;");
         bar_arrive(tempty(buf));
-        if (tid == 64) MT_ACC(6, td);                                                                             // 6: drain
+        MT_ACC(6, td);                                                                             // 6: drain
       }
       MT_T0(ts);
       const int row = q * 32 + lane;
@@ -324,13 +333,14 @@ gemm3x_kernel(const __grid_constant__ GemmBatch batch) {
           asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         }
       }
-      if (tid == 64) MT_ACC(7, ts);                                                                               // 7: store phase
+      MT_ACC(7, ts);                                                                               // 7: store phase
     }
     if (tid == 64) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    if (tid == 64) { MT_FLUSH(5); MT_FLUSH(6); MT_FLUSH(7); }
   }
   asm volatile("tcgen05.fence::before_thread_sync;");
   __syncthreads();
-  if (tid == 0) MT_ACC(0, t_kernel);                                                                              // 0: whole kernel
+  if (tid == 0) { MT_ACC(0, t_kernel); MT_FLUSH(0); }                                                                             // 0: whole kernel
   if (warp == 1) {
     asm volatile("tcgen05.fence::after_thread_sync;");
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "n"(C::TMEM_COLS));

@@ -6,7 +6,7 @@ sys.path.insert(0, ROOT)
 from pytorch_distributed_examples_b200 import _native
 nat = _native.get(); nat.bind_device(0)
 nat.lib.ddp_debug_mlp_timing.argtypes = [ctypes.c_void_p, ctypes.c_int]
-names = ["kernel", "prod wait empty", "mma wait tmem", "mma wait full", "mma issue", "epi wait acc", "epi drain", "epi store"]
+names = ["kernel", "prod wait empty", "mma wait tmem", "mma wait full", "mma issue", "epi wait acc", "epi drain", "epi store", "t first operands", "t last mma issued"]
 def run(tag, fn):
     for _ in range(2):
         fn()
