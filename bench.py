@@ -325,6 +325,31 @@ def main():
         xb = torch.empty(65536, 1, 28, 28, device="cuda"); yb = torch.empty(65536, dtype=torch.int64, device="cuda")
         t = timed(lambda: nat.synth_batch(1, None, 0, 65536, xb, yb))
         extra["synth_batch_65536"] = {"GB/s": 65536 * 3144 / t / 1e9, "frac_hbm": 65536 * 3144 / t / 1e9 / peaks["hbm"], "us": t * 1e6}
+        # the DDP script's own model: native tensor-core MLP step vs torch/cuBLAS strict fp32, same GPU
+        try:
+            from oracle import mlp_oracle   # parameter initialisation only (reference constructor order)
+            Bm = 4096
+            xm, ym = ds.batch(base_index=0, count=Bm)
+            xm = xm.reshape(Bm, -1).contiguous()
+            torch.manual_seed(0)
+            sdm = mlp_oracle.OracleMLP(5, 1024).state_dict()
+            mlp = pkg.Model(5, 1024); mlp.load_state_dict(sdm); mlp = mlp.cuda()
+            t_nat = timed(lambda: mlp.loss_and_grads(xm, ym), reps=10)
+            torch.backends.cuda.matmul.allow_tf32 = False
+            tm = mlp_oracle.OracleMLP(5, 1024); tm.load_state_dict(sdm); tm = tm.cuda()
+            def torch_fb():
+                tm.zero_grad(set_to_none=True)
+                torch.nn.functional.cross_entropy(tm(xm), ym).backward()
+            t_ref = timed(torch_fb, reps=10)
+            flop = 2.0 * 17_364_992 * Bm
+            extra["mlp_5x1024_fwd_bwd_b4096"] = {"native_us": t_nat * 1e6, "native_tflops_fp32_equiv": flop / t_nat / 1e12,
+                                                 "torch_fp32_cublas_us": t_ref * 1e6, "speedup": t_ref / t_nat,
+                                                 "frac_of_tf32_tensor_peak": 3 * flop / t_nat / 1e12 / (peaks["tflops"] / 2),
+                                                 "note": "3xTF32 tcgen05 GEMMs (3 tensor-core products per fp32 product); "
+                                                         "tf32 peak taken as half the measured bf16 peak; timings include an L2 flush"}
+            del mlp, tm, xm, ym
+        except Exception as exc:       # the MLP row is an extra: never lose the headline line over it
+            extra["mlp_5x1024_fwd_bwd_b4096"] = {"error": repr(exc)}
         line["extra"] = extra
         del g, p, s1, s2, flush, chunks, bucket, xb, yb
         if N == 1:

@@ -169,6 +169,34 @@ def main():
         same_on_all_ranks(ms, "fused hook (symmetric)")
     log("DDP comm hooks ok")
 
+    # 3b. the DDP script's own model with native kernels: pkg.Model under stock DDP + our hook, the reference loop body
+    #     (ref: pytorch_elastic/mnist_ddp_elastic.py:58,70-75,172-174) == the oracle's W-rank "average then Adam" loop
+    from oracle import mlp_oracle, synth_oracle
+    import numpy as np
+    Hn, Fn, Bn, steps = 2, 256, 32, 3
+    torch.manual_seed(31)
+    sd0 = {k: v.detach().clone() for k, v in mlp_oracle.OracleMLP(Hn, Fn).state_dict().items()}
+    xn, yn = synth_oracle.synth_batch(1234, np.arange(steps * W * Bn))
+    xs = torch.from_numpy(xn).view(steps, W * Bn, 1, 28, 28); ys = torch.from_numpy(yn).view(steps, W * Bn)
+    _, sd_ref = mlp_oracle.train_steps(sd0, xs, ys, Hn, Fn, "adam", world=W, lr=1e-3)
+    mm = pkg.Model(hidden_layers=Hn, features=Fn); mm.load_state_dict(sd0); mm = mm.cuda()
+    dm = DDP(mm, device_ids=[local], gradient_as_bucket_view=True)
+    dm.register_comm_hook(pkg.HookState(), pkg.allreduce_hook)
+    om = torch.optim.Adam(dm.parameters(), lr=1e-3)
+    crit = torch.nn.CrossEntropyLoss()
+    for k in range(steps):
+        sl = slice(R * Bn, (R + 1) * Bn)
+        om.zero_grad()
+        crit(dm(xs[k, sl].cuda()), ys[k, sl].cuda()).backward()
+        om.step()
+    torch.cuda.synchronize()
+    for key, v in mm.state_dict().items():
+        ref = sd_ref[key]
+        d = (v.cpu() - ref).abs()
+        assert (d <= 1e-5 * ref.abs().max().item() + 1e-3 * 1e-3).float().mean().item() >= 0.98 and d.max().item() <= 0.25 * 1e-3 * steps, key
+    same_on_all_ranks(mm.flat_params, "native MLP under DDP")
+    log("native MLP (tensor-core GEMMs) under DDP == oracle W-rank Adam loop ok")
+
     # 4. TrainStep (allreduce captured in the CUDA graph) == module path
     def run_steps(mode):
         torch.manual_seed(21)
