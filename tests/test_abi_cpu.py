@@ -55,6 +55,21 @@ def test_layout_queries_and_argument_validation_without_gpu():
     assert lib.ddp_bucket_copy(None, None, None, None, None, 3, None, 0, None) == -1000
     assert lib.ddp_allreduce_sum(None, None, 4, 0, None) == -1000
     assert lib.ddp_comm_init(None, None, 2, 0) == -1000
+    # MLP of the DDP script: layout follows the reference state_dict (ref: pytorch_elastic/mnist_ddp_elastic.py:137-147)
+    shape = _native.MLPShape(784, 1024, 5, 10)
+    layout, total = nat.mlp_param_layout(shape)
+    sizes = [784 * 1024, 1024] + [1024 * 1024, 1024] * 5 + [10 * 1024, 10]      # Model(hidden_layers=5, features=1024)
+    assert [n for _, n in layout] == sizes and sum(sizes) == 6_062_090
+    assert all(o % 4 == 0 for o, _ in layout) and total == layout[-1][0] + 12
+    assert nat.mlp_workspace_bytes(shape, 64) % 256 == 0 and nat.mlp_workspace_bytes(shape, 64) > 64 * 1024 * 4 * 2 * 12
+    assert lib.ddp_mlp_workspace_bytes(ctypes.byref(shape), 6) == -1 and b"multiple of 4" in lib.ddp_last_error()
+    bad = _native.MLPShape(783, 1024, 5, 10)
+    assert lib.ddp_mlp_param_count(ctypes.byref(bad)) == -1
+    assert lib.ddp_mlp_forward(ctypes.byref(shape), None, None, None, 64, None, None, None, None) == -1000
+    assert lib.ddp_mlp_backward(ctypes.byref(shape), None, None, None, 1.0, 64, None, None, None) == -1000
+    assert lib.ddp_split_tf32(None, 4, 4, None, None, None, None, None) == -1000
+    assert lib.ddp_gemm_3xtf32(None, None, 0, None, None, 0, 4, 4, 4, None, 4, None) == -1000
+    assert lib.ddp_sym_allreduce(None, 0, 0, 2, 0, 0, 4, 0, 1.0, 0, 0, None) == -1000
 
 
 def test_product_fails_loudly_without_library_or_gpu(tmp_path):
@@ -64,6 +79,8 @@ def test_product_fails_loudly_without_library_or_gpu(tmp_path):
     _native.set_instance(None)
     with pytest.raises(RuntimeError, match="CUDA"):
         pkg.Net()(torch.zeros(2, 1, 28, 28))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        pkg.Model(hidden_layers=1, features=64)(torch.zeros(4, 784))
     nat = _native.get()
     with pytest.raises(RuntimeError, match="CUDA tensor"):
         nat.scale(torch.zeros(4), 2.0)

@@ -86,3 +86,26 @@ def test_synth_oracle_properties():
     assert [int(v[0]) for v in r] == [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]
     r = synth_oracle.philox4x32_10([0x243f6a88], [0x85a308d3], [0x13198a2e], [0x03707344], 0xa4093822, 0x299f31d0)
     assert [int(v[0]) for v in r] == [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1]
+
+
+@pytest.mark.parametrize("name", ["mlp_h1_f128.pt", "mlp_h2_f64.pt"])
+def test_mlp_oracle_matches_reference_golden(name):
+    """oracle/mlp_oracle.py against the fixtures written from the reference's own Model / Trainer._run_batch
+    (ref: pytorch_elastic/mnist_ddp_elastic.py:70-75,133-159)."""
+    from oracle import mlp_oracle
+    fx = load_golden(name)
+    H, Fe = fx["hidden_layers"], fx["features"]
+    logits, loss, grads = mlp_oracle.forward_backward(fx["state_dict0"], fx["xs"][0], fx["ys"][0], H, Fe)
+    torch.testing.assert_close(logits, fx["logits"], rtol=1e-6, atol=1e-6)
+    torch.testing.assert_close(loss, fx["loss"], rtol=1e-6, atol=1e-7)
+    for k, g in fx["grads"].items():
+        torch.testing.assert_close(grads[k], g, rtol=1e-5, atol=1e-8)
+    losses, sd = mlp_oracle.train_steps(fx["state_dict0"], fx["xs"], fx["ys"], H, Fe, "adam", lr=1e-3)
+    torch.testing.assert_close(losses[:, 0], fx["losses"], rtol=1e-6, atol=1e-7)
+    for k, v in fx["state_dict"].items():
+        torch.testing.assert_close(sd[k], v, rtol=1e-5, atol=1e-6)
+    # W = 2 semantics: averaging two half-batch gradients == the full-batch gradient of the mean loss
+    l2, sd2 = mlp_oracle.train_steps(fx["state_dict0"], fx["xs"][:1], fx["ys"][:1], H, Fe, "adam", world=2, lr=1e-3)
+    l1, sd1 = mlp_oracle.train_steps(fx["state_dict0"], fx["xs"][:1], fx["ys"][:1], H, Fe, "adam", world=1, lr=1e-3)
+    for k in sd1:
+        assert (sd2[k] - sd1[k]).abs().max().item() <= 2.5e-4     # one Adam step moves every weight by <= lr; sign(g) agrees
