@@ -210,6 +210,11 @@ constexpr int D2_THREADS = D2_WARPS * 32;
 constexpr int D2_WS = C2 * 25 * 2 * 8;              // [co][tap][g][8]
 constexpr int D2_PER_WARP = A1_PER;                // dy2 [20][8][8] (1280 floats), later reused for the staged output [10][144]
 constexpr int D2_SMEM = (D2_WS + D2_WARPS * D2_PER_WARP) * 4;
+// S warps share one sample (S = 1, 2, 4): warp `part` of the S takes the live output channels co = part, part+S, ...
+// and the S partial planes are added in part order.  S > 1 is the small-batch mode: with one warp per sample the
+// kernel is a single ~40 us dependency chain however few samples there are; at B <= 1024 the SMs are mostly empty
+// and splitting the chain four ways is nearly free.  S = 1 is the throughput mode (no redundant dy2 rebuild).
+template <int S>
 __global__ void __launch_bounds__(D2_THREADS, 2)
 conv2_dgrad_kernel(const float* __restrict__ params, const float* __restrict__ da2,
                    const float* __restrict__ a2, const uint8_t* __restrict__ idx2,
@@ -217,7 +222,9 @@ conv2_dgrad_kernel(const float* __restrict__ params, const float* __restrict__ d
   extern __shared__ __align__(128) float smem[];
   float* w_s = smem;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  float* dy_s = smem + D2_WS + warp * D2_PER_WARP;  // [20][8][8]
+  constexpr int SPC = D2_WARPS / S;                 // samples per CTA iteration
+  const int slot = warp / S, part = warp % S;
+  float* dy_s = smem + D2_WS + warp * D2_PER_WARP;  // [20][8][8], private to the warp
   float* out_s = dy_s;                              // [10][144]: written only after the last read of dy2
   for (int i = tid; i < D2_WS; i += D2_THREADS) {
     int cc = i & 7, g = (i >> 3) & 1, ct = i >> 4;  // ct = co*25 + tap
@@ -235,8 +242,8 @@ conv2_dgrad_kernel(const float* __restrict__ params, const float* __restrict__ d
     cok[r] = cc >= 0 && cc < O2;
   }
   const int pbase = (3 * ty - 4) * O2 + (3 * tx - 4);
-  const int total_warps = gridDim.x * D2_WARPS;
-  for (int b = blockIdx.x * D2_WARPS + warp; b < B; b += total_warps) {
+  const int total_slots = gridDim.x * SPC;
+  for (int b = blockIdx.x * SPC + slot; b < B; b += total_slots) {
     // rebuild dy2: 320 (co,pp) entries, 10 per lane, each a 2x2 block with one non-zero.
     // live_mask bit co: the channel has any gradient for this sample (Dropout2d zeroes ~half of the
     // channels, ReLU some more) -- dead channels are skipped, a warp-uniform branch.
@@ -264,7 +271,7 @@ conv2_dgrad_kernel(const float* __restrict__ params, const float* __restrict__ d
 #pragma unroll
         for (int k = 0; k < 5; ++k) acc[a][c][k] = 0.f;
 #pragma unroll 1
-    for (int co = 0; co < C2; ++co) {
+    for (int co = part; co < C2; co += S) {
       if (!((live_mask >> co) & 1u)) continue;
       float patch[7][7];
       const float* dp = dy_s + co * 64 + pbase;
@@ -299,17 +306,25 @@ conv2_dgrad_kernel(const float* __restrict__ params, const float* __restrict__ d
 #pragma unroll
         for (int ox = 0; ox < 3; ++ox)
           out_s[(g * 5 + k) * 144 + (3 * ty + oy) * P1 + 3 * tx + ox] = acc[oy][ox][k];
-    __syncwarp();
+    if (S == 1) __syncwarp();
+    else asm volatile("bar.sync %0, %1;" :: "r"(1 + slot), "n"(S * 32) : "memory");   // the S partial planes are complete
     const float4* a4 = reinterpret_cast<const float4*>(a1 + size_t(b) * A1_PER);
     float4* o4 = reinterpret_cast<float4*>(dp1 + size_t(b) * A1_PER);
-    for (int i = lane; i < A1_PER / 4; i += 32) {
-      float4 v = reinterpret_cast<const float4*>(out_s)[i];
+    const float* first = smem + D2_WS + (slot * S) * D2_PER_WARP;                     // plane of part 0
+    for (int i = part * 32 + lane; i < A1_PER / 4; i += S * 32) {
+      float4 v = reinterpret_cast<const float4*>(first)[i];
+#pragma unroll
+      for (int p = 1; p < S; ++p) {                   // fixed order: part 0 + part 1 + ...
+        const float4 u = reinterpret_cast<const float4*>(first + p * D2_PER_WARP)[i];
+        v.x += u.x; v.y += u.y; v.z += u.z; v.w += u.w;
+      }
       float4 a = a4[i];
       v.x = a.x > 0.f ? v.x : 0.f; v.y = a.y > 0.f ? v.y : 0.f;
       v.z = a.z > 0.f ? v.z : 0.f; v.w = a.w > 0.f ? v.w : 0.f;
       o4[i] = v;
     }
-    __syncwarp();
+    if (S == 1) __syncwarp();
+    else asm volatile("bar.sync %0, %1;" :: "r"(1 + slot), "n"(S * 32) : "memory");   // planes may be overwritten again
   }
 }
 
@@ -648,7 +663,9 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
   static bool attr_done = false;
   if (!attr_done) {
     DDP_CUDA(cudaFuncSetAttribute(head_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HB_SMEM));
-    DDP_CUDA(cudaFuncSetAttribute(conv2_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, D2_SMEM));
+    DDP_CUDA(cudaFuncSetAttribute(conv2_dgrad_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, D2_SMEM));
+    DDP_CUDA(cudaFuncSetAttribute(conv2_dgrad_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, D2_SMEM));
+    DDP_CUDA(cudaFuncSetAttribute(conv2_dgrad_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, D2_SMEM));
     DDP_CUDA(cudaFuncSetAttribute(conv2_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, W2_SMEM));
     DDP_CUDA(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, W1_SMEM));
     attr_done = true;
@@ -665,10 +682,14 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
   // (conv2_wgrad is independent of dgrad -> conv1_wgrad and was tried on a forked stream: each kernel already
   //  fills the register files, so the CTAs do not co-reside and shrinking the grids to make them fit lost 30 %.)
   {
-    int nblk = (B + D2_WARPS - 1) / D2_WARPS;
+    // warps per sample: 4 while the SMs are mostly empty (latency mode), 1 once one warp per sample fills them
+    const int split = B <= 1024 ? 4 : (B <= 2048 ? 2 : 1);
+    const int spc = D2_WARPS / split;
+    int nblk = (B + spc - 1) / spc;
     int grid = nblk < sms * 2 ? nblk : sms * 2;
-    conv2_dgrad_kernel<<<grid, D2_THREADS, D2_SMEM, stream>>>(params, sc.da2, ws.a2, ws.idx2, ws.a1,
-                                                             drop_scale, sc.dp1, B);
+    if (split == 4) conv2_dgrad_kernel<4><<<grid, D2_THREADS, D2_SMEM, stream>>>(params, sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale, sc.dp1, B);
+    else if (split == 2) conv2_dgrad_kernel<2><<<grid, D2_THREADS, D2_SMEM, stream>>>(params, sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale, sc.dp1, B);
+    else conv2_dgrad_kernel<1><<<grid, D2_THREADS, D2_SMEM, stream>>>(params, sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale, sc.dp1, B);
   }
   prof_mark(6, stream);
   {
