@@ -2,6 +2,7 @@
 // queries and the elastic-state snapshot copies.
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace ddp {
@@ -18,6 +19,12 @@ void set_error(const char* fmt, ...) {
 int cuda_rc(cudaError_t e, const char* what) {
   set_error("%s: CUDA error %d: %s", what, int(e), cudaGetErrorString(e));
   return int(e) > 0 ? int(e) : DDP_EINVAL;
+}
+
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("DDP_NO_PDL"); v = (e && e[0] == '1') ? 0 : 1; }
+  return v == 1;
 }
 
 int sm_count() {

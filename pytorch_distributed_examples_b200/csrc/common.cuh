@@ -109,6 +109,29 @@ __device__ __forceinline__ void prefetch_l1_range(const float* base, int nfloats
     asm volatile("prefetch.global.L1 [%0];" :: "l"(base + i));
 }
 
+// ---- programmatic dependent launch (PDL) ---------------------------------------------------------------------------
+// The step is a chain of ~9 kernels, each with a prologue that only touches parameters and shared memory (weight
+// staging, barrier / TMEM set-up).  Launched with the programmatic-serialization attribute, kernel N+1 may start that
+// prologue while kernel N is still running; pdl_wait() (griddepcontrol.wait) then blocks until kernel N has completed
+// and its writes are visible.  RULE: nothing written by an earlier kernel of the step may be read, and nothing an
+// earlier kernel reads may be written, before pdl_wait().  pdl_trigger() lets the next kernel be scheduled as soon as
+// every CTA of this one has issued it.  Both are no-ops in a kernel launched the ordinary way.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+bool pdl_enabled();                      // api.cu: false when DDP_NO_PDL=1 (A/B switch for measurements)
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, bool pdl,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = (pdl && pdl_enabled()) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 // ---- mbarrier + bulk-copy (TMA engine, 1-D) helpers -----------------------------------------------------
 // cp.async.bulk moves a contiguous block global -> shared without touching registers and signals an
 // mbarrier with the byte count (complete_tx); one thread issues, everybody waits on the barrier.

@@ -134,7 +134,8 @@ conv2_fwd_tc_kernel(const float* __restrict__ params, const float* __restrict__ 
   float* noise_s = bias_s + 32;                                      // [2 buffers][G][20]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  if (offset_dev) offset += uint64_t(*offset_dev);
+  pdl_trigger();
+  if (offset_dev) offset += uint64_t(*offset_dev);   // the step counter is bumped by the update kernel, which precedes conv1_fwd
   TC_T0(t_kernel);
 
   // ---- one-time setup: weights -> B (hi, lo), barriers, TMEM ---------------------------------------
@@ -171,6 +172,7 @@ conv2_fwd_tc_kernel(const float* __restrict__ params, const float* __restrict__ 
   asm volatile("tcgen05.fence::before_thread_sync;");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;");
+  pdl_wait();                                  // a1 (conv1_fwd) is read from here on; everything above touched params + smem only
   const uint32_t tmem = *tmem_ptr;
   const int ngroups = (B + G - 1) / G;
   if (tid == 0) TC_ACC(0, t_kernel);   // slot 0: setup
@@ -363,8 +365,8 @@ int launch_conv2_fwd_tc(const float* params, const float* a1, const float* mask2
   const int ngroups = (B + tc2::G - 1) / tc2::G;
   const int sms = sm_count();
   const int grid = ngroups < sms ? ngroups : sms;
-  tc2::conv2_fwd_tc_kernel<<<grid, tc2::THREADS, tc2::SMEM_BYTES, stream>>>(params, a1, mask2d, seed, offset, offset_dev,
-                                                                         training, a2, idx2, B);
+  DDP_CUDA(launch_pdl(tc2::conv2_fwd_tc_kernel, dim3(grid), dim3(tc2::THREADS), tc2::SMEM_BYTES, stream, true,
+                      params, a1, mask2d, seed, offset, offset_dev, training, a2, idx2, B));
   return 0;
 }
 

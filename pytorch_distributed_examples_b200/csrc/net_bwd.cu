@@ -42,10 +42,14 @@ head_bwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
     const int tb0 = tile * HT;
     const int nv = min(HT, B - tb0);
     mbarrier_expect_tx(bar, uint32_t(nv) * (A2_PER * 4) + (with_w1 ? F1 * A2_PER * 4 : 0));
-    if (with_w1) bulk_copy_g2s(w1_s, params + OFF_F1W, F1 * A2_PER * 4, bar);
+    if (with_w1) {
+      bulk_copy_g2s(w1_s, params + OFF_F1W, F1 * A2_PER * 4, bar);   // parameters: fetched while the previous kernel drains
+      pdl_wait();
+    }
     for (int s = 0; s < nv; ++s)
       bulk_copy_g2s(a2_s + s * HB_A2S, a2 + size_t(tb0 + s) * A2_PER, A2_PER * 4, bar);
   };
+  pdl_trigger();
   if (tid == 0 && int(blockIdx.x) < ntiles_all) issue_tile(blockIdx.x, true);
   uint32_t phase = 0;
   for (int i = tid; i < NC * 52; i += HB_THREADS) {
@@ -63,6 +67,7 @@ head_bwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
   const int jgW = tid >> 5, igW = tid & 31;  // fc1 wgrad mapping
   const int sgD = tid / 40, igD = tid % 40;  // fc1 dgrad mapping
   const int ntiles = (B + HT - 1) / HT;
+  pdl_wait();                               // h, logp (head_fwd) are read and da2 / partials written only after this
   for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int b0 = tile * HT;
     const int nvalid = min(HT, B - b0);
@@ -226,12 +231,14 @@ conv2_dgrad_kernel(const float* __restrict__ params, const float* __restrict__ d
   const int slot = warp / S, part = warp % S;
   float* dy_s = smem + D2_WS + warp * D2_PER_WARP;  // [20][8][8], private to the warp
   float* out_s = dy_s;                              // [10][144]: written only after the last read of dy2
+  pdl_trigger();
   for (int i = tid; i < D2_WS; i += D2_THREADS) {
     int cc = i & 7, g = (i >> 3) & 1, ct = i >> 4;  // ct = co*25 + tap
     int co = ct / 25, tap = ct % 25;
     w_s[i] = cc < 5 ? params[OFF_C2W + co * 250 + (g * 5 + cc) * 25 + tap] : 0.f;
   }
   __syncthreads();
+  pdl_wait();                                       // da2 (head_bwd) is read from here on
   const int g = lane >> 4, tile = lane & 15, ty = tile >> 2, tx = tile & 3;
   // validity of patch rows/cols: dy2 row = 3*ty + r - 4 must be in [0,8)
   bool rok[7], cok[7];
@@ -356,6 +363,8 @@ conv2_wgrad_kernel(const float* __restrict__ da2, const float* __restrict__ a2,
   uint64_t* bar = reinterpret_cast<uint64_t*>(live_s + W2_NS * C2);   // [2]
   uint8_t* ridx = reinterpret_cast<uint8_t*>(bar + 2);   // [2][W2_NS*320] raw idx2
   const int tid = threadIdx.x;
+  pdl_trigger();
+  pdl_wait();                                            // no parameter prologue here: only the launch latency is hidden
   // cq (output-channel residue mod 5) is the SLOWEST index so that a warp is (almost) uniform in co
   // and the dead-channel skip below is (almost) divergence-free
   const int cq = tid / 50, kh = tid % 5, ci = (tid % 50) / 5;   // cq < 5 for tid < 250
@@ -487,6 +496,8 @@ conv1_wgrad_kernel(const float* __restrict__ dp1, const uint8_t* __restrict__ id
   uint64_t* bar = reinterpret_cast<uint64_t*>(rawf + 2 * W1_RAWF);   // [2]
   uint8_t* rawi = reinterpret_cast<uint8_t*>(bar + 2);       // [2 buffers][NS*1440] idx1
   const int tid = threadIdx.x;
+  pdl_trigger();
+  pdl_wait();
   const bool active = tid < W1_ACTIVE;
   const int sl = tid / 120, r = tid % 120, kh = r % 5, oy = r / 5;
   const int nstages = (B + W1_NS - 1) / W1_NS;
@@ -615,6 +626,8 @@ reduce_partials_kernel(const float* __restrict__ partials, int parts_c1, int par
                        int parts_head, float* __restrict__ bucket) {
   __shared__ float red[RP_WARPS][33];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_trigger();
+  pdl_wait();
   const int e = blockIdx.x * 32 + lane;
   float s = 0.f;
   if (e < P_ARENA && !arena_is_pad(e)) {
@@ -675,8 +688,8 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
   {
     int ntiles = (B + HT - 1) / HT;
     parts_head = ntiles < sms ? ntiles : sms;
-    head_bwd_kernel<<<parts_head, HB_THREADS, HB_SMEM, stream>>>(params, ws.a2, ws.h, logp, dlogp, target,
-                                                                 nll_coef, drop_scale, sc.da2, sc.partials, B);
+    DDP_CUDA(launch_pdl(head_bwd_kernel, dim3(parts_head), dim3(HB_THREADS), HB_SMEM, stream, true, params, ws.a2, ws.h, logp,
+                        dlogp, target, nll_coef, drop_scale, sc.da2, sc.partials, B));
   }
   prof_mark(5, stream);
   // (conv2_wgrad is independent of dgrad -> conv1_wgrad and was tried on a forked stream: each kernel already
@@ -687,28 +700,28 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
     const int spc = D2_WARPS / split;
     int nblk = (B + spc - 1) / spc;
     int grid = nblk < sms * 2 ? nblk : sms * 2;
-    if (split == 4) conv2_dgrad_kernel<4><<<grid, D2_THREADS, D2_SMEM, stream>>>(params, sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale, sc.dp1, B);
-    else if (split == 2) conv2_dgrad_kernel<2><<<grid, D2_THREADS, D2_SMEM, stream>>>(params, sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale, sc.dp1, B);
-    else conv2_dgrad_kernel<1><<<grid, D2_THREADS, D2_SMEM, stream>>>(params, sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale, sc.dp1, B);
+    if (split == 4) DDP_CUDA(launch_pdl(conv2_dgrad_kernel<4>, dim3(grid), dim3(D2_THREADS), D2_SMEM, stream, true, params, sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale, sc.dp1, B));
+    else if (split == 2) DDP_CUDA(launch_pdl(conv2_dgrad_kernel<2>, dim3(grid), dim3(D2_THREADS), D2_SMEM, stream, true, params, sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale, sc.dp1, B));
+    else DDP_CUDA(launch_pdl(conv2_dgrad_kernel<1>, dim3(grid), dim3(D2_THREADS), D2_SMEM, stream, true, params, sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale, sc.dp1, B));
   }
   prof_mark(6, stream);
   {
     int nstages = (B + W2_NS - 1) / W2_NS;
     parts_c2 = nstages < MAX_PARTS ? nstages : MAX_PARTS;
     if (parts_c2 > sms * 3) parts_c2 = sms * 3;      // 3 CTAs/SM: one stages while the others compute
-    conv2_wgrad_kernel<<<parts_c2, W2_THREADS, W2_SMEM, stream>>>(sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale,
-                                                           sc.partials, B);
+    DDP_CUDA(launch_pdl(conv2_wgrad_kernel, dim3(parts_c2), dim3(W2_THREADS), W2_SMEM, stream, true, sc.da2, ws.a2, ws.idx2, ws.a1,
+                        drop_scale, sc.partials, B));
   }
   prof_mark(7, stream);
   {
     const int nst1 = (B + W1_NS - 1) / W1_NS;
     parts_c1 = nst1 < sms * 2 ? nst1 : sms * 2;
     if (parts_c1 > MAX_PARTS) parts_c1 = MAX_PARTS;
-    conv1_wgrad_kernel<<<parts_c1, W1_THREADS, W1_SMEM, stream>>>(sc.dp1, ws.idx1, x, sc.partials, B);
+    DDP_CUDA(launch_pdl(conv1_wgrad_kernel, dim3(parts_c1), dim3(W1_THREADS), W1_SMEM, stream, true, sc.dp1, ws.idx1, x, sc.partials, B));
   }
   prof_mark(8, stream);
-  reduce_partials_kernel<<<(P_ARENA + 31) / 32, RP_WARPS * 32, 0, stream>>>(sc.partials, parts_c1, parts_c2,
-                                                                  parts_head, grad_bucket);
+  DDP_CUDA(launch_pdl(reduce_partials_kernel, dim3((P_ARENA + 31) / 32), dim3(RP_WARPS * 32), 0, stream, true, sc.partials, parts_c1,
+                      parts_c2, parts_head, grad_bucket));
   prof_mark(9, stream);
   DDP_CUDA(cudaGetLastError());
   return 0;

@@ -30,6 +30,7 @@ conv1_fwd_kernel(const float* __restrict__ params, const float* __restrict__ x,
   __shared__ __align__(128) float img_s[2][2 * IMG_PIX];   // double-buffered pair of images (bulk-copied)
   __shared__ __align__(8) uint64_t bar[2];
   const int tid = threadIdx.x;
+  pdl_trigger();                                           // conv2_fwd may start building its weight operand now
   const int npairs = (B + 1) >> 1;
   auto issue = [&](int pair, int buf) {                    // thread 0: prefetch a pair of images
     const int b0 = pair * 2;
@@ -139,10 +140,14 @@ head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
     const int b0 = tile * HT;
     const int nvalid = min(HT, B - b0);
     mbarrier_expect_tx(bar, uint32_t(nvalid) * (A2_PER * 4) + (with_w1 ? F1 * A2_PER * 4 : 0));
-    if (with_w1) bulk_copy_g2s(w1_s, params + OFF_F1W, F1 * A2_PER * 4, bar);
+    if (with_w1) {
+      bulk_copy_g2s(w1_s, params + OFF_F1W, F1 * A2_PER * 4, bar);   // parameters: may be fetched while conv2_fwd still runs
+      pdl_wait();                                                    // a2 is conv2_fwd's output
+    }
     for (int s = 0; s < nvalid; ++s)
       bulk_copy_g2s(a2_s + s * HF_A2S, a2 + size_t(b0 + s) * A2_PER, A2_PER * 4, bar);
   };
+  pdl_trigger();
   if (tid == 0 && blockIdx.x < ntiles) issue_tile(blockIdx.x, true);
   if (tid < 52) b1_s[tid] = tid < F1 ? params[OFF_F1B + tid] : 0.f;
   for (int i = tid; i < 50 * 12; i += HF_THREADS) {
@@ -158,6 +163,7 @@ head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
   float loss_acc = 0.f;                    // thread 0 only
   int corr_acc = 0;
   uint32_t phase = 0;
+  pdl_wait();                              // every thread: outputs (h, logp, loss partials) may only be written after this
   for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int b0 = tile * HT;
     const int nvalid = min(HT, B - b0);
@@ -344,9 +350,9 @@ extern "C" int ddp_net_forward(const float* params, const float* x, const int64_
       DDP_CUDA(cudaFuncSetAttribute(head_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HF_SMEM));
       attr_done = true;
     }
-    head_fwd_kernel<<<grid, HF_THREADS, HF_SMEM, stream>>>(
-        params, ws.a2, target, mask1d, seed, offset, offset_dev, training, ws.h, out_logp, out_loss, out_argmax,
-        reinterpret_cast<unsigned long long*>(out_correct), sc.loss_part, sc.counters, B);
+    DDP_CUDA(launch_pdl(head_fwd_kernel, dim3(grid), dim3(HF_THREADS), HF_SMEM, stream, true,
+                        params, ws.a2, target, mask1d, seed, offset, offset_dev, training, ws.h, out_logp, out_loss, out_argmax,
+                        reinterpret_cast<unsigned long long*>(out_correct), sc.loss_part, sc.counters, B));
   }
   prof_mark(3, stream);
   DDP_CUDA(cudaGetLastError());

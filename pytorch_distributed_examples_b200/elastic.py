@@ -30,6 +30,9 @@ from . import _native
 _PLAN_KEY = "ddp_step/elastic/plan"
 
 
+reset_latencies_ms = []   # wall time of every elastic reset seen by this process: interrupt -> new ring -> state synced
+
+
 def _hvd():
     from . import hvd
     return hvd
@@ -227,9 +230,15 @@ def run(func):
     def wrapper(state, *args, **kwargs):
         h = _hvd()
         skip_sync = False
+        t_interrupt = None
         while True:
             if not skip_sync:
                 state.sync()
+            if t_interrupt is not None:          # membership change -> ring re-formed -> state broadcast done
+                if torch.cuda.is_available():
+                    torch.cuda.synchronize()
+                reset_latencies_ms.append((time.perf_counter() - t_interrupt) * 1e3)
+                t_interrupt = None
             try:
                 return func(state, *args, **kwargs)
             except h.HorovodInternalError:
@@ -237,6 +246,7 @@ def run(func):
                 skip_sync = False
             except h.HostsUpdatedInterrupt as e:
                 skip_sync = e.skip_sync
+            t_interrupt = time.perf_counter()
             _reset(state)
             state.on_reset()
 

@@ -273,7 +273,9 @@ def main():
         same_on_all_ranks(model.flat_params, "elastic params")
         for a in opt._fused.arenas():
             same_on_all_ranks(a.float(), "elastic optimizer state")
-    log(f"elastic {W}->{len(half)}->{W} ok, reset sizes seen by rank 0: {events}")
+    lat = [round(v, 1) for v in hvd.elastic.reset_latencies_ms]
+    log(f"elastic {W}->{len(half)}->{W} ok, reset sizes seen by rank 0: {events}, re-formation latency (interrupt -> new NCCL ring -> "
+        f"state broadcast) ms: {lat}")
     dist.barrier()
     dist.destroy_process_group()
     if R == 0:
