@@ -30,7 +30,8 @@ conv1_fwd_kernel(const float* __restrict__ params, const float* __restrict__ x,
   __shared__ __align__(128) float img_s[2][2 * IMG_PIX];   // double-buffered pair of images (bulk-copied)
   __shared__ __align__(8) uint64_t bar[2];
   const int tid = threadIdx.x;
-  pdl_trigger();                                           // conv2_fwd may start building its weight operand now
+  pdl_wait();                                              // first kernel of the step: the optimizer update before it must be complete
+  pdl_trigger();                                           // ... and only then may conv2_fwd start building its weight operand
   const int npairs = (B + 1) >> 1;
   auto issue = [&](int pair, int buf) {                    // thread 0: prefetch a pair of images
     const int b0 = pair * 2;
@@ -334,7 +335,7 @@ extern "C" int ddp_net_forward(const float* params, const float* x, const int64_
   {
     int npairs = (B + 1) / 2;
     int grid = npairs < sms * 2 ? npairs : sms * 2;
-    conv1_fwd_kernel<<<grid, F1_THREADS, 0, stream>>>(params, x, ws.a1, ws.idx1, B);
+    DDP_CUDA(launch_pdl(conv1_fwd_kernel, dim3(grid), dim3(F1_THREADS), 0, stream, true, params, x, ws.a1, ws.idx1, B));
   }
   prof_mark(1, stream);
   if (int rc = launch_conv2_fwd_tc(params, ws.a1, mask2d, seed, offset, offset_dev, training, ws.a2, ws.idx2, B, stream))

@@ -21,6 +21,7 @@ fused_update_kernel(const GT* __restrict__ grad, float* __restrict__ params, flo
                     float* __restrict__ state2, int64_t n, UpdateConsts kc, int64_t step,
                     const int64_t* __restrict__ step_dev, float* __restrict__ grad_wb) {
   __shared__ UpdateConsts ks;
+  pdl_wait();                               // launched as a programmatic dependent of the gradient reduction
   if (threadIdx.x == 0) {
     UpdateConsts k = kc;
     int64_t st = step_dev ? (*step_dev + 1) : step;
@@ -108,11 +109,11 @@ static void launch_update(int grad_dtype, int grid, cudaStream_t stream, const v
                           float* s1, float* s2, int64_t n, const UpdateConsts& k, int64_t step,
                           const int64_t* step_dev, float* wb) {
   if (grad_dtype == 0)
-    fused_update_kernel<OPT, HAS1, HAS2, float><<<grid, 256, 0, stream>>>(
-        static_cast<const float*>(grad), params, s1, s2, n, k, step, step_dev, wb);
+    launch_pdl(fused_update_kernel<OPT, HAS1, HAS2, float>, dim3(grid), dim3(256), 0, stream, true,
+               static_cast<const float*>(grad), params, s1, s2, n, k, step, step_dev, wb);
   else
-    fused_update_kernel<OPT, HAS1, HAS2, __nv_bfloat16><<<grid, 256, 0, stream>>>(
-        static_cast<const __nv_bfloat16*>(grad), params, s1, s2, n, k, step, step_dev, wb);
+    launch_pdl(fused_update_kernel<OPT, HAS1, HAS2, __nv_bfloat16>, dim3(grid), dim3(256), 0, stream, true,
+               static_cast<const __nv_bfloat16*>(grad), params, s1, s2, n, k, step, step_dev, wb);
 }
 
 }  // namespace ddp
