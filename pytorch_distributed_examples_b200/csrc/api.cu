@@ -3,6 +3,7 @@
 #include <stdarg.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <mutex>
 #include "common.cuh"
 
 namespace ddp {
@@ -50,6 +51,33 @@ void prof_mark(int idx, cudaStream_t stream) {
     g_prof_made = true;
   }
   cudaEventRecord(g_prof_ev[idx], stream);
+}
+
+bool prof_enabled() { return g_prof_on; }
+
+// Side stream + event pairs for the small-batch fork in ddp_net_backward (conv2 weight gradient beside the data
+// gradient).  Library-owned, created on first use per device (outside any stream capture: the host layer runs eager
+// warm-up steps before it captures); a ring of event pairs under a mutex keeps record/wait pairs of concurrent callers apart.
+static std::mutex g_side_mu;
+static cudaStream_t g_side_stream[64] = {nullptr};
+static cudaEvent_t g_side_ev[64][8][2];
+static unsigned g_side_next[64] = {0};
+int side_fork(cudaStream_t main, cudaStream_t* side, cudaEvent_t* join) {
+  int dev = 0;
+  DDP_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) { set_error("side_fork: device index out of range"); return DDP_EINVAL; }
+  std::lock_guard<std::mutex> lock(g_side_mu);
+  if (!g_side_stream[dev]) {
+    DDP_CUDA(cudaStreamCreateWithFlags(&g_side_stream[dev], cudaStreamNonBlocking));
+    for (int i = 0; i < 8; ++i)
+      for (int j = 0; j < 2; ++j) DDP_CUDA(cudaEventCreateWithFlags(&g_side_ev[dev][i][j], cudaEventDisableTiming));
+  }
+  const unsigned slot = g_side_next[dev]++ & 7u;
+  DDP_CUDA(cudaEventRecord(g_side_ev[dev][slot][0], main));
+  DDP_CUDA(cudaStreamWaitEvent(g_side_stream[dev], g_side_ev[dev][slot][0], 0));
+  *side = g_side_stream[dev];
+  *join = g_side_ev[dev][slot][1];
+  return 0;
 }
 
 }  // namespace ddp

@@ -101,6 +101,10 @@ int launch_conv2_fwd_tc(const float* params, const float* a1, const float* mask2
                         const int64_t* offset_dev, int training, float* a2, uint8_t* idx2, int B, cudaStream_t stream);
 // per-kernel event timing (api.cu); mark(i) records event i on `stream` when profiling is on
 void prof_mark(int idx, cudaStream_t stream);
+bool prof_enabled();
+// fork: records an event on `main`, makes the library's side stream wait for it, returns the side stream and the
+// event the caller must record on it and wait for on `main` to join (api.cu)
+int side_fork(cudaStream_t main, cudaStream_t* side, cudaEvent_t* join);
 
 // Warm the SM's L1 with a read-only global array that every CTA on the SM will stream through
 // (fc1.weight, 64 KB): all lines are requested at once instead of being missed one loop iteration at a time.

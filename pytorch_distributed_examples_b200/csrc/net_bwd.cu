@@ -692,8 +692,29 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
                         dlogp, target, nll_coef, drop_scale, sc.da2, sc.partials, B));
   }
   prof_mark(5, stream);
-  // (conv2_wgrad is independent of dgrad -> conv1_wgrad and was tried on a forked stream: each kernel already
-  //  fills the register files, so the CTAs do not co-reside and shrinking the grids to make them fit lost 30 %.)
+  // conv2_wgrad depends on head_bwd only, not on dgrad -> conv1_wgrad.  At large batches every kernel fills the SMs
+  // by itself (forking was tried there: the CTAs do not co-reside, and shrinking the grids to make them fit lost 30 %),
+  // but up to B = 1024 the machine is mostly empty and the step is a latency chain: there conv2_wgrad runs on the
+  // library's side stream beside dgrad and joins before the reduction (captured as a fork/join in a CUDA graph).
+  const bool fork = B <= 1024 && !prof_enabled();
+  cudaStream_t wstream = stream;
+  cudaEvent_t join_ev = nullptr;
+  if (fork)
+    if (int rc = side_fork(stream, &wstream, &join_ev)) return rc;
+  {
+    int nstages = (B + W2_NS - 1) / W2_NS;
+    parts_c2 = nstages < MAX_PARTS ? nstages : MAX_PARTS;
+    if (parts_c2 > sms * 3) parts_c2 = sms * 3;      // 3 CTAs/SM: one stages while the others compute
+  }
+  auto launch_wgrad2 = [&]() -> int {
+    DDP_CUDA(launch_pdl(conv2_wgrad_kernel, dim3(parts_c2), dim3(W2_THREADS), W2_SMEM, wstream, !fork, sc.da2, ws.a2, ws.idx2, ws.a1,
+                        drop_scale, sc.partials, B));
+    return 0;
+  };
+  if (fork) {
+    if (int rc = launch_wgrad2()) return rc;
+    DDP_CUDA(cudaEventRecord(join_ev, wstream));
+  }
   {
     // warps per sample: 4 while the SMs are mostly empty (latency mode), 1 once one warp per sample fills them
     const int split = B <= 1024 ? 4 : (B <= 2048 ? 2 : 1);
@@ -705,13 +726,8 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
     else DDP_CUDA(launch_pdl(conv2_dgrad_kernel<1>, dim3(grid), dim3(D2_THREADS), D2_SMEM, stream, true, params, sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale, sc.dp1, B));
   }
   prof_mark(6, stream);
-  {
-    int nstages = (B + W2_NS - 1) / W2_NS;
-    parts_c2 = nstages < MAX_PARTS ? nstages : MAX_PARTS;
-    if (parts_c2 > sms * 3) parts_c2 = sms * 3;      // 3 CTAs/SM: one stages while the others compute
-    DDP_CUDA(launch_pdl(conv2_wgrad_kernel, dim3(parts_c2), dim3(W2_THREADS), W2_SMEM, stream, true, sc.da2, ws.a2, ws.idx2, ws.a1,
-                        drop_scale, sc.partials, B));
-  }
+  if (!fork)
+    if (int rc = launch_wgrad2()) return rc;
   prof_mark(7, stream);
   {
     const int nst1 = (B + W1_NS - 1) / W1_NS;
@@ -720,6 +736,7 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
     DDP_CUDA(launch_pdl(conv1_wgrad_kernel, dim3(parts_c1), dim3(W1_THREADS), W1_SMEM, stream, true, sc.dp1, ws.idx1, x, sc.partials, B));
   }
   prof_mark(8, stream);
+  if (fork) DDP_CUDA(cudaStreamWaitEvent(stream, join_ev, 0));
   DDP_CUDA(launch_pdl(reduce_partials_kernel, dim3((P_ARENA + 31) / 32), dim3(RP_WARPS * 32), 0, stream, true, sc.partials, parts_c1,
                       parts_c2, parts_head, grad_bucket));
   prof_mark(9, stream);
