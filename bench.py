@@ -327,16 +327,20 @@ def main():
         extra["synth_batch_65536"] = {"GB/s": 65536 * 3144 / t / 1e9, "frac_hbm": 65536 * 3144 / t / 1e9 / peaks["hbm"], "us": t * 1e6}
         # the DDP script's own model: native tensor-core MLP step vs torch/cuBLAS strict fp32, same GPU
         try:
-            from oracle import mlp_oracle   # parameter initialisation only (reference constructor order)
             Bm = 4096
             xm, ym = ds.batch(base_index=0, count=Bm)
             xm = xm.reshape(Bm, -1).contiguous()
             torch.manual_seed(0)
-            sdm = mlp_oracle.OracleMLP(5, 1024).state_dict()
-            mlp = pkg.Model(5, 1024); mlp.load_state_dict(sdm); mlp = mlp.cuda()
+            mlp = pkg.Model(5, 1024).cuda()
             t_nat = timed(lambda: mlp.loss_and_grads(xm, ym), reps=10)
-            torch.backends.cuda.matmul.allow_tf32 = False
-            tm = mlp_oracle.OracleMLP(5, 1024); tm.load_state_dict(sdm); tm = tm.cuda()
+            torch.backends.cuda.matmul.allow_tf32 = False      # the reference's arithmetic: strict fp32 matmuls
+            layers = [torch.nn.Linear(784, 1024), torch.nn.ReLU()]
+            for _ in range(5):
+                layers += [torch.nn.Linear(1024, 1024), torch.nn.ReLU()]
+            tm = torch.nn.Sequential(*layers, torch.nn.Linear(1024, 10)).cuda()
+            with torch.no_grad():
+                for dst, src in zip(tm.parameters(), mlp.parameters()):
+                    dst.copy_(src)
             def torch_fb():
                 tm.zero_grad(set_to_none=True)
                 torch.nn.functional.cross_entropy(tm(xm), ym).backward()
