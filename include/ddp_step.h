@@ -87,7 +87,15 @@ int ddp_net_forward(const float* params, const float* x, const int64_t* target,
  * uses the F.nll_loss(mean) gradient  dlogp[b,c] = -loss_scale/B * [c==target[b]].
  * Writes all 8 gradients into grad_bucket[DDP_NET_ARENA_ELEMS] (overwrite, so
  * optimizer.zero_grad() — ref :60 — costs nothing).  Deterministic: per-CTA
- * partial sums in scratch, reduced in fixed order; no float atomics.           */
+ * partial sums in scratch, reduced in fixed order; no float atomics.
+ * Launch structure: the kernels are chained with programmatic dependent launch
+ * (environment DDP_NO_PDL=1 turns that off).  For batch <= 1024 the conv2 weight
+ * gradient is enqueued on a side stream owned by the library (one per device,
+ * created on the first such call made outside a stream capture — until then the
+ * kernels simply run one after the other; captured calls record the fork/join
+ * in the graph); all
+ * work is ordered after `stream` at entry and `stream` waits for it before the
+ * final reduction, so the caller sees ordinary stream semantics.              */
 int ddp_net_backward(const float* params, const float* x, const float* logp,
                      const float* dlogp, const int64_t* target, float loss_scale,
                      int training, int64_t batch, const void* workspace,

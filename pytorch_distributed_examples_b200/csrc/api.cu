@@ -68,6 +68,9 @@ int side_fork(cudaStream_t main, cudaStream_t* side, cudaEvent_t* join) {
   if (dev < 0 || dev >= 64) { set_error("side_fork: device index out of range"); return DDP_EINVAL; }
   std::lock_guard<std::mutex> lock(g_side_mu);
   if (!g_side_stream[dev]) {
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    DDP_CUDA(cudaStreamIsCapturing(main, &cap));
+    if (cap != cudaStreamCaptureStatusNone) { *side = nullptr; *join = nullptr; return 0; }   // cannot create resources now: stay serial
     DDP_CUDA(cudaStreamCreateWithFlags(&g_side_stream[dev], cudaStreamNonBlocking));
     for (int i = 0; i < 8; ++i)
       for (int j = 0; j < 2; ++j) DDP_CUDA(cudaEventCreateWithFlags(&g_side_ev[dev][i][j], cudaEventDisableTiming));

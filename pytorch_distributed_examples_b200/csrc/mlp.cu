@@ -94,6 +94,8 @@ __device__ __forceinline__ float tf32_rna(float v) {
 __global__ void __launch_bounds__(256)
 split_kernel(const float* __restrict__ src, int rows, int cols, float* __restrict__ hi, float* __restrict__ lo,
              float* __restrict__ hiT, float* __restrict__ loT) {
+  pdl_trigger();
+  pdl_wait();                                   // nothing of the step is touched before the previous kernel is complete
   __shared__ float th[32][33], tl[32][33];
   const int tx = threadIdx.x, ty = threadIdx.y;
   const int c = blockIdx.x * 32 + tx;
@@ -122,7 +124,7 @@ split_kernel(const float* __restrict__ src, int rows, int cols, float* __restric
 }
 static void launch_split(const float* src, int rows, int cols, const Planes& p, bool transposed, cudaStream_t st) {
   dim3 grid((cols + 31) / 32, (rows + 31) / 32), block(32, 8);
-  split_kernel<<<grid, block, 0, st>>>(src, rows, cols, p.hi, p.lo, transposed ? p.hiT : nullptr, transposed ? p.loT : nullptr);
+  launch_pdl(split_kernel, dim3(grid), dim3(block), 0, st, true, src, rows, cols, p.hi, p.lo, transposed ? p.hiT : nullptr, transposed ? p.loT : nullptr);
 }
 
 // ---- classifier forward: one warp per HEAD_SPW samples (the classifier rows are loaded once for all of them) -----
@@ -131,6 +133,8 @@ __global__ void __launch_bounds__(256)
 head_fwd_kernel(const float* __restrict__ xh, const float* __restrict__ xl, const float* __restrict__ w, const float* __restrict__ bias,
                 const int64_t* __restrict__ target, int B, int F, int out, float* __restrict__ logits_ws,
                 float* __restrict__ out_logits, float* __restrict__ loss_part) {
+  pdl_trigger();
+  pdl_wait();                                   // nothing of the step is touched before the previous kernel is complete
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   const int b0 = warp * HEAD_SPW;
   if (b0 >= B) return;
@@ -185,6 +189,8 @@ head_fwd_kernel(const float* __restrict__ xh, const float* __restrict__ xl, cons
 // mean of loss_part in a fixed order (one block)
 __global__ void __launch_bounds__(1024)
 loss_mean_kernel(const float* __restrict__ part, int B, float* __restrict__ out) {
+  pdl_trigger();
+  pdl_wait();                                   // nothing of the step is touched before the previous kernel is complete
   __shared__ float s[1024];
   float a = 0.f;
   for (int i = threadIdx.x; i < B; i += 1024) a += part[i];
@@ -202,6 +208,8 @@ loss_mean_kernel(const float* __restrict__ part, int B, float* __restrict__ out)
 __global__ void __launch_bounds__(256)
 head_dz_kernel(const float* __restrict__ logits_ws, const int64_t* __restrict__ target, const float* __restrict__ dlogits,
                float scale, int B, int out, float* __restrict__ dz) {
+  pdl_trigger();
+  pdl_wait();                                   // nothing of the step is touched before the previous kernel is complete
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
   float v[MAXC];
@@ -228,6 +236,8 @@ head_dz_kernel(const float* __restrict__ logits_ws, const int64_t* __restrict__ 
 __global__ void __launch_bounds__(256)
 head_dx_kernel(const float* __restrict__ dz, const float* __restrict__ w, const float* __restrict__ xh, int B, int F, int out,
                float* __restrict__ hi, float* __restrict__ lo) {
+  pdl_trigger();
+  pdl_wait();                                   // nothing of the step is touched before the previous kernel is complete
   __shared__ float dzs[32][MAXC];
   const int tx = threadIdx.x, ty = threadIdx.y, t = ty * 32 + tx;
   const int b0 = blockIdx.y * 32, k = blockIdx.x * 32 + tx;
@@ -256,6 +266,8 @@ head_dx_kernel(const float* __restrict__ dz, const float* __restrict__ w, const 
 __global__ void __launch_bounds__(128)
 head_dw_partial_kernel(const float* __restrict__ dz, const float* __restrict__ xh, const float* __restrict__ xl, int B, int F, int out,
                        float* __restrict__ part) {
+  pdl_trigger();
+  pdl_wait();                                   // nothing of the step is touched before the previous kernel is complete
   __shared__ float dzs[HEAD_CHUNK][MAXC];
   const int k = blockIdx.x * 128 + threadIdx.x, b0 = blockIdx.y * HEAD_CHUNK;
   for (int i = threadIdx.x; i < HEAD_CHUNK * MAXC; i += 128) {
@@ -281,6 +293,8 @@ head_dw_partial_kernel(const float* __restrict__ dz, const float* __restrict__ x
 }
 __global__ void __launch_bounds__(256)
 head_dw_reduce_kernel(const float* __restrict__ part, int chunks, int n /* out*F */, float* __restrict__ dw) {
+  pdl_trigger();
+  pdl_wait();                                   // nothing of the step is touched before the previous kernel is complete
   const int i = blockIdx.x * 256 + threadIdx.x;
   if (i >= n) return;
   float a = 0.f;
@@ -290,6 +304,8 @@ head_dw_reduce_kernel(const float* __restrict__ part, int chunks, int n /* out*F
 // db[c] = sum_b dz[b][c]  (one block, fixed order)
 __global__ void __launch_bounds__(1024)
 head_db_kernel(const float* __restrict__ dz, int B, int out, float* __restrict__ db) {
+  pdl_trigger();
+  pdl_wait();                                   // nothing of the step is touched before the previous kernel is complete
   __shared__ float s[1024];
   const int c = threadIdx.x % MAXC, lane_b = threadIdx.x / MAXC;        // 64 sample lanes x 16 classes
   float a = 0.f;
@@ -310,6 +326,8 @@ constexpr int BIAS_RC = 16;
 struct BiasGradArgs { const float* dh[MAX_PROBLEMS]; const float* dl[MAX_PROBLEMS]; float* db[MAX_PROBLEMS]; };
 __global__ void __launch_bounds__(256)
 bias_grad_partial_kernel(BiasGradArgs args, int F, int B, float* __restrict__ part) {
+  pdl_trigger();
+  pdl_wait();                                   // nothing of the step is touched before the previous kernel is complete
   __shared__ float4 s[8][32];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n = blockIdx.x * 128 + lane * 4;
@@ -337,6 +355,8 @@ bias_grad_partial_kernel(BiasGradArgs args, int F, int B, float* __restrict__ pa
 }
 __global__ void __launch_bounds__(256)
 bias_grad_reduce_kernel(BiasGradArgs args, int F, int layers, const float* __restrict__ part) {
+  pdl_trigger();
+  pdl_wait();                                   // nothing of the step is touched before the previous kernel is complete
   const int n = blockIdx.x * 256 + threadIdx.x;
   if (n >= F) return;
   float t = 0.f;
@@ -349,6 +369,8 @@ bias_grad_reduce_kernel(BiasGradArgs args, int F, int layers, const float* __res
 struct SplitArgs { const float* src[MAX_PROBLEMS]; float* hi[MAX_PROBLEMS]; float* lo[MAX_PROBLEMS]; int64_t n[MAX_PROBLEMS]; };
 __global__ void __launch_bounds__(256)
 split_flat_kernel(SplitArgs args) {
+  pdl_trigger();
+  pdl_wait();                                   // nothing of the step is touched before the previous kernel is complete
   const int64_t n4 = args.n[blockIdx.z] >> 2;                  // every tensor is a multiple of 4 floats (F % 4 == in % 4 == 0)
   const float4* src = reinterpret_cast<const float4*>(args.src[blockIdx.z]);
   float4* hi = reinterpret_cast<float4*>(args.hi[blockIdx.z]);
@@ -416,10 +438,10 @@ extern "C" int ddp_mlp_forward(const ddp_mlp_shape_t* shape, const float* params
       sa.src[l] = params + L.w[l]; sa.hi[l] = w.W[l].hi; sa.lo[l] = w.W[l].lo;
       sa.n[l] = int64_t(s.F) * (l == 0 ? s.in : s.F);
     }
-    split_flat_kernel<<<dim3(128, 1, s.G), 256, 0, st>>>(sa);
+    launch_pdl(split_flat_kernel, dim3(dim3(128, 1, s.G)), dim3(256), 0, st, true, sa);
     SplitArgs sx{};
     sx.src[0] = x; sx.hi[0] = w.X[0].hi; sx.lo[0] = w.X[0].lo; sx.n[0] = int64_t(B) * s.in;
-    split_flat_kernel<<<dim3(256, 1, 1), 256, 0, st>>>(sx);
+    launch_pdl(split_flat_kernel, dim3(dim3(256, 1, 1)), dim3(256), 0, st, true, sx);
   }
   DDP_CUDA(cudaGetLastError());
   for (int l = 0; l < s.G; ++l) {
@@ -434,9 +456,9 @@ extern "C" int ddp_mlp_forward(const ddp_mlp_shape_t* shape, const float* params
     if (int rc = launch_gemm(gb, EPI_BIAS_RELU_SPLIT, false, false, st)) return rc;
   }
   const int spb = 8 * HEAD_SPW;                               // samples per 256-thread block
-  head_fwd_kernel<<<(B + spb - 1) / spb, 256, 0, st>>>(w.X[s.G].hi, w.X[s.G].lo, params + L.w[s.G], params + L.b[s.G], target, B, s.F,
+  launch_pdl(head_fwd_kernel, dim3((B + spb - 1) / spb), dim3(256), 0, st, true, w.X[s.G].hi, w.X[s.G].lo, params + L.w[s.G], params + L.b[s.G], target, B, s.F,
                                                          s.out, w.logits, out_logits, out_loss ? w.loss_part : nullptr);
-  if (out_loss) loss_mean_kernel<<<1, 1024, 0, st>>>(w.loss_part, B, out_loss);
+  if (out_loss) launch_pdl(loss_mean_kernel, dim3(1), dim3(1024), 0, st, true, w.loss_part, B, out_loss);
   DDP_CUDA(cudaGetLastError());
   return 0;
 }
@@ -457,13 +479,13 @@ extern "C" int ddp_mlp_backward(const ddp_mlp_shape_t* shape, const float* param
   const ParamLayout L = param_layout(s);
   const int G = s.G;
   // classifier
-  head_dz_kernel<<<(B + 255) / 256, 256, 0, st>>>(w.logits, target, dlogits, loss_scale, B, s.out, w.dz);
-  head_dx_kernel<<<dim3((s.F + 31) / 32, (B + 31) / 32), dim3(32, 8), 0, st>>>(w.dz, params + L.w[G], w.X[G].hi, B, s.F, s.out,
+  launch_pdl(head_dz_kernel, dim3((B + 255) / 256), dim3(256), 0, st, true, w.logits, target, dlogits, loss_scale, B, s.out, w.dz);
+  launch_pdl(head_dx_kernel, dim3(dim3((s.F + 31) / 32, (B + 31) / 32)), dim3(dim3(32, 8)), 0, st, true, w.dz, params + L.w[G], w.X[G].hi, B, s.F, s.out,
                                                                               w.D[G].hi, w.D[G].lo);
   const int chunks = (B + HEAD_CHUNK - 1) / HEAD_CHUNK;
-  head_dw_partial_kernel<<<dim3((s.F + 127) / 128, chunks), 128, 0, st>>>(w.dz, w.X[G].hi, w.X[G].lo, B, s.F, s.out, w.head_part);
-  head_dw_reduce_kernel<<<(s.out * s.F + 255) / 256, 256, 0, st>>>(w.head_part, chunks, s.out * s.F, grad_bucket + L.w[G]);
-  head_db_kernel<<<1, 1024, 0, st>>>(w.dz, B, s.out, grad_bucket + L.b[G]);
+  launch_pdl(head_dw_partial_kernel, dim3(dim3((s.F + 127) / 128, chunks)), dim3(128), 0, st, true, w.dz, w.X[G].hi, w.X[G].lo, B, s.F, s.out, w.head_part);
+  launch_pdl(head_dw_reduce_kernel, dim3((s.out * s.F + 255) / 256), dim3(256), 0, st, true, w.head_part, chunks, s.out * s.F, grad_bucket + L.w[G]);
+  launch_pdl(head_db_kernel, dim3(1), dim3(1024), 0, st, true, w.dz, B, s.out, grad_bucket + L.b[G]);
   DDP_CUDA(cudaGetLastError());
   // data gradients through the wide layers
   for (int l = G - 1; l >= 1; --l) {
@@ -495,8 +517,8 @@ extern "C" int ddp_mlp_backward(const ddp_mlp_shape_t* shape, const float* param
     BiasGradArgs ba{};
     for (int l = 0; l < G; ++l) { ba.dh[l] = w.D[l + 1].hi; ba.dl[l] = w.D[l + 1].lo; ba.db[l] = grad_bucket + L.b[l]; }
     static_assert(BIAS_RC == 16, "carve() reserves 16 row chunks");
-    bias_grad_partial_kernel<<<dim3((s.F + 127) / 128, G, BIAS_RC), 256, 0, st>>>(ba, s.F, B, w.bias_part);
-    bias_grad_reduce_kernel<<<dim3((s.F + 255) / 256, G), 256, 0, st>>>(ba, s.F, G, w.bias_part);
+    launch_pdl(bias_grad_partial_kernel, dim3(dim3((s.F + 127) / 128, G, BIAS_RC)), dim3(256), 0, st, true, ba, s.F, B, w.bias_part);
+    launch_pdl(bias_grad_reduce_kernel, dim3(dim3((s.F + 255) / 256, G)), dim3(256), 0, st, true, ba, s.F, G, w.bias_part);
   }
   DDP_CUDA(cudaGetLastError());
   return 0;

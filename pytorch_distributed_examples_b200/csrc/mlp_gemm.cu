@@ -162,6 +162,7 @@ gemm3x_kernel(const __grid_constant__ GemmBatch batch) {
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gen_ring + C::STAGES * C::STAGE_BYTES + 2 * C::STORE_BYTES + 8 * (2 * C::STAGES + 4));
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  pdl_trigger();
   MT_T0(t_kernel);
   MT_LOCALS;
   if (tid == 0) {
@@ -176,6 +177,7 @@ gemm3x_kernel(const __grid_constant__ GemmBatch batch) {
   asm volatile("tcgen05.fence::before_thread_sync;");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;");
+  pdl_wait();                                  // barriers, TMEM and the tensor maps are set up; operands come from earlier kernels
   const uint32_t tmem = *tmem_slot;
   const int total = batch.tile_start[batch.count];
 
@@ -445,7 +447,7 @@ static int launch_one(const GemmBatch& batch, cudaStream_t stream) {
   const int total = batch.tile_start[batch.count];
   const int sms = sm_count();
   const int grid = total < sms ? total : sms;
-  gemm3x_kernel<BN, EPI, AMN, BMN><<<grid, THREADS, Cfg<BN>::SMEM, stream>>>(batch);
+  DDP_CUDA(launch_pdl(gemm3x_kernel<BN, EPI, AMN, BMN>, dim3(grid), dim3(THREADS), Cfg<BN>::SMEM, stream, true, batch));
   DDP_CUDA(cudaGetLastError());
   return 0;
 }

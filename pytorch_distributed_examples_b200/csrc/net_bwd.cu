@@ -696,11 +696,13 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
   // by itself (forking was tried there: the CTAs do not co-reside, and shrinking the grids to make them fit lost 30 %),
   // but up to B = 1024 the machine is mostly empty and the step is a latency chain: there conv2_wgrad runs on the
   // library's side stream beside dgrad and joins before the reduction (captured as a fork/join in a CUDA graph).
-  const bool fork = B <= 1024 && !prof_enabled();
+  bool fork = B <= 1024 && !prof_enabled();
   cudaStream_t wstream = stream;
   cudaEvent_t join_ev = nullptr;
-  if (fork)
+  if (fork) {
     if (int rc = side_fork(stream, &wstream, &join_ev)) return rc;
+    if (!wstream) { fork = false; wstream = stream; }   // first call is inside a stream capture: no side stream yet
+  }
   {
     int nstages = (B + W2_NS - 1) / W2_NS;
     parts_c2 = nstages < MAX_PARTS ? nstages : MAX_PARTS;
