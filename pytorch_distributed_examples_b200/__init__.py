@@ -10,6 +10,7 @@ Drop-in surface:
     hvd                      horovod.torch-compatible module              (hvd.py, elastic.py)
     allreduce_hook / HookState   DDP register_comm_hook seam              (ddp_hook.py)
     save_snapshot / load_snapshot  snapshot.pt interchange                (snapshot.py)
+    evaluate                 Trainer.test / test(): fused count, all ranks  (evaluate.py)
 plus TrainStep (the graph-captured fast path), FusedOptimizer, SyntheticMNIST / DeviceLoader.
 """
 from . import _native  # noqa: F401
@@ -20,10 +21,11 @@ from .optim import FusedOptimizer, FusedUpdater
 from .data import SyntheticMNIST, DeviceLoader
 from .step import TrainStep
 from .snapshot import save_snapshot, load_snapshot
+from .evaluate import evaluate
 from .ddp_hook import HookState, allreduce_hook, FusedUpdateHook
 from . import hvd
 from . import elastic
 
 __all__ = ["Net", "Model", "DistributedSampler", "FusedOptimizer", "FusedUpdater", "SyntheticMNIST", "DeviceLoader",
-           "TrainStep", "save_snapshot", "load_snapshot", "HookState", "allreduce_hook", "FusedUpdateHook",
+           "TrainStep", "save_snapshot", "load_snapshot", "evaluate", "HookState", "allreduce_hook", "FusedUpdateHook",
            "hvd", "elastic"]

@@ -212,6 +212,18 @@ def main():
     same_on_all_ranks(mm.flat_params, "native MLP under DDP")
     log("native MLP (tensor-core GEMMs) under DDP == oracle W-rank Adam loop ok")
 
+    # 3c. evaluation over the sharded test set: every rank reports the GLOBAL (correct, total)
+    tds = pkg.SyntheticMNIST(length=10000, seed=9)
+    tsampler = pkg.DistributedSampler(tds, num_replicas=W, rank=R, shuffle=False)
+    enet = pkg.Net().cuda()
+    hvd.broadcast_parameters(enet.state_dict(), root_rank=0)
+    local_c, local_t, _ = pkg.evaluate(enet, pkg.DeviceLoader(tds, 128, tsampler))
+    glob_c, glob_t, glob_acc = pkg.evaluate(enet, pkg.DeviceLoader(tds, 128, tsampler), communicator=c)
+    tot = torch.tensor([local_c, local_t], dtype=torch.int64, device="cuda")
+    dist.all_reduce(tot)
+    assert [glob_c, glob_t] == tot.tolist() and glob_t == len(tsampler) * W, (glob_c, glob_t, tot.tolist())
+    log(f"evaluate over {W} shards ok: {glob_c}/{glob_t} = {glob_acc:.4f}")
+
     # 4. TrainStep (allreduce captured in the CUDA graph) == module path
     def run_steps(mode):
         torch.manual_seed(21)

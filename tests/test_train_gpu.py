@@ -214,3 +214,32 @@ def test_pipelined_host_loop_equals_direct_steps(native):
     piped.append(step_b.read_loss(prev))
     assert piped == direct
     assert torch.equal(model_a.flat_params, model_b.flat_params)
+
+
+def test_evaluate_matches_reference_test_loop(native):
+    """pkg.evaluate == the reference's Trainer.test / test() counting loop (ref: mnist_ddp_elastic.py:117-130;
+    horovod_mnist_elastic.py:85-102), run here on the oracle in eval mode: same correct count, same total."""
+    import pytorch_distributed_examples_b200 as pkg
+    from oracle import mlp_oracle
+    torch.manual_seed(13)
+    onet = net_oracle.OracleNet(); onet.eval()
+    xn, yn = synth_oracle.synth_batch(99, np.arange(3 * 128 + 40))
+    x, y = torch.from_numpy(xn), torch.from_numpy(yn)
+    batches = [(x[i:i + 128], y[i:i + 128]) for i in range(0, x.shape[0], 128)]          # ragged last batch, like N % 128
+    with torch.no_grad():
+        ref_correct = sum(int((onet(bx).max(1)[1] == by).sum()) for bx, by in batches)
+    model = pkg.Net(); model.load_state_dict(onet.state_dict()); model = model.cuda().train()
+    correct, total, acc = pkg.evaluate(model, [(bx.cuda(), by.cuda()) for bx, by in batches])
+    assert (correct, total) == (ref_correct, x.shape[0]) and abs(acc - ref_correct / x.shape[0]) < 1e-12
+    assert model.training, "evaluate must restore the training flag"
+    # the MLP: argmax of the logits (batches must be multiples of 4 for the tensor-core path)
+    omlp = mlp_oracle.OracleMLP(1, 128); omlp.eval()
+    mb = [(x[i:i + 128], y[i:i + 128]) for i in range(0, 384, 128)]
+    with torch.no_grad():
+        lg = [omlp(bx) for bx, _ in mb]
+    mlp = pkg.Model(1, 128); mlp.load_state_dict(omlp.state_dict()); mlp = mlp.cuda()
+    correct_m, total_m, _ = pkg.evaluate(mlp, [(bx.cuda(), by.cuda()) for bx, by in mb])
+    top2 = torch.cat(lg).topk(2, 1).values
+    undecided = int(((top2[:, 0] - top2[:, 1]) < 1e-5).sum())                              # ties within rounding may go either way
+    ref_m = sum(int((l.max(1)[1] == by).sum()) for l, (_, by) in zip(lg, mb))
+    assert total_m == 384 and abs(correct_m - ref_m) <= undecided
