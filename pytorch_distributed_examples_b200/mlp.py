@@ -8,9 +8,10 @@ so the reference loop body (ref :70-75)
 runs unchanged, under stock DDP as well (the gradients appear in ``p.grad`` like any module's).
 On a CUDA device the parameters are views of one flat fp32 arena (ddp_mlp_param_layout) and the backward
 kernels write the gradients into a flat bucket of the same layout.  The wide layers are 3xTF32 tensor-core GEMMs
-(csrc/mlp_gemm.cu), fp32-accurate.  The batch must be a multiple of 4 (the weight-gradient GEMM's K is the
-batch and TMA rows are 16-byte aligned).  No CPU implementation: calling it with CPU tensors raises.
-``loss_and_grads`` is the fused path: cross-entropy and its gradient computed by the head kernels.
+(csrc/mlp_gemm.cu), fp32-accurate.  The kernels want a batch that is a multiple of 4 (the weight-gradient GEMM's K is
+the batch and TMA rows are 16-byte aligned): ``model(x)`` pads a ragged last batch with zero rows, which is exact
+(zero rows add nothing to any gradient); ``loss_and_grads`` — the fused path, cross-entropy and its gradient
+computed by the head kernels — insists on a multiple of 4.  No CPU implementation: CPU tensors raise.
 """
 import torch
 import torch.nn as nn
@@ -18,17 +19,28 @@ import torch.nn as nn
 from . import _native
 
 
+def _pad_rows(t: torch.Tensor, rows: int) -> torch.Tensor:
+    """t with zero rows appended up to ``rows``.  A zero input row / zero dlogits row contributes nothing to any weight
+    or bias gradient, so padding a ragged last batch (ref DataLoader, drop_last=False) to the GEMM's granule is exact."""
+    if t.shape[0] == rows:
+        return t
+    out = torch.zeros(rows, t.shape[1], dtype=t.dtype, device=t.device)
+    out[:t.shape[0]].copy_(t)
+    return out
+
+
 class _MLPFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, net, *params):
         nat = _native.get()
         batch = x.shape[0]
-        logits = torch.empty(batch, net._shape.out_features, dtype=torch.float32, device=x.device)
-        ws = net._get_workspace(batch)
-        nat.mlp_forward(net._shape, net._arena, x, None, ws, out_logits=logits)
-        ctx.net, ctx.batch = net, batch
+        padded = -(-batch // 4) * 4
+        logits = torch.empty(padded, net._shape.out_features, dtype=torch.float32, device=x.device)
+        ws = net._get_workspace(padded)
+        nat.mlp_forward(net._shape, net._arena, _pad_rows(x, padded), None, ws, out_logits=logits)
+        ctx.net, ctx.batch, ctx.padded = net, batch, padded
         ctx.ws_version = net._ws_version = net._ws_version + 1
-        return logits
+        return logits[:batch]
 
     @staticmethod
     def backward(ctx, dlogits):
@@ -39,7 +51,8 @@ class _MLPFunction(torch.autograd.Function):
                                "(two forwards before a backward are not supported)")
         fresh = all(p.grad is None for p in net._param_list)
         bucket = net._grad_arena if fresh else torch.empty_like(net._grad_arena)
-        nat.mlp_backward(net._shape, net._arena, dlogits.contiguous(), None, 1.0, ctx.batch, net._workspace, bucket)
+        nat.mlp_backward(net._shape, net._arena, _pad_rows(dlogits.contiguous(), ctx.padded), None, 1.0, ctx.padded,
+                         net._workspace, bucket)
         grads = [bucket[o:o + n].view(p.shape) for p, (o, n) in zip(net._param_list, net._layout)]
         return (None, None, *grads)
 
@@ -121,10 +134,12 @@ class Model(nn.Module):
             raise RuntimeError("Model.forward needs a CUDA tensor (no CPU fallback)")
         x = x.reshape(x.size(0), -1).to(torch.float32).contiguous()          # ref :151 x.view(x.size(0), -1)
         if not torch.is_grad_enabled():
-            logits = torch.empty(x.shape[0], 10, dtype=torch.float32, device=x.device)
-            _native.get().mlp_forward(self._shape, self._arena, x, None, self._get_workspace(x.shape[0]), out_logits=logits)
+            batch, padded = x.shape[0], -(-x.shape[0] // 4) * 4
+            logits = torch.empty(padded, 10, dtype=torch.float32, device=x.device)
+            _native.get().mlp_forward(self._shape, self._arena, _pad_rows(x, padded), None, self._get_workspace(padded),
+                                      out_logits=logits)
             self._ws_version += 1
-            return logits
+            return logits[:batch]
         return _MLPFunction.apply(x, self, *self._param_list)
 
     def loss_and_grads(self, x, target, loss_scale: float = 1.0):

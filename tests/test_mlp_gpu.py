@@ -162,3 +162,27 @@ def test_mlp_full_size_against_oracle(native):
     g1 = model.flat_grads.clone()
     model.loss_and_grads(x.cuda(), y.cuda())
     assert torch.equal(g1, model.flat_grads)
+
+
+@pytest.mark.parametrize("B", [30, 1, 7])
+def test_mlp_ragged_batch_is_padded_exactly(native, B):
+    """The reference DataLoader's last batch is whatever is left (drop_last=False): model(x) must take any size."""
+    import pytorch_distributed_examples_b200 as pkg
+    from oracle import mlp_oracle, synth_oracle
+    torch.manual_seed(2)
+    sd = {k: v.detach().clone() for k, v in mlp_oracle.OracleMLP(1, 128).state_dict().items()}
+    xn, yn = synth_oracle.synth_batch(5, np.arange(B))
+    x, y = torch.from_numpy(xn), torch.from_numpy(yn)
+    lg32, loss32, g32 = mlp_oracle.forward_backward(sd, x, y, 1, 128)
+    _, _, g64 = mlp_oracle.forward_backward(sd, x, y, 1, 128, dtype=torch.float64)
+    model = pkg.Model(1, 128); model.load_state_dict(sd); model = model.cuda()
+    logits = model(x.cuda())
+    assert logits.shape == (B, 10)
+    loss = torch.nn.functional.cross_entropy(logits, y.cuda())
+    loss.backward()
+    assert abs(loss.item() - loss32.item()) <= 1e-5 * abs(loss32.item())
+    for k, p in model.named_parameters():
+        scale = g64[k].abs().max().item()
+        assert (p.grad.double().cpu() - g64[k]).abs().max().item() <= 1e-5 * scale + 2 * (g32[k].double() - g64[k]).abs().max().item() + 4 * scale / max(B, 64), k
+    with torch.no_grad():
+        assert torch.equal(model(x.cuda()), logits.detach())
