@@ -98,6 +98,14 @@ def _worker_optimizer(rank, world, port, q):
     assert hvd.broadcast_object({"a": rank}, root_rank=1) == {"a": 1}
     sd = opt.state_dict()
     assert "momentum_buffer" in sd["state"][0]
+    # evaluate(): every rank ends with the GLOBAL (correct, total) of the sharded test set (one allreduce)
+    shards = [[_data(50 + r * 3 + k, r, n=7 + k) for k in range(3)] for r in range(world)]
+    with torch.no_grad():
+        want_c = sum(int((model(x_).argmax(1) == y_).sum()) for sh in shards for x_, y_ in sh)
+    want_t = sum(x_.shape[0] for sh in shards for x_, _ in sh)
+    model.train()
+    c_, t_, acc = pkg.evaluate(model, shards[rank], communicator=hvd._require())
+    assert (c_, t_) == (want_c, want_t) and abs(acc - want_c / want_t) < 1e-12 and model.training
     q.put((rank, "ok"))
     dist.destroy_process_group()
 
