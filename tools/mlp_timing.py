@@ -1,4 +1,8 @@
-"""Per-role clock64 breakdown of the MLP GEMM kernel (needs lib/libddp_step_dbg.so built with -DDDP_MLP_TIMING)."""
+"""Per-role clock64 breakdown of the MLP GEMM kernel.  Needs a debug build of the library next to the real one:
+    nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -shared -Xcompiler -fPIC -DDDP_MLP_TIMING \
+         -I<site-packages>/nvidia/nccl/include pytorch_distributed_examples_b200/csrc/*.cu \
+         -o pytorch_distributed_examples_b200/lib/libddp_step_dbg.so -ldl
+(the counters live in registers and are flushed once per CTA, so the instrumented kernel runs at full speed)."""
 import ctypes, os, sys, torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 os.environ["DDP_LIB_PATH"] = os.path.join(ROOT, "pytorch_distributed_examples_b200/lib/libddp_step_dbg%s.so" % (sys.argv[1] if len(sys.argv) > 1 else ""))

@@ -1,5 +1,7 @@
 """Development probe for the symmetric two-shot allreduce: per-phase NVSwitch bandwidth (tools/probe/mc_probe.cu)
-and NCCL / product-kernel time as a function of message size.  torchrun --nproc-per-node=N tools/sym_probe.py"""
+and NCCL / product-kernel time as a function of message size.
+    nvcc -gencode arch=compute_100a,code=sm_100a -O3 -shared -Xcompiler -fPIC -o tools/probe/libmc_probe.so tools/probe/mc_probe.cu
+    torchrun --nproc-per-node=N tools/sym_probe.py"""
 import ctypes
 import json
 import os
