@@ -186,3 +186,27 @@ def test_mlp_ragged_batch_is_padded_exactly(native, B):
         assert (p.grad.double().cpu() - g64[k]).abs().max().item() <= 1e-5 * scale + 2 * (g32[k].double() - g64[k]).abs().max().item() + 4 * scale / max(B, 64), k
     with torch.no_grad():
         assert torch.equal(model(x.cuda()), logits.detach())
+
+
+@pytest.mark.parametrize("H,Fe,B", [(1, 100, 36), (2, 36, 64), (0, 260, 132)])
+def test_mlp_odd_shapes_against_oracle(native, H, Fe, B):
+    """Feature counts that are multiples of 4 but not of the 32 / 128 tile sizes, and batches that are not multiples of
+    32: the TMA units clip / zero-fill the ragged tiles (K, M and N edges of all three GEMM layouts)."""
+    import pytorch_distributed_examples_b200 as pkg
+    from oracle import mlp_oracle, synth_oracle
+    torch.manual_seed(H * 1000 + Fe)
+    sd = {k: v.detach().clone() for k, v in mlp_oracle.OracleMLP(H, Fe).state_dict().items()}
+    xn, yn = synth_oracle.synth_batch(11, np.arange(B))
+    x, y = torch.from_numpy(xn), torch.from_numpy(yn)
+    lg32, loss32, g32 = mlp_oracle.forward_backward(sd, x, y, H, Fe)
+    lg64, loss64, g64 = mlp_oracle.forward_backward(sd, x, y, H, Fe, dtype=torch.float64)
+    model = pkg.Model(hidden_layers=H, features=Fe); model.load_state_dict(sd); model = model.cuda()
+    loss = model.loss_and_grads(x.cuda(), y.cuda())
+    assert abs(loss.item() - loss64.item()) <= 1e-5 * abs(loss64.item())
+    for k, p in model.named_parameters():
+        scale = g64[k].abs().max().item()
+        err = (p.grad.double().cpu() - g64[k]).abs().max().item()
+        assert err <= 1e-5 * scale + 2 * (g32[k].double() - g64[k]).abs().max().item() + 4 * scale / max(B, 64), (k, err, scale)
+    with torch.no_grad():
+        logits = model(x.cuda())
+    assert (logits.cpu().double() - lg64).abs().max().item() <= 1e-5 * lg64.abs().max().item() + 2 * (lg32.double() - lg64).abs().max().item()
