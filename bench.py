@@ -121,7 +121,7 @@ def reference_arm(args, world, rank):
 
 def workload_config(B, n):
     return {"workload": f"MNIST CNN Net (mnist_horovod.py) fused fwd/bwd/optimizer step, synthetic 28x28, "
-                        f"batch {B}/GPU, fp32, SGD lr=0.01 momentum=0.9" + (", NCCL bucket allreduce" if n > 1 else ""),
+                        f"batch {B}/GPU, fp32, SGD lr=0.01 momentum=0.9" + (", per-step bucket allreduce" if n > 1 else ""),
             "per_gpu_batch": B, "global_batch": B * n, "optimizer": "sgd(lr=0.01,momentum=0.9)",
             "parallelism": f"dp{n}", "l2": "inputs rotate through a resident pool larger than the 126 MB L2"}
 
@@ -254,6 +254,9 @@ def main():
         "gpu_launches": step.kernel_launches_per_step * K,
         "final_loss": loss_final,
     }
+    if N > 1:    # which exchange ran: the one-shot NVLink peer-memory allreduce fused with the update, or ncclAllReduce + fused update
+        line["config"]["collective"] = "nvlink-peer-memory one-shot allreduce fused with the update" if step.use_peer \
+            else "ncclAllReduce + fused update"
 
     # ---------------- roofline of the dominant kernel (rank 0) ----------------
     if rank == 0:
