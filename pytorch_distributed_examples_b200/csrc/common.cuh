@@ -99,6 +99,12 @@ int sm_count();
 // tensor-core conv2 forward (conv2_fwd_tc.cu)
 int launch_conv2_fwd_tc(const float* params, const float* a1, const float* mask2d, uint64_t seed, uint64_t offset,
                         const int64_t* offset_dev, int training, float* a2, uint8_t* idx2, int B, cudaStream_t stream);
+// sparse conv2 backward (net_bwd_sparse.cu): one visit per live (channel, pool cell) entry instead of dense 8x8 planes
+int launch_conv2_wgrad_sp(const float* da2, const float* a2, const uint8_t* idx2, const float* a1, float drop_scale,
+                          float* partials, int B, int* parts_out, cudaStream_t stream, bool pdl);
+int launch_conv2_dgrad_sp(const float* params, const float* da2, const float* a2, const uint8_t* idx2, const float* a1,
+                          float drop_scale, float* dp1, int B, cudaStream_t stream);
+bool bwd_dense();                        // api.cu: true when DDP_BWD_DENSE=1 (A/B switch: the dense conv2 backward kernels)
 // per-kernel event timing (api.cu); mark(i) records event i on `stream` when profiling is on
 void prof_mark(int idx, cudaStream_t stream);
 bool prof_enabled();

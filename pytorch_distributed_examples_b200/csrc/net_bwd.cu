@@ -673,15 +673,19 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
   const float drop_scale = training ? 2.f : 1.f;
   const float nll_coef = -loss_scale / float(B);
 
-  static bool attr_done = false;
-  if (!attr_done) {
-    DDP_CUDA(cudaFuncSetAttribute(head_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HB_SMEM));
-    DDP_CUDA(cudaFuncSetAttribute(conv2_dgrad_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, D2_SMEM));
-    DDP_CUDA(cudaFuncSetAttribute(conv2_dgrad_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, D2_SMEM));
-    DDP_CUDA(cudaFuncSetAttribute(conv2_dgrad_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, D2_SMEM));
-    DDP_CUDA(cudaFuncSetAttribute(conv2_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, W2_SMEM));
-    DDP_CUDA(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, W1_SMEM));
-    attr_done = true;
+  {   // function attributes are per device: a process may drive several GPUs (ddp_set_device per host thread)
+    static bool attr_done[64] = {false};
+    int dev = 0;
+    DDP_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !attr_done[dev]) {
+      DDP_CUDA(cudaFuncSetAttribute(head_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HB_SMEM));
+      DDP_CUDA(cudaFuncSetAttribute(conv2_dgrad_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, D2_SMEM));
+      DDP_CUDA(cudaFuncSetAttribute(conv2_dgrad_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, D2_SMEM));
+      DDP_CUDA(cudaFuncSetAttribute(conv2_dgrad_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, D2_SMEM));
+      DDP_CUDA(cudaFuncSetAttribute(conv2_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, W2_SMEM));
+      DDP_CUDA(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, W1_SMEM));
+      attr_done[dev] = true;
+    }
   }
   int parts_head, parts_c2, parts_c1;
   prof_mark(4, stream);
@@ -708,7 +712,10 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
     parts_c2 = nstages < MAX_PARTS ? nstages : MAX_PARTS;
     if (parts_c2 > sms * 3) parts_c2 = sms * 3;      // 3 CTAs/SM: one stages while the others compute
   }
+  const bool dense = bwd_dense();
   auto launch_wgrad2 = [&]() -> int {
+    if (!dense)
+      return launch_conv2_wgrad_sp(sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale, sc.partials, B, &parts_c2, wstream, !fork);
     DDP_CUDA(launch_pdl(conv2_wgrad_kernel, dim3(parts_c2), dim3(W2_THREADS), W2_SMEM, wstream, !fork, sc.da2, ws.a2, ws.idx2, ws.a1,
                         drop_scale, sc.partials, B));
     return 0;
@@ -717,7 +724,9 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
     if (int rc = launch_wgrad2()) return rc;
     DDP_CUDA(cudaEventRecord(join_ev, wstream));
   }
-  {
+  if (!dense) {
+    if (int rc = launch_conv2_dgrad_sp(params, sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale, sc.dp1, B, stream)) return rc;
+  } else {
     // warps per sample: 4 while the SMs are mostly empty (latency mode), 1 once one warp per sample fills them
     const int split = B <= 1024 ? 4 : (B <= 2048 ? 2 : 1);
     const int spc = D2_WARPS / split;
