@@ -35,13 +35,14 @@ __device__ __forceinline__ void mbarrier_arrive(uint64_t* bar) {
 // CTA = 20 consumer warps (warp <-> output channel co) + 2 producer warps, persistent over the samples b = blockIdx,
 // blockIdx + grid, ...  Consumer lane = cp*5 + kw (cp = input-channel pair, 25 active lanes) holds the 10
 // accumulators dW[co][2cp+c][kh][kw] (c < 2 packed in one 64-bit register, kh < 5) for ALL samples the CTA sees.
-// Per live entry: 5 LDS.64 + 5 packed FFMA2.
+// Per live entry: 5 LDS.64 + 5 packed FFMA2; entries are taken two at a time so that 10 loads are in flight.
 // Shared memory per sample ("slot", ring of SW_SLOTS): a1 as channel-pair-interleaved planes [cp][12x12][c] with a
-// pair stride of 149 eight-byte words (== 5 mod 16: the lanes of a half-warp read distinct 8-byte banks), and the
-// 320 entries pre-decoded to (g, position oy*12+ox).  The raw tiles (a1, a2, da2, idx2) arrive by cp.async.bulk
-// into a 4-deep raw ring; the producer warps (even / odd samples) turn them into slots.  There is NO block-wide
-// barrier in the loop: Dropout2d kills half of the (sample, channel) pairs, so the consumer warps have very
-// different amounts of work per sample -- full/empty mbarriers per slot let them drift apart by up to the ring depth.
+// pair stride of 149 eight-byte words (== 5 mod 16: the lanes of a half-warp read distinct 8-byte banks), and per
+// channel the COMPACTED list of its live entries (g, position oy*12+ox), zero-filled to 16.  The raw tiles (a1, a2,
+// da2, idx2) arrive by cp.async.bulk into a 4-deep raw ring; the producer warps (even / odd samples) turn them into
+// slots.  There is NO block-wide barrier in the loop: Dropout2d kills half of the (sample, channel) pairs, so the
+// consumer warps have very different amounts of work per sample -- full/empty mbarriers per slot let them drift
+// apart by up to the ring depth.
 // ---------------------------------------------------------------------------
 constexpr int SW_CONS = C2;                        // consumer warps
 constexpr int SW_THREADS = (SW_CONS + 2) * 32;     // 704
@@ -49,7 +50,7 @@ constexpr int SW_SLOTS = 6;
 constexpr int SW_RAW = 4;                          // raw stages (even: a producer warp always meets its own stages)
 constexpr int SW_PS2 = 149;                        // channel-pair stride in 8-byte words
 constexpr int SW_A1W = 5 * SW_PS2 + 3;             // 748 words per slot
-constexpr int SW_SLOT_BYTES = SW_A1W * 8 + A2_PER * 4 + A2_PER;           // a1p | g[320] f32 | pos[320] u8 = 7584
+constexpr int SW_SLOT_BYTES = SW_A1W * 8 + C2 * 16 * 8 + 32;              // a1p | list[20][16] (g, pos) | cnt[20] u8 = 8576
 constexpr int SW_RAW_BYTES = A1_PER * 4 + 2 * A2_PER * 4 + A2_PER;        // a1 | a2 | da2 | idx2 = 8640
 constexpr int SW_SMEM = SW_SLOTS * SW_SLOT_BYTES + SW_RAW * SW_RAW_BYTES + (2 * SW_SLOTS + SW_RAW) * 8;
 __global__ void __launch_bounds__(SW_THREADS, 2)
@@ -89,6 +90,7 @@ conv2_wgrad_sp_kernel(const float* __restrict__ da2, const float* __restrict__ a
       if (p < n) issue(p);
       if (p + 2 < n) issue(p + 2);
     }
+    const unsigned half_lt = (1u << (lane & 15)) - 1u;   // lanes below this one inside its half-warp
     for (int k = p; k < n; k += 2) {
       const int slot = k % SW_SLOTS, rs = k % SW_RAW;
       mbarrier_wait(&raw_bar[rs], (k / SW_RAW) & 1);
@@ -106,20 +108,26 @@ conv2_wgrad_sp_kernel(const float* __restrict__ da2, const float* __restrict__ a
           if (pos < 144) d[pos] = pack2(r0[pos], r0[pos + 144]);
         }
       }
-      // entries: g = dL/d(conv2 output at the pool argmax) or 0, pos = oy*12 + ox
+      // entries: a half-warp owns one channel (16 pool cells); live ones (g != 0) are packed to the front of the
+      // channel's list in cell order, dead ones become zero entries behind them
       {
         const float* e_a2 = ra + A1_PER;
         const float* e_da2 = e_a2 + A2_PER;
         const uint8_t* e_id = reinterpret_cast<const uint8_t*>(e_da2 + A2_PER);
-        float* g_out = reinterpret_cast<float*>(dst + SW_A1W);
-        uint8_t* p_out = reinterpret_cast<uint8_t*>(g_out + A2_PER);
+        unsigned long long* list = dst + SW_A1W;
+        uint8_t* cnt = reinterpret_cast<uint8_t*>(list + C2 * 16);
 #pragma unroll
         for (int q = 0; q < 10; ++q) {
           const int e = lane + 32 * q;               // = co*16 + pp
           const float gv = e_a2[e] > 0.f ? e_da2[e] * drop_scale : 0.f;
-          const int id = e_id[e], pp = e & 15;
-          g_out[e] = gv;
-          p_out[e] = uint8_t((2 * (pp >> 2) + (id >> 1)) * P1 + 2 * (pp & 3) + (id & 1));
+          const int id = e_id[e], pp = e & 15, co = e >> 4;
+          const unsigned pos = unsigned((2 * (pp >> 2) + (id >> 1)) * P1 + 2 * (pp & 3) + (id & 1));
+          const bool on = gv != 0.f;
+          const unsigned m = (__ballot_sync(0xffffffffu, on) >> (lane & 16)) & 0xffffu;
+          const int nlive = __popc(m);
+          const int at = on ? __popc(m & half_lt) : nlive + __popc(~m & half_lt);
+          list[co * 16 + at] = on ? ((unsigned long long)__float_as_uint(gv) | ((unsigned long long)pos << 32)) : 0ull;
+          if ((lane & 15) == 0) cnt[co] = uint8_t(nlive);
         }
       }
       __syncwarp();
@@ -141,27 +149,29 @@ conv2_wgrad_sp_kernel(const float* __restrict__ da2, const float* __restrict__ a
   unsigned long long acc[5];
 #pragma unroll
   for (int k = 0; k < 5; ++k) acc[k] = 0ull;
-  float bacc = 0.f;                                    // lanes 0..15: bias-gradient share of pool cell `lane`
+  float bacc = 0.f;                                    // bias gradient: every lane adds the same g's in list order
   for (int k = 0; k < n; ++k) {
     const int slot = k % SW_SLOTS;
     mbarrier_wait(&full_bar[slot], (k / SW_SLOTS) & 1);
     const unsigned long long* a1w = reinterpret_cast<const unsigned long long*>(slots + slot * SW_SLOT_BYTES);
-    const float* g_in = reinterpret_cast<const float*>(a1w + SW_A1W);
-    const uint8_t* p_in = reinterpret_cast<const uint8_t*>(g_in + A2_PER);
-    float g = 0.f; int pos = 0;
-    if (lane < 16) { g = g_in[co * 16 + lane]; pos = p_in[co * 16 + lane]; }
-    bacc += g;
-    unsigned live = __ballot_sync(0xffffffffu, g != 0.f);
+    const ulonglong2* list = reinterpret_cast<const ulonglong2*>(a1w + SW_A1W + co * 16);
+    const int cnt = reinterpret_cast<const uint8_t*>(a1w + SW_A1W + C2 * 16)[co];
     const unsigned long long* base = a1w + lane_w;
-    while (live) {
-      const int pp = __ffs(live) - 1;
-      live &= live - 1;
-      const float gb = __shfl_sync(0xffffffffu, g, pp);
-      const int pb = __shfl_sync(0xffffffffu, pos, pp);
-      const unsigned long long g2 = pack2(gb, gb);
-      const unsigned long long* q = base + pb;
+    for (int i = 0; i < cnt; i += 2) {                 // two entries per trip (an odd count meets a zero entry)
+      const ulonglong2 e = list[i >> 1];
+      const float g0 = lo_f(e.x), g1 = lo_f(e.y);
+      const unsigned long long* q0 = base + unsigned(e.x >> 32);
+      const unsigned long long* q1 = base + unsigned(e.y >> 32);
+      unsigned long long v0[5], v1[5];
 #pragma unroll
-      for (int kh = 0; kh < 5; ++kh) fma2(acc[kh], g2, q[kh * P1]);
+      for (int kh = 0; kh < 5; ++kh) { v0[kh] = q0[kh * P1]; v1[kh] = q1[kh * P1]; }
+      const unsigned long long g20 = pack2(g0, g0), g21 = pack2(g1, g1);
+#pragma unroll
+      for (int kh = 0; kh < 5; ++kh) fma2(acc[kh], g20, v0[kh]);
+#pragma unroll
+      for (int kh = 0; kh < 5; ++kh) fma2(acc[kh], g21, v1[kh]);
+      bacc += g0;
+      bacc += g1;
     }
     __syncwarp();
     if (lane == 0) mbarrier_arrive(&empty_bar[slot]);
@@ -174,9 +184,6 @@ conv2_wgrad_sp_kernel(const float* __restrict__ da2, const float* __restrict__ a
       part[OFF_C2W + co * 250 + (2 * cp + 1) * 25 + kh * 5 + kw] = hi_f(acc[kh]);
     }
   }
-  // bias: lanes 0..15 hold per-cell sums; fixed-order tree
-#pragma unroll
-  for (int o = 8; o > 0; o >>= 1) bacc += __shfl_xor_sync(0xffffffffu, bacc, o);
   if (lane == 0) part[OFF_C2B + co] = bacc;
 }
 
@@ -185,17 +192,19 @@ conv2_wgrad_sp_kernel(const float* __restrict__ da2, const float* __restrict__ a
 // The 12 output rows are produced in 4 bands: band py (the entries of pool row py) touches rows 2py .. 2py+5.
 // lane = ry*5 + cp (ry = row inside the band, cp = input-channel pair; 30 active lanes) holds the band's
 // accumulators acc[x 0..11] as packed pairs (channels 2cp, 2cp+1).  An entry (co, py, px; g, idy, idx) adds
-//   g * W[co][2cp+c][ry-idy][k-idx]   to   acc[2px+k][c],   k = 0..5
-// W sits in shared memory as [co][kw+1 (7)][kh+1 (7)][cp][c] with ZERO blocks at kw+1, kh+1 in {0, 6}: taps outside
-// the 5x5 window read zeros, so there is neither a branch on idx nor a predicate on the row -- the entry's phase
-// only moves the (warp-uniform) base address, and the lanes of one LDS.64 read consecutive 8-byte words.
-// Per live entry: 6 LDS.64 + 6 packed FFMA2 (fma.rn.f32x2).  After a band, rows 2py and 2py+1 are final and are
-// written out; the rest moves down two rows with shuffles.  Entry data of band py+1 is fetched while band py runs.
-// Output dp1 = da1 * (a1 > 0): gradient w.r.t. the pooled conv1 map before ReLU.
+//   g * W[co][2cp+c][ry-idy][kw]   to   acc[2px+idx+kw][c],   kw = 0..4
+// W sits in shared memory as [co][kw][kh+1 (7)][cp][c] with ZERO rows at kh+1 in {0, 6}: rows outside the 5x5 window
+// read zeros (no predicate), the entry's idy only moves the warp-uniform base address, and the lanes of one LDS.64
+// read consecutive 8-byte words.  Per band the live entries of each pool cell are first COMPACTED into two lists in
+// shared memory, one per idx, so the inner loops have static accumulator indices, no branch and no shuffle:
+// per live entry 5 LDS.64 + 5 packed FFMA2 (fma.rn.f32x2), two entries per trip.  After a band, rows 2py and 2py+1
+// are final and are written out; the rest moves down two rows with shuffles.  Entry data of band py+1 is fetched
+// while band py runs.  Output dp1 = da1 * (a1 > 0): gradient w.r.t. the pooled conv1 map before ReLU.
 // ---------------------------------------------------------------------------
-constexpr int SD_MAXW = 8;                             // warps per CTA (launch picks 4..8)
-constexpr int SD_CO2 = 245;                            // float2 words per output channel: 7 x 7 x 5
-constexpr int SD_W2 = C2 * SD_CO2 + 4;                 // + over-read of the two idle lanes
+constexpr int SD_MAXW = 10;                            // warps per CTA (launch picks 4..10)
+constexpr int SD_CO2 = 175;                            // 8-byte words per output channel: 5 x 7 x 5
+constexpr int SD_W2 = C2 * SD_CO2 + 8;                 // + over-read of the two idle lanes
+constexpr int SD_LIST = 22;                            // entries per list: 20 + zero terminator, even
 __device__ __forceinline__ void sd_emit(const unsigned long long (&acc)[12], int lane, int y, bool on,
                                         const float* __restrict__ a1b, float* __restrict__ dpb) {
   if (!on) return;
@@ -218,20 +227,39 @@ __device__ __forceinline__ void sd_emit(const unsigned long long (&acc)[12], int
     reinterpret_cast<float4*>(dpb + o0 + 144)[q] = u;
   }
 }
-__global__ void __launch_bounds__(SD_MAXW * 32, 4)
+// all entries of one list: acc[X0 + kw] += g * W-row, two entries per trip
+template <int X0>
+__device__ __forceinline__ void sd_run_list(unsigned long long (&acc)[12], const ulonglong2* __restrict__ list, int cnt,
+                                            const unsigned long long* __restrict__ wl) {
+  for (int i = 0; i < cnt; i += 2) {
+    const ulonglong2 e = list[i >> 1];
+    const unsigned long long* w0 = wl + unsigned(e.x >> 32);
+    const unsigned long long* w1 = wl + unsigned(e.y >> 32);
+    unsigned long long v0[5], v1[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) { v0[k] = w0[k * 35]; v1[k] = w1[k * 35]; }
+    const unsigned long long g0 = pack2(lo_f(e.x), lo_f(e.x)), g1 = pack2(lo_f(e.y), lo_f(e.y));
+#pragma unroll
+    for (int k = 0; k < 5; ++k) fma2(acc[X0 + k], g0, v0[k]);
+#pragma unroll
+    for (int k = 0; k < 5; ++k) fma2(acc[X0 + k], g1, v1[k]);
+  }
+}
+__global__ void __launch_bounds__(SD_MAXW * 32, 3)
 conv2_dgrad_sp_kernel(const float* __restrict__ params, const float* __restrict__ da2,
                       const float* __restrict__ a2, const uint8_t* __restrict__ idx2,
                       const float* __restrict__ a1, float drop_scale, float* __restrict__ dp1, int B) {
   __shared__ __align__(16) unsigned long long w_s[SD_W2];
+  __shared__ __align__(16) unsigned long long list_s[SD_MAXW][8][SD_LIST];     // per warp: [px*2 + idx][entry]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int nthreads = blockDim.x, wpc = nthreads >> 5;
   pdl_trigger();
   for (int i = tid; i < SD_W2; i += nthreads) {
     float v0 = 0.f, v1 = 0.f;
     if (i < C2 * SD_CO2) {
-      const int co = i / SD_CO2, r = i % SD_CO2, kwp = r / 35, khp = (r % 35) / 5, cp = r % 5;
-      if (kwp >= 1 && kwp <= 5 && khp >= 1 && khp <= 5) {
-        const float* w = params + OFF_C2W + co * 250 + (2 * cp) * 25 + (khp - 1) * 5 + (kwp - 1);
+      const int co = i / SD_CO2, r = i % SD_CO2, kw = r / 35, khp = (r % 35) / 5, cp = r % 5;
+      if (khp >= 1 && khp <= 5) {
+        const float* w = params + OFF_C2W + co * 250 + (2 * cp) * 25 + (khp - 1) * 5 + kw;
         v0 = w[0]; v1 = w[25];
       }
     }
@@ -241,6 +269,8 @@ conv2_dgrad_sp_kernel(const float* __restrict__ params, const float* __restrict_
   pdl_wait();                                          // da2 (head_bwd) is read from here on
   const int ry = lane / 5;                             // 0..5 (6 for the two idle lanes)
   const unsigned long long* wl = w_s + lane;
+  unsigned long long (*lists)[SD_LIST] = list_s[warp];
+  const unsigned lt_mask = (1u << lane) - 1u;
   const int nwarps = gridDim.x * wpc;
   const int lco = lane < C2 ? lane : 0;                // lane co < 20 fetches its channel's entries
   for (int b = blockIdx.x * wpc + warp; b < B; b += nwarps) {
@@ -256,34 +286,40 @@ conv2_dgrad_sp_kernel(const float* __restrict__ params, const float* __restrict_
     for (int x = 0; x < 12; ++x) acc[x] = 0ull;
 #pragma unroll
     for (int py = 0; py < 4; ++py) {
-      // this band's 4 entries of channel `lane`: gradient (0 = dead) and phase offset into W (bytes of `offs`)
+      // this band's 4 entries of channel `lane`
       float g[4];
       g[0] = na.x > 0.f ? nd.x * drop_scale : 0.f;
       g[1] = na.y > 0.f ? nd.y * drop_scale : 0.f;
       g[2] = na.z > 0.f ? nd.z * drop_scale : 0.f;
       g[3] = na.w > 0.f ? nd.w * drop_scale : 0.f;
-      unsigned offs = 0u;
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const unsigned id = (ni >> (8 * e)) & 3u;      // idy = id >> 1, idx = id & 1
-        offs |= (40u - 35u * (id & 1u) - 5u * (id >> 1)) << (8 * e);
-      }
       if (lane >= C2) { g[0] = 0.f; g[1] = 0.f; g[2] = 0.f; g[3] = 0.f; }
+      const unsigned ids = ni;
       if (py < 3) { na = a4[py + 1]; nd = d4[py + 1]; ni = i4[py + 1]; }
+      int cnt[8];
+      __syncwarp();                                    // the previous band's lists are consumed
 #pragma unroll
       for (int px = 0; px < 4; ++px) {
-        unsigned live = __ballot_sync(0xffffffffu, g[px] != 0.f);
-        while (live) {
-          const int co = __ffs(live) - 1;
-          live &= live - 1;
-          const float gb = __shfl_sync(0xffffffffu, g[px], co);
-          const unsigned ob = (__shfl_sync(0xffffffffu, offs, co) >> (8 * px)) & 0xffu;
-          const unsigned long long g2 = pack2(gb, gb);
-          const unsigned long long* wp = wl + co * SD_CO2 + ob;
-#pragma unroll
-          for (int k = 0; k < 6; ++k) fma2(acc[2 * px + k], g2, wp[k * 35]);
-        }
+        const unsigned id = (ids >> (8 * px)) & 3u;    // idy = id >> 1, idx = id & 1
+        const bool on = g[px] != 0.f;
+        const unsigned m0 = __ballot_sync(0xffffffffu, on && !(id & 1u));
+        const unsigned m1 = __ballot_sync(0xffffffffu, on && (id & 1u));
+        cnt[2 * px] = __popc(m0);
+        cnt[2 * px + 1] = __popc(m1);
+        // entry = (g, word offset of W[co][kw=0][kh+1 = ry - idy + 1][cp] relative to this lane's base)
+        const unsigned long long ent = (unsigned long long)__float_as_uint(g[px]) |
+                                       ((unsigned long long)(unsigned(lane) * SD_CO2 + 5u - 5u * (id >> 1)) << 32);
+        if (on) lists[2 * px + (id & 1u)][__popc(((id & 1u) ? m1 : m0) & lt_mask)] = ent;
+        if (lane == 0) { lists[2 * px][cnt[2 * px]] = 0ull; lists[2 * px + 1][cnt[2 * px + 1]] = 0ull; }
       }
+      __syncwarp();
+      sd_run_list<0>(acc, reinterpret_cast<const ulonglong2*>(lists[0]), cnt[0], wl);
+      sd_run_list<1>(acc, reinterpret_cast<const ulonglong2*>(lists[1]), cnt[1], wl);
+      sd_run_list<2>(acc, reinterpret_cast<const ulonglong2*>(lists[2]), cnt[2], wl);
+      sd_run_list<3>(acc, reinterpret_cast<const ulonglong2*>(lists[3]), cnt[3], wl);
+      sd_run_list<4>(acc, reinterpret_cast<const ulonglong2*>(lists[4]), cnt[4], wl);
+      sd_run_list<5>(acc, reinterpret_cast<const ulonglong2*>(lists[5]), cnt[5], wl);
+      sd_run_list<6>(acc, reinterpret_cast<const ulonglong2*>(lists[6]), cnt[6], wl);
+      sd_run_list<7>(acc, reinterpret_cast<const ulonglong2*>(lists[7]), cnt[7], wl);
       if (py < 3) {
         sd_emit(acc, lane, 2 * py + ry, lane < 10, a1b, dpb);        // rows 2py, 2py+1 are complete
 #pragma unroll
@@ -322,15 +358,15 @@ int launch_conv2_wgrad_sp(const float* da2, const float* a2, const uint8_t* idx2
 
 int launch_conv2_dgrad_sp(const float* params, const float* da2, const float* a2, const uint8_t* idx2, const float* a1,
                           float drop_scale, float* dp1, int B, cudaStream_t stream) {
-  // one warp per sample; warps per CTA chosen so that the samples spread evenly over 4 CTAs per SM in ONE round
-  // (B = 4096: 28 per SM = 4 CTAs x 7 warps); larger batches loop with 8 warps per CTA
+  // one warp per sample; warps per CTA chosen so that the samples spread evenly over 3 CTAs per SM
+  // (B = 4096: 28 per SM -> 8 warps per CTA, two rounds for a few CTAs); larger batches loop with 8 warps per CTA
   const int sms = sm_count();
   const int per_sm = (B + sms - 1) / sms;
-  int wpc = (per_sm + 3) / 4;
+  int wpc = (per_sm + 2) / 3;
   if (wpc < 4) wpc = 4;
   if (wpc > SD_MAXW) wpc = SD_MAXW;
   const int nblk = (B + wpc - 1) / wpc;
-  int grid = sms * 4;
+  int grid = sms * 3;
   if (grid > nblk) grid = nblk;
   DDP_CUDA(launch_pdl(conv2_dgrad_sp_kernel, dim3(grid), dim3(wpc * 32), 0, stream, true, params, da2, a2, idx2, a1,
                       drop_scale, dp1, B));
