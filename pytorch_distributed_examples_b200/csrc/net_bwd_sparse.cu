@@ -284,8 +284,8 @@ conv2_dgrad_sp_kernel(const float* __restrict__ params, const float* __restrict_
     unsigned long long acc[12];
 #pragma unroll
     for (int x = 0; x < 12; ++x) acc[x] = 0ull;
-#pragma unroll
-    for (int py = 0; py < 4; ++py) {
+#pragma unroll 1
+    for (int py = 0; py < 4; ++py) {                   // NOT unrolled: 8 list loops per band are 1/4 of the code this way
       // this band's 4 entries of channel `lane`
       float g[4];
       g[0] = na.x > 0.f ? nd.x * drop_scale : 0.f;
@@ -320,15 +320,12 @@ conv2_dgrad_sp_kernel(const float* __restrict__ params, const float* __restrict_
       sd_run_list<5>(acc, reinterpret_cast<const ulonglong2*>(lists[5]), cnt[5], wl);
       sd_run_list<6>(acc, reinterpret_cast<const ulonglong2*>(lists[6]), cnt[6], wl);
       sd_run_list<7>(acc, reinterpret_cast<const ulonglong2*>(lists[7]), cnt[7], wl);
-      if (py < 3) {
-        sd_emit(acc, lane, 2 * py + ry, lane < 10, a1b, dpb);        // rows 2py, 2py+1 are complete
+      // rows 2py, 2py+1 are complete (after the last band: all six rows)
+      sd_emit(acc, lane, 2 * py + ry, lane < (py < 3 ? 10 : 30), a1b, dpb);
 #pragma unroll
-        for (int x = 0; x < 12; ++x) {
-          const unsigned long long v = __shfl_down_sync(0xffffffffu, acc[x], 10);
-          acc[x] = lane < 20 ? v : 0ull;
-        }
-      } else {
-        sd_emit(acc, lane, 6 + ry, lane < 30, a1b, dpb);             // rows 6..11
+      for (int x = 0; x < 12; ++x) {
+        const unsigned long long v = __shfl_down_sync(0xffffffffu, acc[x], 10);
+        acc[x] = lane < 20 ? v : 0ull;
       }
     }
   }
