@@ -127,3 +127,35 @@ def train_steps(state_dict, xs, ys, masks2d, masks1d, opt_kind="sgd", world=1, *
         opt.step()
         losses.append(torch.stack(step_losses))
     return torch.stack(losses), {k: v.detach().clone() for k, v in net.state_dict().items()}
+
+
+def routing(state_dict, x, mask2d=None, mask1d=None, dtype=torch.float64):
+    """Where the forward ROUTES gradients (ref: horovod/mnist_horovod.py:19-23): per 2x2 pool window the argmax
+    (0..3 in window scan order) and the margin to the runner-up, per ReLU the pre-activation.  Two fp32
+    implementations can only disagree on a route where the margin / |pre-activation| is within rounding noise,
+    so parity tests count the disagreements and require every one of them to sit on such a near-tie."""
+    net = OracleNet().to(dtype)
+    net.load_state_dict({k: v.to(dtype) for k, v in state_dict.items()})
+    x = x.to(dtype)
+
+    def pool_route(y):                                   # y [B,C,H,W] -> idx [B,C,H/2,W/2] in 0..3, best, margin
+        B, C, H, W = y.shape
+        w = y.view(B, C, H // 2, 2, W // 2, 2).permute(0, 1, 2, 4, 3, 5).reshape(B, C, H // 2, W // 2, 4)
+        srt, _ = w.sort(dim=-1, descending=True)
+        best = srt[..., 0]
+        idx = (w == best.unsqueeze(-1)).float().argmax(dim=-1)   # first maximum wins, like max_pool2d
+        return idx, best, srt[..., 0] - srt[..., 1]
+
+    with torch.no_grad():
+        y1 = net.conv1(x)
+        idx1, p1, m1 = pool_route(y1)
+        a1 = F.relu(p1)
+        y2 = net.conv2(a1)
+        if mask2d is not None:
+            y2 = y2 * (mask2d.to(dtype).view(-1, 20, 1, 1) * 2.0)
+        idx2, p2, m2 = pool_route(y2)
+        a2 = F.relu(p2).view(-1, 320)
+        z1 = net.fc1(a2)
+    return dict(idx1=idx1.reshape(x.shape[0], -1), pre1=p1.reshape(x.shape[0], -1), margin1=m1.reshape(x.shape[0], -1),
+                idx2=idx2.reshape(x.shape[0], -1), pre2=p2.reshape(x.shape[0], -1), margin2=m2.reshape(x.shape[0], -1),
+                pre_fc1=z1, scale1=y1.abs().max().item(), scale2=y2.abs().max().item(), scale_fc1=z1.abs().max().item())

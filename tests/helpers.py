@@ -58,3 +58,46 @@ def assert_grad_close(actual, g32, g64, batch, rtol=RTOL, flips=4, name=""):
     assert not bool(bad.any()), (f"{name}: {int(bad.sum())} elements off, worst {err.max().item():.3e} "
                                  f"(scale {scale:.3e}, allowance {rtol * scale + flips * scale / batch:.3e})")
     return err.max().item() / scale
+
+
+def saved_routing(workspace, batch):
+    """Our forward's saved activations out of the caller-owned workspace (layout: csrc/common.cuh carve_workspace):
+    a1 [B,1440] f32, idx1 u8, a2 [B,320] f32, idx2 u8, h [B,50] f32 -- the ReLU masks and pool argmaxes the
+    backward kernels route gradients by."""
+    a256 = lambda v: (v + 255) & ~255
+    B = batch
+    o = 0
+    a1 = workspace[o:o + B * 1440 * 4].view(torch.float32).view(B, 1440); o += a256(B * 1440 * 4)
+    idx1 = workspace[o:o + B * 1440].view(B, 1440); o += a256(B * 1440)
+    a2 = workspace[o:o + B * 320 * 4].view(torch.float32).view(B, 320); o += a256(B * 320 * 4)
+    idx2 = workspace[o:o + B * 320].view(B, 320); o += a256(B * 320)
+    h = workspace[o:o + B * 50 * 4].view(torch.float32).view(B, 50)
+    return dict(a1=a1.cpu(), idx1=(idx1 & 3).cpu().long(), a2=a2.cpu(), idx2=(idx2 & 3).cpu().long(), h=h.cpu())
+
+
+def count_routing_flips(ours, ref, mask2d=None, mask1d=None, rel=1e-5):
+    """Disagreements between OUR gradient routes and the fp64 oracle's (oracle/net_oracle.routing).
+    Returns (flips, bad): `flips` = routes that differ where a gradient actually flows; `bad` = those of them whose
+    fp64 margin (pool: best minus runner-up; ReLU: |pre-activation|) exceeds rel * the layer's scale, i.e. NOT a
+    near-tie.  A correct fp32 kernel has bad == 0 at any batch size; a kernel that mis-routes for a systematic
+    reason does not."""
+    flips = bad = 0
+    for L, pre_k, idx_k, mar_k, act_k, sc_k in ((1, "pre1", "idx1", "margin1", "a1", "scale1"),
+                                               (2, "pre2", "idx2", "margin2", "a2", "scale2")):
+        pre, scale = ref[pre_k], ref[sc_k]
+        live_ref, live_ours = pre > 0, ours[act_k] > 0
+        relu_flip = live_ref != live_ours
+        pool_flip = (ref[idx_k] != ours[idx_k]) & live_ref & live_ours      # a dead cell routes nothing either way
+        if L == 2 and mask2d is not None:                                    # dropped channels route nothing
+            keep = (mask2d.view(-1, 20, 1) > 0).expand(-1, 20, 16).reshape(pre.shape)
+            relu_flip &= keep; pool_flip &= keep
+        flips += int(relu_flip.sum()) + int(pool_flip.sum())
+        bad += int((relu_flip & (pre.abs() > rel * scale)).sum()) + int((pool_flip & (ref[mar_k] > rel * scale)).sum())
+    z, scale = ref["pre_fc1"], ref["scale_fc1"]
+    h_live = ours["h"] > 0
+    ref_live = z > 0
+    if mask1d is not None:
+        ref_live = ref_live & (mask1d > 0)
+    f = h_live != ref_live
+    flips += int(f.sum()); bad += int((f & (z.abs() > rel * scale)).sum())
+    return flips, bad

@@ -170,7 +170,16 @@ def main():
     log("DDP comm hooks ok")
 
     # 3b. the DDP script's own model with native kernels: pkg.Model under stock DDP + our hook, the reference loop body
-    #     (ref: pytorch_elastic/mnist_ddp_elastic.py:58,70-75,172-174) == the oracle's W-rank "average then Adam" loop
+    #     (ref: pytorch_elastic/mnist_ddp_elastic.py:58,70-75,172-174).  Two sharp checks (neither can pass with wrong
+    #     numbers):
+    #       (i)  EVERY step, the averaged gradient DDP leaves in p.grad == mean over the W shards of the oracle's fp64
+    #            gradient evaluated AT OUR CURRENT PARAMETERS (no drift between the two trajectories to hide behind);
+    #       (ii) the W-rank loop with plain SGD -- gradient error maps linearly into parameter error, no eps
+    #            discontinuity -- == the oracle's W-rank "average then step" loop at 1e-5 of the parameter scale
+    #            plus lr * steps * (the gradient allowance of (i)).
+    #     Adam (the script's optimizer, :173) then runs on the same hooks; its UPDATE RULE is pinned at 1e-5 against
+    #     torch.optim on injected gradients in tests/test_update_gpu.py, and the fraction of elements within
+    #     1e-5 * scale + 1e-3 * lr of the oracle loop is REPORTED (an |g| ~ eps element legitimately moves by O(lr)).
     from oracle import mlp_oracle, synth_oracle
     import numpy as np
     Hn, Fn, Bn, steps = 2, 256, 32, 3
@@ -178,39 +187,63 @@ def main():
     sd0 = {k: v.detach().clone() for k, v in mlp_oracle.OracleMLP(Hn, Fn).state_dict().items()}
     xn, yn = synth_oracle.synth_batch(1234, np.arange(steps * W * Bn))
     xs = torch.from_numpy(xn).view(steps, W * Bn, 1, 28, 28); ys = torch.from_numpy(yn).view(steps, W * Bn)
-    _, sd_ref = mlp_oracle.train_steps(sd0, xs, ys, Hn, Fn, "adam", world=W, lr=1e-3)
-    mm = pkg.Model(hidden_layers=Hn, features=Fn); mm.load_state_dict(sd0); mm = mm.cuda()
-    dm = DDP(mm, device_ids=[local], gradient_as_bucket_view=True)
-    dm.register_comm_hook(pkg.HookState(), pkg.allreduce_hook)
-    om = torch.optim.Adam(dm.parameters(), lr=1e-3)
     crit = torch.nn.CrossEntropyLoss()
-    # the averaged gradient of the first step: mean over the W shards' gradients (what DDP's bucket allreduce leaves in p.grad)
-    g_ref = None
-    for r in range(W):
-        _, _, gr = mlp_oracle.forward_backward(sd0, xs[0, r * Bn:(r + 1) * Bn], ys[0, r * Bn:(r + 1) * Bn], Hn, Fn, dtype=torch.float64)
-        g_ref = gr if g_ref is None else {k2: g_ref[k2] + gr[k2] for k2 in gr}
-    g_ref = {k2: v / W for k2, v in g_ref.items()}
-    for k in range(steps):
-        sl = slice(R * Bn, (R + 1) * Bn)
-        om.zero_grad()
-        crit(dm(xs[k, sl].cuda()), ys[k, sl].cuda()).backward()
-        if k == 0:
+    FLIPS = 4            # ReLU units within rounding of zero may fall on the other side: each moves a gradient by ~scale/B
+
+    def oracle_mean_grad(sd_now, k):
+        g_ref = None
+        for r in range(W):
+            _, _, gr = mlp_oracle.forward_backward(sd_now, xs[k, r * Bn:(r + 1) * Bn], ys[k, r * Bn:(r + 1) * Bn], Hn, Fn,
+                                                   dtype=torch.float64)
+            g_ref = gr if g_ref is None else {k2: g_ref[k2] + gr[k2] for k2 in gr}
+        return {k2: v / W for k2, v in g_ref.items()}
+
+    def mlp_ddp_loop(opt_kind, lr_):
+        mm = pkg.Model(hidden_layers=Hn, features=Fn); mm.load_state_dict(sd0); mm = mm.cuda()
+        dm = DDP(mm, device_ids=[local], gradient_as_bucket_view=True)
+        dm.register_comm_hook(pkg.HookState(), pkg.allreduce_hook)
+        om = (torch.optim.SGD if opt_kind == "sgd" else torch.optim.Adam)(dm.parameters(), lr=lr_)
+        worst = 0.0
+        for k in range(steps):
+            sl = slice(R * Bn, (R + 1) * Bn)
+            sd_now = {key: v.detach().cpu().clone() for key, v in mm.state_dict().items()}
+            om.zero_grad()
+            crit(dm(xs[k, sl].cuda()), ys[k, sl].cuda()).backward()
+            g_ref = oracle_mean_grad(sd_now, k)
             for key, p_ in mm.named_parameters():
                 scale = g_ref[key].abs().max().item()
                 err = (p_.grad.double().cpu() - g_ref[key]).abs().max().item()
-                # 1e-5 plus the O(1/B) a ReLU unit sitting within rounding of zero may move (see tests/test_mlp_gpu.py)
-                assert err <= 1e-5 * scale + 4 * scale / (W * Bn), (key, err, scale)
-        om.step()
-    torch.cuda.synchronize()
+                assert err <= 1e-5 * scale + FLIPS * scale / (W * Bn), (opt_kind, k, key, err, scale)
+                worst = max(worst, err / scale)
+            om.step()
+        torch.cuda.synchronize()
+        same_on_all_ranks(mm.flat_params, f"native MLP under DDP ({opt_kind})")
+        return mm, worst
+
+    lr_sgd = 0.05
+    _, sd_sgd = mlp_oracle.train_steps(sd0, xs, ys, Hn, Fn, "sgd", world=W, lr=lr_sgd)
+    mm, worst_g = mlp_ddp_loop("sgd", lr_sgd)
+    g0 = oracle_mean_grad(sd0, 0)
+    worst_p = 0.0
     for key, v in mm.state_dict().items():
-        ref = sd_ref[key]
+        ref = sd_sgd[key]
+        pscale, gscale = ref.abs().max().item(), g0[key].abs().max().item()
+        err = (v.cpu() - ref).abs().max().item()
+        assert err <= 1e-5 * pscale + lr_sgd * steps * (1e-5 * gscale + FLIPS * gscale / (W * Bn)), (key, err, pscale, gscale)
+        worst_p = max(worst_p, err / pscale)
+    log(f"native MLP under DDP, SGD loop == oracle W-rank loop: worst gradient error {worst_g:.2e} of scale (every step, "
+        f"at our parameters), worst parameter error {worst_p:.2e} of scale")
+    _, sd_adam = mlp_oracle.train_steps(sd0, xs, ys, Hn, Fn, "adam", world=W, lr=1e-3)
+    mm, worst_g = mlp_ddp_loop("adam", 1e-3)
+    fr = []
+    for key, v in mm.state_dict().items():
+        ref = sd_adam[key]
         d = (v.cpu() - ref).abs()
-        # Adam turns a 1e-6 relative gradient difference into an O(lr) parameter difference wherever |g| is within
-        # ~100x of eps = 1e-8 -- more elements the larger the global batch (more cancellation), so: most elements
-        # tight, every element within the total distance Adam can move a weight in `steps` steps
-        assert (d <= 1e-5 * ref.abs().max().item() + 1e-3 * 1e-3).float().mean().item() >= 0.90 and d.max().item() <= 1.01 * 1e-3 * steps, key
-    same_on_all_ranks(mm.flat_params, "native MLP under DDP")
-    log("native MLP (tensor-core GEMMs) under DDP == oracle W-rank Adam loop ok")
+        fr.append((d <= 1e-5 * ref.abs().max().item() + 1e-3 * 1e-3).float().mean().item())
+        assert d.max().item() <= 1e-3 * steps * 1.001, key        # sanity only: Adam cannot move further
+    log(f"native MLP under DDP, Adam loop: worst gradient error {worst_g:.2e} of scale (every step); fraction of elements "
+        f"within 1e-5*scale + 1e-3*lr of the oracle loop at W={W}: min over tensors {min(fr):.4f} (reported, not gated: "
+        f"|g| ~ eps elements move by O(lr))")
 
     # 3c. evaluation over the sharded test set: every rank reports the GLOBAL (correct, total)
     tds = pkg.SyntheticMNIST(length=10000, seed=9)
