@@ -87,33 +87,43 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def cpu_reference(n_ranks, B, steps, warmup, budget_s):
+    """The reference's W-rank CPU/gloo loop on this box's host cores (oracle/cpu_baseline.py): stock CPU DDP around the
+    reference CNN, SGD(lr=0.01, momentum=0.9), per-rank batch B, W = n_ranks processes.  Two thread settings:
+    all host threads (cores // W per rank; the arm's `value`) and the reference-faithful OMP_NUM_THREADS=1
+    (ref: pytorch_elastic/mnist_ddp_elastic.py:27; torchrun's own default).  Each on a bounded sample."""
+    from oracle import cpu_baseline
+    cores = cpu_baseline.host_cores()
+    per_rank = max(1, cores // n_ranks)
+    opt = dict(kind=OPT["kind"], lr=OPT["lr"], momentum=OPT["momentum"])
+    best = cpu_baseline.bounded_reference_run(n_ranks, B, steps, warmup, per_rank, budget_s, "cnn", opt)
+    faithful = best if per_rank == 1 else cpu_baseline.bounded_reference_run(n_ranks, B, steps, warmup, 1, budget_s, "cnn", opt)
+    def describe(r):
+        return (f"{r['steps']} timed steps of a {r['sample_batch']}-sample-per-rank slice of the {B}-sample-per-rank step, "
+                f"{n_ranks}-rank gloo DDP job (stock CPU DDP, reference loop body), {r['threads']} thread(s) per rank")
+    return dict(value=best["samples_per_s"], unit="samples/s", cores=per_rank * n_ranks, kind="port", sample=describe(best),
+                ms_per_full_step=best["ms_per_full_step"], ranks=n_ranks, threads_per_rank=per_rank, host_cores=cores,
+                cpu_model=cpu_baseline.cpu_model(),
+                reference_faithful_1_thread_per_rank={"value": faithful["samples_per_s"], "unit": "samples/s",
+                                                      "cores": n_ranks, "sample": describe(faithful),
+                                                      "ms_per_full_step": faithful["ms_per_full_step"]})
+
+
 def reference_arm(args, world, rank):
-    """--impl reference: the reference's CPU implementation of the step on the host cores (oracle port)."""
+    """--impl reference: the reference's CPU implementation of the step on the host cores.  Rank 0 alone launches and
+    prints it; what it launches is the reference's own configuration -- an N-rank gloo DDP job (N = --gpus) of the
+    reference loop, per-rank batch as in the GPU arm -- so the two arms' `config` are the same workload."""
     if rank != 0:
         return
-    import torch
-    from oracle import cpu_baseline
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    B = args.batch
-    probe = cpu_baseline.time_reference_loop(min(B, 256), 2, 1, OPT["kind"], lr=OPT["lr"], momentum=OPT["momentum"])
-    est_full = B / probe["samples_per_s"]                       # seconds per full-size step
-    budget = 150.0
-    sample_b = B
-    if est_full * (args.steps + args.warmup) > budget:          # bound the per-step sample, keep K and W
-        sample_b = max(64, int(B * budget / (est_full * (args.steps + args.warmup))) // 64 * 64)
-    r = cpu_baseline.time_reference_loop(sample_b, args.steps, args.warmup, OPT["kind"], lr=OPT["lr"],
-                                         momentum=OPT["momentum"])
-    sample = (f"{args.steps} timed steps of a {sample_b}-sample slice of the {B}-sample step, "
-              f"torch {torch.__version__} CPU, {r['threads']} threads")
+    B, N = args.batch, args.gpus
+    r = cpu_reference(N, B, args.steps, args.warmup, budget_s=70.0)
     line = {
-        "impl": "reference", "metric": METRIC, "value": r["samples_per_s"], "unit": "samples/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"] * (B / sample_b),
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": "samples/s", "n_gpus": N,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_full_step"],
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
-        "config": workload_config(B, args.gpus),
-        "cpu_baseline": {"value": r["samples_per_s"], "unit": "samples/s", "cores": r["threads"], "kind": "port",
-                         "sample": sample},
-        "e2e": {"value": r["samples_per_s"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "config": workload_config(B, N),
+        "cpu_baseline": r,
+        "e2e": {"value": r["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
@@ -124,6 +134,104 @@ def workload_config(B, n):
                         f"batch {B}/GPU, fp32, SGD lr=0.01 momentum=0.9" + (", per-step bucket allreduce" if n > 1 else ""),
             "per_gpu_batch": B, "global_batch": B * n, "optimizer": "sgd(lr=0.01,momentum=0.9)",
             "parallelism": f"dp{n}", "l2": "inputs rotate through a resident pool larger than the 126 MB L2"}
+
+
+def step_latency_stats(pkg, nat, B, momentum, steps=1000, warmup=50, slots=4):
+    """Per-step latency distribution of the graph-replayed step at batch B on one GPU (BASELINE configs[1]/[2] sizes):
+    one CUDA event per step boundary, consecutive differences -> median / p99 / mean."""
+    import torch
+    torch.manual_seed(0)
+    model = pkg.Net().cuda().train()
+    opt = pkg.FusedOptimizer(torch.optim.SGD(model.parameters(), lr=OPT["lr"], momentum=momentum))
+    st = pkg.TrainStep(model, opt, B, slots=slots)
+    ds = pkg.SyntheticMNIST(length=1 << 30, seed=1234)
+    for s_ in range(slots):
+        nat.synth_batch(ds.seed, None, s_ * B, B, st.xs[s_], st.ys[s_])
+    for i in range(warmup):
+        st.run_slot(i % slots)
+    torch.cuda.synchronize()
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+    evs[0].record()
+    for i in range(steps):
+        st.run_slot(i % slots)
+        evs[i + 1].record()
+    torch.cuda.synchronize()
+    d = sorted(evs[i].elapsed_time(evs[i + 1]) * 1e3 for i in range(steps))
+    return {"batch": B, "optimizer": f"sgd(lr=0.01,momentum={momentum})", "steps": steps,
+            "us_median": d[len(d) // 2], "us_p99": d[min(len(d) - 1, int(len(d) * 0.99))], "us_mean": sum(d) / len(d),
+            "samples_per_s_at_median": B / (d[len(d) // 2] * 1e-6)}
+
+
+def module_path_stats(pkg, nat, B, steps=200, warmup=20):
+    """The five-line loop the reference scripts contain, through the drop-in seam (ref: horovod/mnist_horovod.py:59-64):
+    optimizer.zero_grad(); output = model(data); loss = F.nll_loss(output, target); loss.backward(); optimizer.step()
+    with `Net` (autograd.Function) + `hvd.DistributedOptimizer` -- eager launches, no CUDA graph."""
+    import torch
+    import torch.nn.functional as F
+    torch.manual_seed(0)
+    model = pkg.Net().cuda().train()
+    opt = pkg.hvd.DistributedOptimizer(torch.optim.SGD(model.parameters(), lr=OPT["lr"], momentum=OPT["momentum"]),
+                                       named_parameters=model.named_parameters())
+    ds = pkg.SyntheticMNIST(length=1 << 30, seed=1234)
+    batches = [ds.batch(base_index=i * B, count=B) for i in range(4)]
+    def one(i):
+        data, target = batches[i % 4]
+        opt.zero_grad()
+        output = model(data)
+        loss = F.nll_loss(output, target)
+        loss.backward()
+        opt.step()
+        return loss
+    for i in range(warmup):
+        one(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        loss = one(i)
+    e1.record()
+    torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) * 1e3 / steps
+    return {"batch": B, "us_per_step": us, "samples_per_s": B / (us * 1e-6), "steps": steps, "final_loss": float(loss.item())}
+
+
+def bucket_allreduce_stats(comm, N, reps=20):
+    """ResNet-50-sized gradient bucket (BASELINE configs[4]: 25,557,032 parameters) over NVLink at N ranks: ncclAllReduce
+    and the in-switch two-shot allreduce (ddp_sym_allreduce), fp32 (102 MB) and bf16 (51 MB).  Collective: every rank calls it.
+    busbw = (S / t) * 2 (N - 1) / N (nccl-tests convention); t = max over ranks of the mean over `reps` back-to-back calls."""
+    import torch
+    import torch.distributed as dist
+    out = {}
+    n = 25_557_032 // 8 * 8
+    have_sym = comm.enable_symmetric(n * 4 + 4096)
+    for dtype, name in ((torch.float32, "fp32"), (torch.bfloat16, "bf16")):
+        S = n * (4 if dtype == torch.float32 else 2)
+        buf = torch.randn(n, device="cuda").to(dtype)
+        def timed(fn):
+            for _ in range(3):
+                fn()
+            torch.cuda.synchronize(); dist.barrier()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(reps):
+                fn()
+            b.record(); torch.cuda.synchronize()
+            t = torch.tensor([a.elapsed_time(b) / reps], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item()) * 1e-3
+        t = timed(lambda: comm.allreduce_sum_(buf))
+        out[f"nccl_{name}"] = {"bytes": S, "us": t * 1e6, "busbw_GB/s": S / t * 2 * (N - 1) / N / 1e9,
+                               "frac_of_900": S / t * 2 * (N - 1) / N / 900e9}
+        if have_sym:
+            comm.sym_view(dtype, n).copy_(buf)
+            t = timed(lambda: comm.sym_allreduce_(dtype, n, 0, 1.0 / N))
+            out[f"sym_two_shot_{name}"] = {"bytes": S, "us": t * 1e6, "busbw_GB/s": S / t * 2 * (N - 1) / N / 1e9,
+                                           "frac_of_900": S / t * 2 * (N - 1) / N / 900e9,
+                                           "mode": "multimem (in-switch)" if comm.sym["multicast"] else "peer load/store"}
+        del buf
+    if not have_sym:
+        out["sym_two_shot"] = {"unavailable": comm.sym_error}
+    return out
 
 
 def main():
@@ -255,7 +363,7 @@ def main():
         "final_loss": loss_final,
     }
     if N > 1:    # which exchange ran: the one-shot NVLink peer-memory allreduce fused with the update, or ncclAllReduce + fused update
-        line["config"]["collective"] = "nvlink-peer-memory one-shot allreduce fused with the update" if step.use_peer \
+        line["collective"] = "nvlink-peer-memory one-shot allreduce fused with the update" if step.use_peer \
             else "ncclAllReduce + fused update"
 
     # ---------------- roofline of the dominant kernel (rank 0) ----------------
@@ -282,24 +390,52 @@ def main():
         achieved = flops / dur_s / 1e12
         sm_mhz = clock_info.get("sm_mhz") or 1900.0
         ffma_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12
-        traffic = None
-        tpath = os.path.join(ROOT, "profiles", "r01_ncu_traffic_b4096.json")
-        if B == 4096 and os.path.exists(tpath):          # DRAM bytes per launch from the committed ncu --set full capture
-            traffic = json.load(open(tpath)).get(top)
+        traffic, traffic_src = None, None
+        for tname in ("r02_ncu_traffic_b4096.json", "r01_ncu_traffic_b4096.json"):
+            tpath = os.path.join(ROOT, "profiles", tname)
+            if B == 4096 and os.path.exists(tpath):      # DRAM bytes per launch: NOT measured in this run
+                traffic = json.load(open(tpath)).get(top)
+                traffic_src = f"from committed ncu --set full capture profiles/{tname}, not measured in this run"
+                if traffic is not None:
+                    break
+        # the conv2 backward kernels visit only the live (channel, pool cell) entries: executed MACs = 250 per entry
+        a256 = lambda v: (v + 255) & ~255
+        o_a2 = a256(B * 1440 * 4) + a256(B * 1440)
+        live_per_sample = float((step.ws[o_a2:o_a2 + B * 320 * 4].view(torch.float32) > 0).float().sum().item()) / B
+        executed_macs = dict(KERNEL_MACS)
+        if os.environ.get("DDP_BWD_DENSE", "0") != "1":
+            executed_macs["conv2_dgrad"] = executed_macs["conv2_wgrad"] = 250.0 * live_per_sample
         line["roofline"] = {"kernel": top, "bound": "tensor", "achieved": achieved, "peak": peaks["tflops"],
                             "unit": "TFLOP/s", "frac": achieved / peaks["tflops"], "traffic": traffic,
+                            "traffic_source": traffic_src,
                             "peak_source": f"MEASURED_PEAKS.json bf16 sustained ({peaks['source']})",
-                            "note": "fp32 FFMA kernel (1e-5 parity bar rules out single-pass TF32/BF16); "
-                                    "fraction of the fp32 FFMA peak given beside it",
+                            "note": "achieved = dense-equivalent algorithmic FLOPs (SURVEY 8(d) M3) / measured duration; "
+                                    "fp32 kernels (1e-5 parity bar rules out single-pass TF32/BF16): fraction of the fp32 "
+                                    "FFMA peak beside it; executed_* count the multiply-adds the kernel really issues "
+                                    "(the sparse conv2 backward skips structural zeros of the pool / Dropout2d / ReLU gradient)",
                             "fp32_ffma_peak_tflops": ffma_peak, "frac_of_fp32_ffma_peak": achieved / ffma_peak,
+                            "executed_tflops": 2.0 * executed_macs[top] * B / dur_s / 1e12,
+                            "live_conv2_entries_per_sample": live_per_sample,
                             "kernel_us": per_kernel_us,
+                            "kernel_dense_equiv_tflops": {k: 2.0 * KERNEL_MACS[k] * B / max(v, 1e-9) / 1e6 for k, v in per_kernel_us.items()},
+                            "kernel_executed_tflops": {k: 2.0 * executed_macs[k] * B / max(v, 1e-9) / 1e6 for k, v in per_kernel_us.items()},
                             "step_share": per_kernel_us[top] / max(sum(per_kernel_us.values()), 1e-9)}
         step_flops = FLOP_PER_SAMPLE * B
         line["step_tflops"] = step_flops / (ms_total / K * 1e-3) / 1e12
 
-    # ---------------- extras: HBM-bound kernels + CPU baseline (rank 0, N=1) ----------------
+    # ---------------- collective extra (all ranks): ResNet-50-sized bucket allreduce over NVLink ----------------
+    bucket_stats = None
+    if N > 1 and not args.no_extras:
+        try:
+            bucket_stats = bucket_allreduce_stats(comm, N)
+        except Exception as exc:
+            bucket_stats = {"error": repr(exc)}
+
+    # ---------------- extras: HBM-bound kernels, other BASELINE configs, CPU baselines (rank 0) ----------------
     if rank == 0 and not args.no_extras:
         extra = {}
+        if bucket_stats is not None:
+            extra[f"resnet50_bucket_allreduce_n{N}"] = bucket_stats
         n = 25_557_032 // 4 * 4     # ResNet-50-sized bucket (BASELINE configs[4])
         g = torch.randn(n, device="cuda"); p = torch.randn(n, device="cuda"); s1 = torch.zeros(n, device="cuda")
         h = _native.Hyper(); h.lr = 0.01; h.momentum = 0.9
@@ -357,17 +493,30 @@ def main():
             del mlp, tm, xm, ym
         except Exception as exc:       # the MLP row is an extra: never lose the headline line over it
             extra["mlp_5x1024_fwd_bwd_b4096"] = {"error": repr(exc)}
+        if N == 1:
+            try:      # BASELINE configs[1] / configs[2] sizes and the reference-exact optimizer (SGD, momentum 0: mnist_horovod.py:50)
+                extra["step_latency_b64_sgd_momentum"] = step_latency_stats(pkg, nat, 64, 0.9)
+                extra["step_latency_b512_sgd_momentum"] = step_latency_stats(pkg, nat, 512, 0.9)
+                extra["step_latency_b64_sgd_mu0"] = step_latency_stats(pkg, nat, 64, 0.0)
+                extra["step_latency_b4096_sgd_mu0"] = step_latency_stats(pkg, nat, 4096, 0.0, steps=300)
+                extra["step_latency_b4096_sgd_momentum"] = step_latency_stats(pkg, nat, 4096, 0.9, steps=300)
+                extra["module_path_b4096"] = module_path_stats(pkg, nat, 4096)
+                extra["module_path_b64"] = module_path_stats(pkg, nat, 64)
+            except Exception as exc:
+                extra["latency_extras_error"] = repr(exc)
+            try:      # the DDP script's real configuration on the host cores: Model(5, 1024) + Adam + CrossEntropyLoss (:172-174)
+                from oracle import cpu_baseline
+                rm = cpu_baseline.bounded_reference_run(1, 4096, 2, 1, cpu_baseline.host_cores(), 10.0, "mlp", dict(kind="adam", lr=1e-3))
+                extra["mlp_5x1024_adam_cpu_reference"] = {"samples_per_s": rm["samples_per_s"], "ms_per_4096_step": rm["ms_per_full_step"],
+                                                          "threads": rm["threads"], "sample": f"{rm['steps']} steps of a {rm['sample_batch']}-sample slice, 1-rank gloo DDP"}
+            except Exception as exc:
+                extra["mlp_5x1024_adam_cpu_reference"] = {"error": repr(exc)}
         line["extra"] = extra
         del g, p, s1, s2, flush, chunks, bucket, xb, yb
-        if N == 1:
-            from oracle import cpu_baseline
-            cores = os.cpu_count() or 1
-            probe = cpu_baseline.time_reference_loop(256, 2, 1, OPT["kind"], threads=cores, lr=OPT["lr"], momentum=OPT["momentum"])
-            nsteps = max(2, min(40, int(15.0 * probe["samples_per_s"] / B)))
-            r = cpu_baseline.time_reference_loop(B, nsteps, 1, OPT["kind"], threads=cores, lr=OPT["lr"], momentum=OPT["momentum"])
-            line["cpu_baseline"] = {"value": r["samples_per_s"], "unit": "samples/s", "cores": r["threads"], "kind": "port",
-                                    "sample": f"{nsteps} steps of the same {B}-sample step (reference loop, torch CPU, "
-                                              f"{r['threads']} threads, {r['ms_per_step']:.1f} ms/step)"}
+        pass
+    if rank == 0 and not args.no_extras:
+        # the reference's W-rank CPU/gloo loop on this box's host cores, W = N, bounded sample
+        line["cpu_baseline"] = cpu_reference(N, B, steps=4, warmup=1, budget_s=12.0)
     if rank == 0:
         print(json.dumps(line), flush=True)
     if N > 1:

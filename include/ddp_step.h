@@ -196,6 +196,11 @@ int ddp_comm_unique_id(void* uid_out);
 int ddp_comm_init(void** comm_out, const void* uid, int world, int rank);
 int ddp_comm_destroy(void* comm);
 int ddp_comm_abort(void* comm);
+/* Failure detection (ref: horovod/horovod_mnist_elastic.py:55 -- @hvd.elastic.run retries after a failed collective):
+ * *nccl_result_out <- ncclCommGetAsyncError (0 = healthy, 7 = still in progress, anything else = the ring is broken).
+ * The host layer polls it while it waits for a collective with a deadline; a broken or timed-out ring is torn down
+ * with ddp_comm_abort (never ddp_comm_destroy, which would wait for the stuck kernel). */
+int ddp_comm_async_error(void* comm, int* nccl_result_out);
 /* dtype 0 = f32, 1 = bf16, 2 = i64, 3 = u8 */
 int ddp_allreduce_sum(void* comm, void* buf, int64_t count, int dtype, void* stream);
 int ddp_allreduce_max(void* comm, void* buf, int64_t count, int dtype, void* stream);

@@ -1,46 +1,179 @@
 """The reference training loop timed on the host cores (reported baseline, never the optimisation target).
 
-Loop body = ref: horovod/mnist_horovod.py:59-64 (zero_grad / model(data) / F.nll_loss / backward / step) with
-the reference's own CNN (restated in net_oracle.OracleNet, bit-identical to the reference class — checked in
-gen_golden.py) under the installed torch CPU kernels, synthetic tensors pre-generated in RAM.
+What runs is the reference's own configuration of the path:
+  * `init_process_group("gloo")` + `OMP_NUM_THREADS`           ref: pytorch_elastic/mnist_ddp_elastic.py:22-27
+  * `DDP(model, device_ids=None)` (stock CPU DDP: bucket allreduce over gloo)        ref: :58
+  * loop body `Trainer._run_batch`: zero_grad / model(source) / criterion / backward / step   ref: :70-75
+with either the Horovod scripts' CNN + SGD(+momentum) + F.nll_loss (ref: horovod/mnist_horovod.py:9-25,50,59-64 --
+Horovod itself is not installable here, so its "average every p.grad, then step" is what stock DDP's bucket
+allreduce does) or the DDP script's real model, `Model(hidden_layers=5, features=1024)` + Adam + CrossEntropyLoss
+(ref: pytorch_elastic/mnist_ddp_elastic.py:133-159,172-174).  Models are the oracle restatements (net_oracle.OracleNet,
+mlp_oracle.OracleMLP: bit-identical to the reference classes, checked in gen_golden.py); synthetic tensors are
+pre-generated in RAM (MNIST cannot be downloaded).  `time_reference_ddp` launches W worker processes of this
+module (one per rank, 127.0.0.1 rendezvous), times `steps` steps between barriers with time.perf_counter and
+returns GLOBAL samples/s (W * per-rank batch / step time, max over ranks).
 TEST/BENCH INFRASTRUCTURE ONLY: bench.py's ``cpu_baseline`` leg and ``--impl reference`` arm call this.
 """
 from __future__ import annotations
 
+import json
+import os
+import socket
+import subprocess
+import sys
 import time
 
-import torch
-import torch.nn.functional as F
-
-from . import net_oracle
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def time_reference_loop(batch: int, steps: int, warmup: int, opt_kind: str = "sgd", threads: int | None = None,
-                        seed: int = 0, **opt_kw):
-    """Returns dict(samples_per_s, ms_per_step, threads, steps, batch)."""
-    if threads:
-        torch.set_num_threads(threads)
-    torch.manual_seed(seed)
-    net = net_oracle.OracleNet()
+def cpu_model() -> str:
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.lower().startswith("model name"):
+                    return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
+def host_cores() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _build(model: str, opt_kw: dict):
+    import torch
+    import torch.nn.functional as F
+    from . import mlp_oracle, net_oracle
+    if model == "cnn":
+        net = net_oracle.OracleNet()
+        opt_kind = opt_kw.pop("kind", "sgd")
+        crit = F.nll_loss
+        shape = (1, 28, 28)
+    elif model == "mlp":
+        net = mlp_oracle.OracleMLP(5, 1024)
+        opt_kind = opt_kw.pop("kind", "adam")
+        crit = torch.nn.CrossEntropyLoss()
+        shape = (1, 28, 28)
+    else:
+        raise ValueError(model)
+    return net, opt_kind, crit, shape
+
+
+def _worker(args):
+    """One rank of the reference job (ref: mnist_ddp_elastic.py:22-27,58,70-75)."""
+    import torch
+    import torch.distributed as dist
+    from torch.nn.parallel import DistributedDataParallel as DDP
+    from . import net_oracle
+    torch.set_num_threads(args["threads"])
+    dist.init_process_group("gloo")                                   # env://, 127.0.0.1
+    rank, world = dist.get_rank(), dist.get_world_size()
+    torch.manual_seed(0)                                              # same initial replica on every rank
+    net, opt_kind, crit, shape = _build(args["model"], dict(args["opt"]))
     net.train()
-    opt = net_oracle.make_optimizer(opt_kind, net.parameters(), **opt_kw)
-    g = torch.Generator().manual_seed(seed + 1)
-    x = torch.randn(batch, 1, 28, 28, generator=g)
-    y = torch.randint(0, 10, (batch,), generator=g)
+    ddp = DDP(net, device_ids=None)
+    opt_kw = {k: v for k, v in args["opt"].items() if k != "kind"}
+    opt = net_oracle.make_optimizer(opt_kind, ddp.parameters(), **opt_kw)
+    g = torch.Generator().manual_seed(1 + rank)                       # every rank its own shard
+    x = torch.randn(args["batch"], *shape, generator=g)
+    y = torch.randint(0, 10, (args["batch"],), generator=g)
 
-    def one():
+    def run_batch():
         opt.zero_grad()
-        out = net(x)
-        loss = F.nll_loss(out, y)
+        loss = crit(ddp(x), y)
         loss.backward()
         opt.step()
-        return loss
 
-    for _ in range(warmup):
-        one()
+    for _ in range(args["warmup"]):
+        run_batch()
+    dist.barrier()
     t0 = time.perf_counter()
-    for _ in range(steps):
-        one()
+    for _ in range(args["steps"]):
+        run_batch()
+    dist.barrier()
     dt = time.perf_counter() - t0
-    return dict(samples_per_s=batch * steps / dt, ms_per_step=dt / steps * 1e3, threads=torch.get_num_threads(),
-                steps=steps, batch=batch)
+    t = torch.tensor([dt], dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        print("CPU_BASELINE_RESULT " + json.dumps(dict(
+            seconds=float(t.item()), steps=args["steps"], batch=args["batch"], world=world,
+            threads=torch.get_num_threads(), samples_per_s=world * args["batch"] * args["steps"] / float(t.item()),
+            ms_per_step=float(t.item()) / args["steps"] * 1e3)), flush=True)
+    dist.destroy_process_group()
+
+
+def time_reference_ddp(world: int, batch: int, steps: int, warmup: int, threads_per_rank: int, model: str = "cnn",
+                       opt: dict | None = None, timeout: float = 900.0) -> dict:
+    """Launch the W-rank gloo job and return rank 0's result dict (global samples/s, ms/step, threads per rank)."""
+    opt = dict(opt or {})
+    port = _free_port()
+    spec = json.dumps(dict(model=model, batch=int(batch), steps=int(steps), warmup=int(warmup),
+                           threads=int(threads_per_rank), opt=opt))
+    procs = []
+    for r in range(world):
+        env = dict(os.environ)
+        for k in list(env):                       # the GPU job's torchrun environment must not leak into the CPU job
+            if k.startswith(("TORCHELASTIC", "GROUP_", "ROLE_")) or k in ("LOCAL_RANK", "LOCAL_WORLD_SIZE"):
+                env.pop(k)
+        env.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(r), WORLD_SIZE=str(world),
+                   OMP_NUM_THREADS=str(threads_per_rank), MKL_NUM_THREADS=str(threads_per_rank), CUDA_VISIBLE_DEVICES="",
+                   PYTHONPATH=ROOT + os.pathsep + env.get("PYTHONPATH", ""))
+        procs.append(subprocess.Popen([sys.executable, "-m", "oracle.cpu_baseline", "--worker", spec], cwd=ROOT, env=env,
+                                      stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True))
+    out0 = err0 = ""
+    deadline = time.time() + timeout
+    try:
+        for r, p in enumerate(procs):
+            o, e = p.communicate(timeout=max(1.0, deadline - time.time()))
+            if r == 0:
+                out0, err0 = o, e
+            if p.returncode != 0:
+                raise RuntimeError(f"cpu baseline rank {r} failed ({p.returncode}): {e[-2000:]}")
+    finally:
+        for p in procs:
+            if p.poll() is None:
+                p.kill()
+    for line in out0.splitlines():
+        if line.startswith("CPU_BASELINE_RESULT "):
+            return json.loads(line[len("CPU_BASELINE_RESULT "):])
+    raise RuntimeError("cpu baseline produced no result: " + err0[-2000:])
+
+
+def bounded_reference_run(world: int, batch: int, steps: int, warmup: int, threads_per_rank: int, budget_s: float,
+                          model: str = "cnn", opt: dict | None = None) -> dict:
+    """`time_reference_ddp` on a BOUNDED sample of the workload: a short probe sizes the per-rank slice of the
+    batch so that `warmup + steps` steps fit in `budget_s` seconds; steps and warm-up are kept as asked.
+    The result carries `sample_batch` (per-rank samples per step actually run) beside the full `batch`."""
+    probe_b = min(batch, 128 if model == "cnn" else 32)
+    probe = time_reference_ddp(world, probe_b, 2, 1, threads_per_rank, model, opt)
+    per_rank_rate = probe["samples_per_s"] / world
+    sample_b = batch
+    need = batch * (steps + warmup) / max(per_rank_rate, 1e-9)
+    if need > budget_s:
+        q = 64 if model == "cnn" else 16
+        sample_b = max(q, int(batch * budget_s / need) // q * q)
+    r = time_reference_ddp(world, sample_b, steps, warmup, threads_per_rank, model, opt)
+    r["sample_batch"] = sample_b
+    r["full_batch"] = batch
+    r["ms_per_full_step"] = r["ms_per_step"] * batch / sample_b
+    return r
+
+
+if __name__ == "__main__":
+    if len(sys.argv) >= 3 and sys.argv[1] == "--worker":
+        _worker(json.loads(sys.argv[2]))
+    else:       # by hand: python -m oracle.cpu_baseline W B steps threads [cnn|mlp]
+        W, B, K, T = (int(v) for v in sys.argv[1:5])
+        print(json.dumps(time_reference_ddp(W, B, K, 2, T, sys.argv[5] if len(sys.argv) > 5 else "cnn",
+                                            dict(kind="sgd", lr=0.01, momentum=0.9) if len(sys.argv) <= 5 or sys.argv[5] == "cnn"
+                                            else dict(kind="adam", lr=1e-3))))

@@ -66,6 +66,7 @@ SIGNATURES = {
     "ddp_comm_init": (c_int, [POINTER(c_void_p), c_void_p, c_int, c_int]),
     "ddp_comm_destroy": (c_int, [c_void_p]),
     "ddp_comm_abort": (c_int, [c_void_p]),
+    "ddp_comm_async_error": (c_int, [c_void_p, POINTER(c_int)]),
     "ddp_allreduce_sum": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "ddp_allreduce_max": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "ddp_broadcast": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p]),
@@ -126,6 +127,12 @@ def _stream():
     return torch.cuda.current_stream().cuda_stream
 
 
+class CollectiveError(RuntimeError):
+    """A collective (NCCL or NVLink peer-memory) entry point failed, reported an asynchronous error, or did not
+    finish before its deadline: a peer is lost or the ring is broken.  ``hvd.HorovodInternalError`` is this class;
+    ``hvd.elastic.run`` answers it with restore() + re-formation (ref: horovod/horovod_mnist_elastic.py:55)."""
+
+
 class Native:
     """Tensor-level façade over the C-ABI.  One instance per process."""
 
@@ -136,10 +143,14 @@ class Native:
         self._dev_bound = set()
 
     # -- plumbing ---------------------------------------------------------------------------------
-    def _check(self, rc: int, what: str):
+    def _check(self, rc: int, what: str, collective: bool = False):
         if rc != 0:
             msg = self.lib.ddp_last_error()
-            raise RuntimeError(f"{what} failed (rc={rc}): {msg.decode() if msg else ''}")
+            text = f"{what} failed (rc={rc}): {msg.decode() if msg else ''}"
+            # argument errors (DDP_EINVAL / DDP_ENOSYS, <= -1000) stay plain RuntimeErrors: they are caller bugs, not lost peers
+            if collective and rc > -1000:
+                raise CollectiveError(text)
+            raise RuntimeError(text)
 
     def bind_device(self, device: int):
         self._check(self.lib.ddp_set_device(int(device)), "ddp_set_device")
@@ -252,7 +263,7 @@ class Native:
     def comm_init(self, uid: bytes, world: int, rank: int):
         handle = c_void_p()
         buf = ctypes.create_string_buffer(uid, UID_BYTES)
-        self._check(self.lib.ddp_comm_init(ctypes.byref(handle), buf, world, rank), "ddp_comm_init")
+        self._check(self.lib.ddp_comm_init(ctypes.byref(handle), buf, world, rank), "ddp_comm_init", collective=True)
         return handle
 
     def comm_destroy(self, comm):
@@ -261,17 +272,23 @@ class Native:
     def comm_abort(self, comm):
         self._check(self.lib.ddp_comm_abort(comm), "ddp_comm_abort")
 
+    def comm_async_error(self, comm) -> int:
+        """ncclCommGetAsyncError: 0 healthy, 7 in progress, else broken."""
+        res = c_int(0)
+        self._check(self.lib.ddp_comm_async_error(comm, ctypes.byref(res)), "ddp_comm_async_error", collective=True)
+        return int(res.value)
+
     def allreduce_sum(self, comm, buf):
         self._check(self.lib.ddp_allreduce_sum(comm, _ptr(buf, "buf"), buf.numel(), _DTYPES[buf.dtype], _stream()),
-                    "ddp_allreduce_sum")
+                    "ddp_allreduce_sum", collective=True)
 
     def allreduce_max(self, comm, buf):
         self._check(self.lib.ddp_allreduce_max(comm, _ptr(buf, "buf"), buf.numel(), _DTYPES[buf.dtype], _stream()),
-                    "ddp_allreduce_max")
+                    "ddp_allreduce_max", collective=True)
 
     def broadcast(self, comm, buf, root: int):
         self._check(self.lib.ddp_broadcast(comm, _ptr(buf, "buf"), buf.numel() * buf.element_size(), root, _stream()),
-                    "ddp_broadcast")
+                    "ddp_broadcast", collective=True)
 
     # -- NVLink peer-memory allreduce (+ fused update) ----------------------------------------------
     def peer_create(self, world: int, rank: int, max_elems: int):
@@ -286,14 +303,14 @@ class Native:
 
     def peer_connect(self, peer, handles: bytes):
         buf = ctypes.create_string_buffer(handles, len(handles))
-        self._check(self.lib.ddp_peer_connect(peer, buf), "ddp_peer_connect")
+        self._check(self.lib.ddp_peer_connect(peer, buf), "ddp_peer_connect", collective=True)
 
     def peer_destroy(self, peer):
         self._check(self.lib.ddp_peer_destroy(peer), "ddp_peer_destroy")
 
     def peer_allreduce(self, peer, bucket):
         self._check(self.lib.ddp_peer_allreduce(peer, _ptr(bucket, "bucket", torch.float32), bucket.numel(), _stream()),
-                    "ddp_peer_allreduce")
+                    "ddp_peer_allreduce", collective=True)
 
     def peer_allreduce_update(self, peer, opt, bucket, params, state1, state2, n, hyper: Hyper, step=1, step_dev=None):
         rc = self.lib.ddp_peer_allreduce_update(peer, _ptr(bucket, "bucket", torch.float32), int(n), opt,
@@ -301,7 +318,7 @@ class Native:
                                                 _ptr(state1, "state1", torch.float32), _ptr(state2, "state2", torch.float32),
                                                 ctypes.byref(hyper), int(step), _ptr(step_dev, "step_dev", torch.int64),
                                                 _stream())
-        self._check(rc, "ddp_peer_allreduce_update")
+        self._check(rc, "ddp_peer_allreduce_update", collective=True)
 
     # -- two-shot allreduce in symmetric memory ------------------------------------------------------
     def sym_flag_bytes(self) -> int:
@@ -312,7 +329,7 @@ class Native:
         arr = (ctypes.c_uint64 * world)(*[int(a) for a in replicas])
         rc = self.lib.ddp_sym_allreduce(arr, int(multicast or 0), int(flag_offset), int(world), int(rank), int(byte_offset),
                                         int(n), _DTYPES[dtype], float(scale), int(max_ctas), int(unroll), _stream())
-        self._check(rc, "ddp_sym_allreduce")
+        self._check(rc, "ddp_sym_allreduce", collective=True)
 
     # -- MLP of the DDP script (tensor-core 3xTF32 GEMMs) ---------------------------------------------
     def mlp_param_layout(self, shape: "MLPShape"):

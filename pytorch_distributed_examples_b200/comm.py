@@ -9,8 +9,11 @@ Replaces ref: pytorch_elastic/mnist_ddp_elastic.py:22-27 (``init_process_group("
 """
 from __future__ import annotations
 
+import collections
 import os
 import pickle
+import threading
+import time
 
 import torch
 import torch.distributed as dist
@@ -53,6 +56,10 @@ class Communicator:
         self.sym = None           # symmetric buffer for the two-shot large-bucket allreduce (enable_symmetric)
         self.sym_error = None
         self._obj_seq = 0
+        self.broken = None        # reason string once the ring is known to be dead (a peer is lost); see wait()
+        self.timeout_s = float(os.environ.get("DDP_COLLECTIVE_TIMEOUT_S", "120"))
+        self._pending = collections.deque()   # (event, enqueue time) of collectives enqueued from Python
+        self._watchdog = None
         nat = _native.get()
         if self.world > 1:
             key = f"ddp_step/uid/gen{generation}"
@@ -61,7 +68,88 @@ class Communicator:
                 store.set(key, uid)
             else:
                 uid = bytes(store.get(key))
+                store.add(key + "/acks", 1)
             self.handle = nat.comm_init(uid, self.world, self.rank)
+            if self.rank == 0:
+                # Once every member has read the id, delete it: a later ring that reuses this tag
+                # (hvd.shutdown(); hvd.init()) can then never pick up a stale id -- its readers block until the new one is set.
+                try:
+                    deadline = time.monotonic() + 60
+                    while store.add(key + "/acks", 0) < self.world - 1 and time.monotonic() < deadline:
+                        time.sleep(0.002)
+                    store.delete_key(key)
+                    store.delete_key(key + "/acks")
+                except Exception:
+                    pass
+
+    # -- failure detection -----------------------------------------------------------------------------
+    # A dead peer does not make an intra-node NCCL collective fail: its kernel spins forever.  Every collective
+    # enqueued through this class therefore leaves a CUDA event behind; wait() polls the newest one against a deadline
+    # (and ncclCommGetAsyncError for transport errors), and a watchdog thread does the same for loops whose only host
+    # synchronisation is torch's own (loss.item()).  Either way a late collective ends in ncclCommAbort -- which makes
+    # the stuck kernel exit -- and CollectiveError (= hvd.HorovodInternalError) at the next call into this class.
+    def _note_collective(self):
+        if self.world <= 1 or not torch.cuda.is_available() or torch.cuda.is_current_stream_capturing():
+            return
+        ev = torch.cuda.Event()
+        ev.record()
+        self._pending.append((ev, time.monotonic()))
+        while len(self._pending) > 64:
+            self._pending.popleft()
+        if self._watchdog is None:
+            self._watchdog = threading.Thread(target=self._watch, name="ddp-comm-watchdog", daemon=True)
+            self._watchdog.start()
+
+    def _watch(self):
+        while self.handle is not None and self.broken is None:
+            time.sleep(min(1.0, max(0.05, self.timeout_s / 10)))
+            try:
+                while self._pending and self._pending[0][0].query():
+                    self._pending.popleft()
+                if self._pending and time.monotonic() - self._pending[0][1] > self.timeout_s:
+                    self.abort(f"a collective did not finish within {self.timeout_s:.0f} s (peer lost?)")
+            except Exception:
+                return
+
+    def abort(self, reason: str):
+        """Tear the ring down without waiting for it (ncclCommAbort): in-flight collective kernels exit."""
+        if self.broken is None:
+            self.broken = reason
+        h, self.handle = self.handle, None
+        if h is not None:
+            try:
+                _native.get().comm_abort(h)
+            except Exception:
+                pass
+
+    def raise_if_broken(self):
+        if self.broken is not None:
+            raise _native.CollectiveError(self.broken)
+
+    def wait(self, timeout_s: float | None = None):
+        """Block until every collective enqueued so far has finished; CollectiveError if the ring is broken, reports an
+        asynchronous NCCL error, or the deadline passes (the ring is aborted first, so the stream drains)."""
+        self.raise_if_broken()
+        if self.world <= 1 or not torch.cuda.is_available():
+            return
+        timeout_s = self.timeout_s if timeout_s is None else timeout_s
+        ev = torch.cuda.Event()
+        ev.record()
+        t0 = time.monotonic()
+        nat = _native.get()
+        while not ev.query():
+            if self.broken is not None:
+                break
+            if self.handle is not None:
+                err = nat.comm_async_error(self.handle)
+                if err not in (0, 7):
+                    self.abort(f"asynchronous NCCL error {err}")
+                    break
+            if time.monotonic() - t0 > timeout_s:
+                self.abort(f"a collective did not finish within {timeout_s:.0f} s (peer lost?)")
+                break
+            time.sleep(0.0005)
+        self.raise_if_broken()
 
     # -- NVLink peer-memory path for latency-bound buckets -------------------------------------------
     def enable_peer(self, max_elems: int) -> bool:
@@ -77,15 +165,24 @@ class Communicator:
             return True
         nat = _native.get()
         max_elems = (int(max_elems) + 3) // 4 * 4
+        if self.peer is not None:                       # growing: release the old context (device memory + IPC mappings)
+            torch.cuda.synchronize()
+            nat.peer_destroy(self.peer)
+            self.peer, self.peer_max_elems = None, 0
+        self._peer_seq = getattr(self, "_peer_seq", 0) + 1
         peer = nat.peer_create(self.world, self.rank, max_elems)
-        base = f"ddp_step/peer/gen{self.generation}/{max_elems}"
+        base = f"ddp_step/peer/gen{self.generation}/{self._peer_seq}/{max_elems}"
         self.store.set(f"{base}/{self.rank}", nat.peer_local_handle(peer))
         handles = b"".join(bytes(self.store.get(f"{base}/{r}")) for r in range(self.world))
         nat.peer_connect(peer, handles)
         # nobody may push before everyone has mapped everyone: rendezvous once through NCCL
         flag = torch.zeros(1, device="cuda")
         self.allreduce_sum_(flag)
-        torch.cuda.current_stream().synchronize()
+        self.wait()
+        try:                                            # every member has read every handle: no stale keys for a later ring
+            self.store.delete_key(f"{base}/{self.rank}")
+        except Exception:
+            pass
         self.peer, self.peer_max_elems = peer, max_elems
         return True
 
@@ -147,17 +244,23 @@ class Communicator:
     # -- tensor collectives (in place, on the current stream) ---------------------------------------
     def allreduce_sum_(self, t: torch.Tensor):
         if self.world > 1:
+            self.raise_if_broken()
             _native.get().allreduce_sum(self.handle, t)
+            self._note_collective()
         return t
 
     def allreduce_max_(self, t: torch.Tensor):
         if self.world > 1:
+            self.raise_if_broken()
             _native.get().allreduce_max(self.handle, t)
+            self._note_collective()
         return t
 
     def broadcast_(self, t: torch.Tensor, root: int = 0):
         if self.world > 1:
+            self.raise_if_broken()
             _native.get().broadcast(self.handle, t, root)
+            self._note_collective()
         return t
 
     # -- small host objects through the store --------------------------------------------------------
@@ -172,10 +275,18 @@ class Communicator:
         return pickle.loads(bytes(self.store.get(key)))
 
     def destroy(self):
+        """Orderly teardown of a healthy ring; a broken one (see abort) only releases its local resources."""
         if self.peer is not None:
             _native.get().peer_destroy(self.peer)
             self.peer = None
         self.sym = None
-        if self.handle is not None:
-            _native.get().comm_destroy(self.handle)
-            self.handle = None
+        h, self.handle = self.handle, None
+        self._pending.clear()
+        if h is not None:
+            if self.broken is None:
+                _native.get().comm_destroy(h)
+            else:
+                try:
+                    _native.get().comm_abort(h)
+                except Exception:
+                    pass

@@ -18,6 +18,7 @@ struct NcclApi {
   decltype(&ncclCommInitRank) CommInitRank = nullptr;
   decltype(&ncclCommDestroy) CommDestroy = nullptr;
   decltype(&ncclCommAbort) CommAbort = nullptr;
+  decltype(&ncclCommGetAsyncError) CommGetAsyncError = nullptr;
   decltype(&ncclAllReduce) AllReduce = nullptr;
   decltype(&ncclBroadcast) Broadcast = nullptr;
   decltype(&ncclGetErrorString) GetErrorString = nullptr;
@@ -41,7 +42,7 @@ static int load_nccl() {
 #define LOAD(sym)                                                                  \
   g_nccl.sym = reinterpret_cast<decltype(g_nccl.sym)>(dlsym(h, "nccl" #sym));      \
   if (!g_nccl.sym) { set_error("dlsym(nccl" #sym ") failed"); return DDP_ENOSYS; }
-  LOAD(GetUniqueId) LOAD(CommInitRank) LOAD(CommDestroy) LOAD(CommAbort)
+  LOAD(GetUniqueId) LOAD(CommInitRank) LOAD(CommDestroy) LOAD(CommAbort) LOAD(CommGetAsyncError)
   LOAD(AllReduce) LOAD(Broadcast) LOAD(GetErrorString)
 #undef LOAD
   g_nccl.handle = h;
@@ -106,6 +107,17 @@ extern "C" int ddp_comm_abort(void* comm) {
   if (!comm) return 0;
   if (int rc = load_nccl()) return rc;
   DDP_NCCL(g_nccl.CommAbort(static_cast<ncclComm_t>(comm)));
+  return 0;
+}
+
+extern "C" int ddp_comm_async_error(void* comm, int* nccl_result_out) {
+  DDP_REQUIRE(comm && nccl_result_out, "null argument");
+  if (int rc = load_nccl()) return rc;
+  ncclResult_t async = ncclSuccess;
+  DDP_NCCL(g_nccl.CommGetAsyncError(static_cast<ncclComm_t>(comm), &async));
+  *nccl_result_out = int(async);
+  if (async != ncclSuccess && async != ncclInProgress)
+    set_error("asynchronous NCCL error %d: %s", int(async), g_nccl.GetErrorString(async));
   return 0;
 }
 

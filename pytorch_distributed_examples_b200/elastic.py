@@ -28,6 +28,7 @@ import torch
 from . import _native
 
 _PLAN_KEY = "ddp_step/elastic/plan"
+_ALIVE_KEY = "ddp_step/elastic/alive"
 
 
 reset_latencies_ms = []   # wall time of every elastic reset seen by this process: interrupt -> new ring -> state synced
@@ -75,7 +76,9 @@ class State:
         for cb in self._reset_callbacks:
             cb()
 
-    # scalars
+    # scalars.  Commits are double-buffered: a commit is STAGED into the spare copy, then the ring's health is checked
+    # (with a deadline), and only then does the spare become "the last commit".  A commit taken while a collective of a
+    # lost peer was still stuck on the GPU would snapshot garbage; this way restore() never sees it.
     def _save_scalars(self):
         self._saved_scalars = {k: copy.deepcopy(getattr(self, k)) for k in self._scalar_names}
 
@@ -90,8 +93,15 @@ class State:
             setattr(self, k, v)
         self._save_scalars()
 
+    def _stage(self):
+        self._staged_scalars = {k: copy.deepcopy(getattr(self, k)) for k in self._scalar_names}
+
+    def _promote(self):
+        self._saved_scalars = self._staged_scalars
+
     def save(self):
-        self._save_scalars()
+        self._stage()
+        self._promote()
 
     def restore(self):
         self._restore_scalars()
@@ -100,8 +110,17 @@ class State:
         self._sync_scalars()
 
     def commit(self):
-        self.save()
-        self.check_host_updates()
+        """ref: horovod/horovod_mnist_elastic.py:72.  Stage a copy of the state, check the ring (a lost peer raises
+        HorovodInternalError here and the staged copy is dropped), make the copy the last commit, then act on an
+        announced membership change."""
+        h = _hvd()
+        self._stage()
+        try:
+            self.check_host_updates()
+        except h.HostsUpdatedInterrupt:
+            self._promote()
+            raise
+        self._promote()
 
     def check_host_updates(self):
         """Raise HostsUpdatedInterrupt on EVERY member at the same commit if a resize was announced."""
@@ -115,6 +134,7 @@ class State:
             self._flag = torch.zeros(1, dtype=torch.int64, device=dev)
         self._flag.fill_(seen)
         c.allreduce_max_(self._flag)
+        c.wait()                 # with a deadline: a lost peer surfaces here as HorovodInternalError, not as a hang
         agreed = int(self._flag.item())
         if agreed > self._known_generation:
             self._pending_generation = agreed
@@ -128,9 +148,12 @@ class TorchState(State):
         super().__init__(**kwargs)
         self.model = model
         self.optimizer = optimizer
-        self._host = None        # pinned host copies of the arenas
-        self._host_extra = None  # deep copy of non-parameter state (buffers)
-        self._event = None
+        self._host = None        # two sets of pinned host copies of the arenas: last commit + the one being staged
+        self._host_extras = None # deep copies of non-parameter state (buffers), per set
+        self._events = None      # CUDA event fencing each set's asynchronous copies
+        self._good = 0           # which set is the last confirmed commit
+        self._staged = False
+        self._staged_generic = None
         self.save()
 
     # -- what must be captured -------------------------------------------------------------------------
@@ -151,24 +174,43 @@ class TorchState(State):
         pnames = {n for n, _ in self.model.named_parameters()}
         return {k: v for k, v in self.model.state_dict().items() if k not in pnames}
 
-    def save(self):
-        self._save_scalars()
+    def _stage(self):
+        State._stage(self)
         arenas = self._arenas() if (self.model is not None or self.optimizer is not None) else None
         if arenas is None:
             # generic fallback for objects we do not manage flat: plain deep copies (host logic only)
-            self._generic = (copy.deepcopy(self.model.state_dict()) if self.model is not None else None,
-                             copy.deepcopy(self.optimizer.state_dict()) if self.optimizer is not None else None)
+            self._staged_generic = (copy.deepcopy(self.model.state_dict()) if self.model is not None else None,
+                                    copy.deepcopy(self.optimizer.state_dict()) if self.optimizer is not None else None)
             return
         nat = _native.get()
-        if self._host is None or len(self._host) != len(arenas) or any(
-                h.numel() * h.element_size() < a.numel() * a.element_size() for h, a in zip(self._host, arenas)):
-            self._host = [torch.empty(a.shape, dtype=a.dtype, pin_memory=a.is_cuda) for a in arenas]
-        for a, hbuf in zip(arenas, self._host):
-            nat.state_snapshot(a, hbuf)
+        spare = 1 - self._good
+        if self._host is None:
+            self._host = [None, None]
+            self._events = [None, None]
+            self._host_extras = [None, None]
+        hb = self._host[spare]
+        if hb is None or len(hb) != len(arenas) or any(
+                h.numel() * h.element_size() < a.numel() * a.element_size() for h, a in zip(hb, arenas)):
+            hb = self._host[spare] = [torch.empty(a.shape, dtype=a.dtype, pin_memory=a.is_cuda) for a in arenas]
+        if self._events[spare] is not None:
+            self._events[spare].synchronize()          # an older copy into this buffer has long finished; be sure
+        for a, hbuf in zip(arenas, hb):
+            nat.state_snapshot(a, hbuf)                # asynchronous device -> pinned host copy on the current stream
         if torch.cuda.is_available() and arenas and arenas[0].is_cuda:
-            self._event = torch.cuda.Event()
-            self._event.record()
-        self._host_extra = {k: v.detach().to("cpu", copy=True) for k, v in self._extra_state().items()}
+            ev = torch.cuda.Event()
+            ev.record()
+            self._events[spare] = ev
+        self._host_extras[spare] = {k: v.detach().to("cpu", copy=True) for k, v in self._extra_state().items()}
+        self._staged = True
+
+    def _promote(self):
+        State._promote(self)
+        if getattr(self, "_staged_generic", None) is not None:
+            self._generic = self._staged_generic
+            self._staged_generic = None
+        if getattr(self, "_staged", False):
+            self._good = 1 - self._good
+            self._staged = False
 
     def restore(self):
         self._restore_scalars()
@@ -180,18 +222,20 @@ class TorchState(State):
             if os_ is not None:
                 self.optimizer.load_state_dict(os_)
             return
-        if self._event is not None:
-            self._event.synchronize()
+        self._staged = False                           # a staged-but-unconfirmed commit is dropped
+        if self._events[self._good] is not None:
+            self._events[self._good].synchronize()
         nat = _native.get()
-        for a, hbuf in zip(arenas, self._host):
+        for a, hbuf in zip(arenas, self._host[self._good]):
             nat.state_restore(a, hbuf)
         fused = getattr(self.optimizer, "_fused", None)
         if fused is not None:
             torch.cuda.current_stream().synchronize() if torch.cuda.is_available() else None
             fused.set_steps_from_device()
-        if self._host_extra:
+        extra = self._host_extras[self._good]
+        if extra:
             sd = self.model.state_dict()
-            for k, v in self._host_extra.items():
+            for k, v in extra.items():
                 sd[k].copy_(v)
 
     def sync(self):
@@ -202,7 +246,38 @@ class TorchState(State):
         if self.optimizer is not None and getattr(self.optimizer, "_fused", None) is not None:
             h.broadcast_optimizer_state(self.optimizer, root_rank=0)
         self._sync_scalars()
+        c = h._ctx.comm
+        if c is not None:
+            c.wait()             # the broadcasts have landed (deadline: a peer lost during the sync raises here)
         self.save()
+
+
+def _recover_membership(failed_comm, state):
+    """After a failed collective: the survivors of the broken ring agree on who is left and publish it as the next
+    membership plan (what horovod's driver does with its host-discovery script, ref: horovod_mnist_elastic.py:108).
+    Every survivor registers under the broken ring's tag; the first to arrive waits a grace period for the others,
+    then writes the plan; everybody adopts it in _reset()."""
+    import os
+    h = _hvd()
+    store = h._ctx.store
+    if store is None or failed_comm is None:
+        return
+    grace = float(os.environ.get("DDP_ELASTIC_GRACE_S", "5"))
+    tag = f"{_ALIVE_KEY}/{failed_comm.generation}"
+    store.set(f"{tag}/{h._ctx.global_rank}", b"1")
+    first = store.add(f"{tag}/arrivals", 1) == 1
+    known = state._known_generation
+    if first:
+        time.sleep(grace)
+        alive = [r for r in failed_comm.ranks if store.check([f"{tag}/{r}"])]
+        gen = max(_read_plan(store)[0], known) + 1
+        store.set(_PLAN_KEY, pickle.dumps((gen, alive)))
+    else:
+        deadline = time.monotonic() + 10 * grace + 30
+        while _read_plan(store)[0] <= known:
+            if time.monotonic() > deadline:
+                raise RuntimeError("elastic recovery: no membership plan was published after a failed collective")
+            time.sleep(0.05)
 
 
 def _reset(state):
@@ -242,11 +317,23 @@ def run(func):
             try:
                 return func(state, *args, **kwargs)
             except h.HorovodInternalError:
+                t_interrupt = time.perf_counter()
+                # a peer is lost: make sure nothing of the broken ring is still running, roll back to the last
+                # commit, and let the survivors agree on the next membership
+                failed = h._ctx.comm
+                if failed is not None:
+                    failed.abort(failed.broken or "collective failed")
+                if torch.cuda.is_available():
+                    try:
+                        torch.cuda.synchronize()
+                    except RuntimeError:
+                        pass
                 state.restore()
+                _recover_membership(failed, state)
                 skip_sync = False
             except h.HostsUpdatedInterrupt as e:
+                t_interrupt = time.perf_counter()
                 skip_sync = e.skip_sync
-            t_interrupt = time.perf_counter()
             _reset(state)
             state.on_reset()
 

@@ -25,8 +25,10 @@ from .optim import FusedUpdater, _arena_from
 Average, Sum = "Average", "Sum"
 
 
-class HorovodInternalError(RuntimeError):
-    """A collective failed (peer lost).  elastic.run restores the last commit and re-forms the ring."""
+# A collective failed, reported an asynchronous error or missed its deadline (peer lost): raised by every collective /
+# peer-memory entry point of the C-ABI wrapper and by Communicator.wait().  elastic.run restores the last commit and
+# re-forms the ring over the survivors (ref: horovod/horovod_mnist_elastic.py:55).
+HorovodInternalError = _native.CollectiveError
 
 
 class HostsUpdatedInterrupt(RuntimeError):
@@ -114,7 +116,13 @@ def reform(ranks, generation=None):
     """Re-form the ring over ``ranks`` (global ranks).  Processes not listed become standbys (comm None).
     This is what hvd.shutdown()+hvd.init() do inside horovod's elastic reset."""
     if _ctx.comm is not None:
-        torch.cuda.synchronize() if torch.cuda.is_available() else None
+        if _ctx.comm.broken is None:
+            torch.cuda.synchronize() if torch.cuda.is_available() else None
+        else:                                 # the ring was aborted: its kernels have exited, nothing orderly to wait for
+            try:
+                torch.cuda.synchronize() if torch.cuda.is_available() else None
+            except RuntimeError:
+                pass
         _ctx.comm.destroy()
     generation = _ctx.generation if generation is None else generation
     _ctx.attempt = _ctx.attempt + 1 if generation == _ctx.generation else 0

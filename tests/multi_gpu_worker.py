@@ -337,6 +337,70 @@ def main():
     log(f"elastic {W}->{len(half)}->{W} ok, reset sizes seen by rank 0: {events}, re-formation latency (interrupt -> new NCCL ring -> "
         f"state broadcast) ms: {lat}")
     dist.barrier()
+
+    # 6. LOST PEER (ref: horovod/horovod_mnist_elastic.py:55 -- @hvd.elastic.run retries after a failed collective).
+    #    The last rank exits in the middle of an epoch without telling anybody.  The survivors' next allreduce can never
+    #    finish: the deadline in commit() aborts the ring (ncclCommAbort), HorovodInternalError reaches elastic.run, which
+    #    restores the last CONFIRMED commit, lets the survivors agree on the new membership through the store, re-forms
+    #    the ring over W-1 ranks, re-syncs from rank 0, runs the reset callbacks, and training finishes.
+    if W >= 2:
+        os.environ["DDP_ELASTIC_GRACE_S"] = "2"
+        victim = W - 1
+        torch.manual_seed(50 + R)
+        model2 = pkg.Net().cuda().train()
+        opt2 = hvd.DistributedOptimizer(torch.optim.AdamW(model2.parameters(), lr=lr / math.sqrt(hvd.size())),
+                                        named_parameters=model2.named_parameters())
+        sizes2, last_commit, restored = [], [None, None], []
+
+        def on_reset2():
+            for g in opt2.param_groups:
+                g["lr"] = lr / math.sqrt(hvd.size())
+            sizes2.append(hvd.size())
+            restored.append((state2.batch, state2.batch == last_commit[0] and torch.equal(model2.flat_params, last_commit[1])))
+
+        @hvd.elastic.run
+        def train2(state):
+            sampler = pkg.DistributedSampler(ds, num_replicas=hvd.size(), rank=hvd.rank())
+            loader = pkg.DeviceLoader(ds, 128, sampler)
+            for batch_idx, (x, y) in enumerate(loader):
+                if batch_idx >= 30:
+                    break
+                if batch_idx < state.batch:
+                    continue
+                if batch_idx == 12 and hvd.size() == W and R == victim:
+                    torch.cuda.synchronize()
+                    os._exit(0)                                  # gone: no goodbye, no plan
+                opt2.zero_grad(); F.nll_loss(model2(x), y).backward(); opt2.step()
+                if batch_idx % 5 == 0:
+                    state.commit()
+                    last_commit[0], last_commit[1] = state.batch, model2.flat_params.clone()
+                state.batch = batch_idx
+
+        hvd._require().timeout_s = 4.0                           # the deadline for this ring's collectives
+        state2 = hvd.elastic.TorchState(model2, opt2, batch=0)
+        state2.register_reset_callbacks([on_reset2])
+        t_fail = __import__("time").perf_counter()
+        train2(state2)
+        c2 = hvd._require()
+
+        def same_on_ring(t, name):                               # the job-wide torch group still lists the dead rank
+            hi, neg = t.clone(), -t
+            c2.allreduce_max_(hi); c2.allreduce_max_(neg); c2.wait()
+            assert torch.equal(hi, -neg), f"{name}: replicas diverged"
+
+        assert hvd.size() == W - 1 and sizes2 == [W - 1], (hvd.size(), sizes2)
+        # what restore() brought back is bit-for-bit the state of the last confirmed commit (batch 10's), not the
+        # commit that was being staged when the ring died
+        assert len(restored) == 1 and restored[0][1], restored
+        assert abs(opt2.param_groups[0]["lr"] - lr / math.sqrt(W - 1)) < 1e-12
+        same_on_ring(model2.flat_params, "params after peer loss")
+        log(f"lost peer: rank {victim} exited at batch 12; survivors raised HorovodInternalError, restored the commit of "
+            f"batch {restored[0][0]}, re-formed a {W - 1}-rank ring and finished (detection + recovery latency "
+            f"{[round(v) for v in hvd.elastic.reset_latencies_ms[-1:]]} ms incl. the 2 s grace period)")
+        if R == 0:
+            print("MULTI_GPU_OK", flush=True)
+        sys.stdout.flush()
+        os._exit(0)                                              # the torch process group cannot be shut down collectively any more
     dist.destroy_process_group()
     if R == 0:
         print("MULTI_GPU_OK", flush=True)
