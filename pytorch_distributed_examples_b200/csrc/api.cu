@@ -28,6 +28,12 @@ bool pdl_enabled() {
   return v == 1;
 }
 
+bool wgrad2_tc() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("DDP_W2_SPARSE"); v = (e && e[0] == '1') ? 0 : 1; }
+  return v == 1;
+}
+
 bool bwd_dense() {
   static int v = -1;
   if (v < 0) { const char* e = getenv("DDP_BWD_DENSE"); v = (e && e[0] == '1') ? 1 : 0; }

@@ -104,6 +104,9 @@ int launch_conv2_wgrad_sp(const float* da2, const float* a2, const uint8_t* idx2
                           float* partials, int B, int* parts_out, cudaStream_t stream, bool pdl);
 int launch_conv2_dgrad_sp(const float* params, const float* da2, const float* a2, const uint8_t* idx2, const float* a1,
                           float drop_scale, float* dp1, int B, cudaStream_t stream);
+int launch_conv2_wgrad_tc(const float* da2, const float* a2, const uint8_t* idx2, const float* a1, float drop_scale,
+                          float* partials, int B, int* parts_out, cudaStream_t stream, bool pdl);   // conv2_wgrad_tc.cu
+bool wgrad2_tc();                        // api.cu: false when DDP_W2_SPARSE=1 (A/B switch: the sparse FFMA2 conv2 weight gradient)
 bool bwd_dense();                        // api.cu: true when DDP_BWD_DENSE=1 (A/B switch: the dense conv2 backward kernels)
 // per-kernel event timing (api.cu); mark(i) records event i on `stream` when profiling is on
 void prof_mark(int idx, cudaStream_t stream);

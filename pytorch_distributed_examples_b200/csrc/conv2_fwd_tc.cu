@@ -22,6 +22,7 @@
 // Pipelines: full/empty mbarriers over a 3-stage ring of k-steps (producer <-> MMA) and tmem_full/tmem_empty
 // over two accumulator buffers (MMA <-> epilogue), so the epilogue of group g overlaps the MMAs of group g+1.
 #include "common.cuh"
+#include "tc_common.cuh"
 
 namespace ddp {
 namespace tc2 {
@@ -61,57 +62,7 @@ constexpr int THREADS = 352;                // 4 epilogue + 4 producer + 3 MMA-i
 constexpr int DCOLS = 2 * NPAD;              // accumulator columns per tile: [hi*hi + lo*hi | hi*lo]
 constexpr int TMEM_COLS = 512;              // 2 buffers x 3 tiles x 64 columns = 384 -> next power of two
 
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
-  // un-swizzled K-major: LBO = byte stride between k-chunks (16 B of K), SBO = byte stride between 8-row groups
-  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)((lbo >> 4) & 0x3FFFu) << 16) |
-         ((uint64_t)((sbo >> 4) & 0x3FFFu) << 32) | ((uint64_t)1 << 46);
-}
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-  asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" :: "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  uint32_t done = 0;
-  uint32_t spins = 0;
-  while (!done) {
-    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.b32 %0, 1, 0, p;\n\t}"
-                 : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
-    if (++spins > (1u << 26)) __trap();   // a protocol bug must abort the launch, never hang the GPU
-  }
-}
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-               "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
-               :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
-  asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-               "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-                 "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
-                 "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
-                 "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-               : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ float rna_tf32(float v) {      // round-to-nearest (ties away) to the 10-bit tf32 mantissa
-  uint32_t r;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
-  return __uint_as_float(r);
-}
-__device__ __forceinline__ void split_tf32(float v, float& hi, float& lo) {
-  // v = hi + lo with both parts exactly representable in tf32 (the tensor core would otherwise TRUNCATE the
-  // 13 low mantissa bits, a biased 2^-20 error); v - hi is exact in fp32, and rounding it leaves 2^-22 of |v|
-  hi = rna_tf32(v);
-  lo = rna_tf32(v - hi);
-}
+using namespace ::ddp::tc;
 
 __global__ void __launch_bounds__(THREADS, 1)
 conv2_fwd_tc_kernel(const float* __restrict__ params, const float* __restrict__ a1,

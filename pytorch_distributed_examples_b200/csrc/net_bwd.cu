@@ -6,6 +6,7 @@
 //   K_R   fixed-order reduction of the per-CTA partials into the gradient bucket
 // Weight gradients are accumulated in registers across all samples a CTA sees and
 // written once per CTA; there are no floating-point atomics anywhere.
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace ddp {
@@ -700,7 +701,9 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
   // by itself (forking was tried there: the CTAs do not co-reside, and shrinking the grids to make them fit lost 30 %),
   // but up to B = 1024 the machine is mostly empty and the step is a latency chain: there conv2_wgrad runs on the
   // library's side stream beside dgrad and joins before the reduction (captured as a fork/join in a CUDA graph).
-  bool fork = B <= 1024 && !prof_enabled();
+  static int fork_max_b = -1;
+  if (fork_max_b < 0) { const char* e = getenv("DDP_FORK_MAX_B"); fork_max_b = e ? atoi(e) : 1024; }
+  bool fork = B <= fork_max_b && !prof_enabled();
   cudaStream_t wstream = stream;
   cudaEvent_t join_ev = nullptr;
   if (fork) {
@@ -714,6 +717,8 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
   }
   const bool dense = bwd_dense();
   auto launch_wgrad2 = [&]() -> int {
+    if (!dense && wgrad2_tc())
+      return launch_conv2_wgrad_tc(sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale, sc.partials, B, &parts_c2, wstream, !fork);
     if (!dense)
       return launch_conv2_wgrad_sp(sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale, sc.partials, B, &parts_c2, wstream, !fork);
     DDP_CUDA(launch_pdl(conv2_wgrad_kernel, dim3(parts_c2), dim3(W2_THREADS), W2_SMEM, wstream, !fork, sc.da2, ws.a2, ws.idx2, ws.a1,
