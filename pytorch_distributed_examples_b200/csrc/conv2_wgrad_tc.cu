@@ -13,10 +13,17 @@
 // or shared-memory pipes on this shape.)  Accumulation runs in TMEM over all samples of a persistent CTA; the
 // epilogue folds the four phases back into dW and writes one partial row per CTA (reduced in fixed order by K_R).
 //
+// Shared-memory bandwidth is what bounds a small-N tcgen05 kernel (an MMA that reads a 128x8 A tile from shared memory
+// spends more time fetching it than multiplying), so A' never touches shared memory: each producer thread owns one ROW
+// of A' (= one TMEM lane), gathers its 8 values of the k-step from the raw a1 tile, splits them into tf32 hi/lo in
+// registers and writes them straight into TMEM with tcgen05.st; the MMAs take A from TMEM and only the small G tile
+// (80 x 8) from shared memory.
+//
 // Warp roles (288 threads, 1 CTA/SM):
 //   warps 0-7  producers: the sample's raw tiles (a1, a2, da2, idx2) arrive by cp.async.bulk (3-deep ring, mbarrier
-//              complete_tx); per k-step (8 cells = half a sample) they gather A' (stride-2 reads), build G, split both
-//              into tf32 hi/lo and store 16-byte k-chunks into a 3-stage operand ring (un-swizzled K-major planes)
+//              complete_tx); per k-step (8 cells = half a sample) warp w fills the TMEM lanes 32*(w%4).. of its M-tiles
+//              (warps 0-3: tiles 0 and 2, warps 4-7: tile 1) and 40 threads of warps 4-5 build G (hi/lo, un-swizzled
+//              K-major 16-byte chunks) in a 3-stage ring
 //   warp 8     one lane issues 9 MMAs per k-step (3 M-tiles x {hi*hi, hi*lo, lo*hi}) and the commits; owns TMEM
 //   warps 0-3  after the last k-step: tcgen05.ld the accumulators, phase fold through shared memory
 #include "common.cuh"
@@ -27,26 +34,32 @@ namespace wtc {
 using namespace ::ddp::tc;
 
 constexpr int MROWS = 360;                  // (ci, kh', kw') = 10 x 6 x 6
-constexpr int MPAD = 384;                   // 3 M-tiles of 128
+constexpr int MPAD = 384;                   // 3 M-tiles of 128 (rows 360..383 are zero)
+static_assert(MPAD == 3 * 128, "three M-tiles");
 constexpr int MT = 3;
 constexpr int NB = 80;                      // (phase, co) = 4 x 20
 constexpr int TCOL = 96;                    // TMEM column stride between the tiles' accumulators
-constexpr int TMEM_COLS = 512;              // 3 x 96 = 288 -> next power of two
+constexpr int TMEM_COLS = 512;              // 3 x 96 accumulator columns + 3 stages x 3 tiles x 16 operand columns = 432
 constexpr int STAGES = 3;
-constexpr int A_PLANE = MPAD * 16;          // bytes of one k-chunk plane of A' (4 k values x 384 rows)
-constexpr int A_HL = 2 * A_PLANE;           // one k-step of hi (or lo)
-constexpr int B_PLANE = NB * 16;
-constexpr int B_HL = 2 * B_PLANE;
-constexpr int STAGE_BYTES = 2 * A_HL + 2 * B_HL;                       // A_hi | A_lo | B_hi | B_lo = 29,696
+constexpr int ACOL0 = MT * TCOL;            // first operand column: stage s, tile t -> ACOL0 + (s*3 + t)*16 (+8 for lo)
+constexpr int B_PLANE = NB * 16;            // bytes of one k-chunk plane of G (4 k values x 80 rows)
+constexpr int B_HL = 2 * B_PLANE;           // one k-step of hi (or lo)
+constexpr int STAGE_BYTES = 2 * B_HL;       // B_hi | B_lo = 5,120
 constexpr int RAWS = 3;
 constexpr int RAW_BYTES = A1_PER * 4 + 2 * A2_PER * 4 + A2_PER;        // a1 | a2 | da2 | idx2 = 8,640
 constexpr int PROD_THREADS = 256;
 constexpr int THREADS = PROD_THREADS + 32;
-constexpr int ITEMS = 2 * MROWS + 2 * NB;   // 16-byte chunks to build per k-step: 720 of A', 160 of G
 constexpr int DS = 81;                      // row stride of the staged D' (floats)
 constexpr int SMEM_MAIN = MROWS * DS * 4 > STAGES * STAGE_BYTES + RAWS * RAW_BYTES ? MROWS * DS * 4
                                                                                     : STAGES * STAGE_BYTES + RAWS * RAW_BYTES;
 constexpr int SMEM_BYTES = ((SMEM_MAIN + 127) / 128) * 128 + 256;
+
+// A from tensor memory (128 lanes x 8 columns of tf32), B from shared memory
+__device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+               "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+               :: "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
 
 __global__ void __launch_bounds__(THREADS, 1)
 conv2_wgrad_tc_kernel(const float* __restrict__ da2, const float* __restrict__ a2,
@@ -88,26 +101,21 @@ conv2_wgrad_tc_kernel(const float* __restrict__ da2, const float* __restrict__ a
 
   if (warp < 8) {
     // ======================= producers =======================
-    // chunk i = tid + 256*q of a k-step is fixed per thread: decode it once
-    int src[4], dst[4], phq[4];
-    bool isA[4], on[4];
+    // this thread's rows of A' (= its TMEM lane in tiles t0 and, for warps 0-3, tile 2) are fixed: decode them once
+    const int quad = warp & 3, lrow = quad * 32 + lane;             // TMEM lane this thread may write
+    const int t0 = warp < 4 ? 0 : 1, nrows = warp < 4 ? 2 : 1;
+    int src[2];
+    bool live[2];
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const int i = tid + PROD_THREADS * q;
-      on[q] = i < ITEMS;
-      isA[q] = i < 2 * MROWS;
-      if (isA[q]) {
-        const int plane = i / MROWS, m = i % MROWS, ci = m / 36, khp = (m % 36) / 6, kwp = m % 6;
-        src[q] = ci * 144 + (2 * plane + khp) * P1 + kwp;          // + 48*j: cell row py = 2j + plane starts at row 2*py
-        dst[q] = plane * A_PLANE + m * 16;
-        phq[q] = 0;
-      } else {
-        const int jx = (on[q] ? i : 2 * MROWS) - 2 * MROWS, plane = jx / NB, nn = jx % NB;
-        src[q] = (nn % C2) * 16 + plane * 4;                        // + 8*j: entries (co, py = 2j + plane, px 0..3)
-        dst[q] = 2 * A_HL + plane * B_PLANE + nn * 16;
-        phq[q] = nn / C2;
-      }
+    for (int r = 0; r < 2; ++r) {
+      const int m = (t0 + 2 * r) * 128 + lrow;
+      live[r] = r < nrows && m < MROWS;
+      const int mm = live[r] ? m : 0, ci = mm / 36, khp = (mm % 36) / 6, kwp = mm % 6;
+      src[r] = ci * 144 + khp * P1 + kwp;                           // + (4j + 2*plane)*12 + 2*px
     }
+    // G: thread 128 + 2*co + plane builds the four phase rows of (co, plane) from one look at the entries
+    const bool doB = tid >= 128 && tid < 128 + 2 * C2;
+    const int bco = (tid - 128) >> 1, bplane = (tid - 128) & 1;
     auto issue_raw = [&](int k) {                                   // thread 0: raw tiles of the CTA's k-th sample
       const size_t b = size_t(blockIdx.x) + size_t(k) * gridDim.x;
       unsigned char* r = raws + (k % RAWS) * RAW_BYTES;
@@ -139,36 +147,57 @@ conv2_wgrad_tc_kernel(const float* __restrict__ da2, const float* __restrict__ a
 #pragma unroll 1
       for (int j = 0; j < 2; ++j, ++it) {
         const int slot = it % STAGES;
-        if (it >= STAGES) mbar_wait(&empty_bar[slot], ((it / STAGES) - 1) & 1);
-        unsigned char* st = ring + slot * STAGE_BYTES;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          if (!on[q]) continue;
-          float v[4];
-          int lo_off;
-          if (isA[q]) {
-            const float* s = a1_s + src[q] + 48 * j;
-            v[0] = s[0]; v[1] = s[2]; v[2] = s[4]; v[3] = s[6];
-            lo_off = A_HL;
-          } else {
-            const int e0 = src[q] + 8 * j;
-            const float4 a = *reinterpret_cast<const float4*>(a2_s + e0);
-            const float4 d = *reinterpret_cast<const float4*>(da2_s + e0);
-            const unsigned ids = *reinterpret_cast<const unsigned*>(id_s + e0);
-            const unsigned ph = unsigned(phq[q]);
-            v[0] = (a.x > 0.f && ((ids) & 3u) == ph) ? d.x * drop_scale : 0.f;
-            v[1] = (a.y > 0.f && ((ids >> 8) & 3u) == ph) ? d.y * drop_scale : 0.f;
-            v[2] = (a.z > 0.f && ((ids >> 16) & 3u) == ph) ? d.z * drop_scale : 0.f;
-            v[3] = (a.w > 0.f && ((ids >> 24) & 3u) == ph) ? d.w * drop_scale : 0.f;
-            lo_off = B_HL;
-          }
-          float hi[4], lo[4];
-#pragma unroll
-          for (int e = 0; e < 4; ++e) split_tf32(v[e], hi[e], lo[e]);
-          *reinterpret_cast<float4*>(st + dst[q]) = make_float4(hi[0], hi[1], hi[2], hi[3]);
-          *reinterpret_cast<float4*>(st + dst[q] + lo_off) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+        if (it >= STAGES) {
+          mbar_wait(&empty_bar[slot], ((it / STAGES) - 1) & 1);     // the MMAs that read this stage have finished
+          asm volatile("tcgen05.fence::after_thread_sync;");
         }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+          if (r >= nrows) continue;                                 // warp-uniform
+          uint32_t hi[8], lo[8];
+          const float* s0 = a1_s + src[r] + 48 * j;
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {                             // k = plane*4 + px
+            float v = live[r] ? s0[(e >> 2) * 2 * P1 + 2 * (e & 3)] : 0.f;
+            float h, l;
+            split_tf32(v, h, l);
+            hi[e] = __float_as_uint(h); lo[e] = __float_as_uint(l);
+          }
+          const uint32_t ta = tmem + (uint32_t(quad * 32) << 16) + uint32_t(ACOL0 + (slot * MT + t0 + 2 * r) * 16);
+          asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                       :: "r"(ta), "r"(hi[0]), "r"(hi[1]), "r"(hi[2]), "r"(hi[3]), "r"(hi[4]), "r"(hi[5]), "r"(hi[6]), "r"(hi[7]) : "memory");
+          asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                       :: "r"(ta + 8), "r"(lo[0]), "r"(lo[1]), "r"(lo[2]), "r"(lo[3]), "r"(lo[4]), "r"(lo[5]), "r"(lo[6]), "r"(lo[7]) : "memory");
+        }
+        if (doB) {
+          unsigned char* st = ring + slot * STAGE_BYTES;
+          const int e0 = bco * 16 + (2 * j + bplane) * 4;           // entries (co, py = 2j + plane, px 0..3)
+          const float4 a = *reinterpret_cast<const float4*>(a2_s + e0);
+          const float4 d = *reinterpret_cast<const float4*>(da2_s + e0);
+          const unsigned ids = *reinterpret_cast<const unsigned*>(id_s + e0);
+          float g[4];
+          g[0] = a.x > 0.f ? d.x * drop_scale : 0.f;
+          g[1] = a.y > 0.f ? d.y * drop_scale : 0.f;
+          g[2] = a.z > 0.f ? d.z * drop_scale : 0.f;
+          g[3] = a.w > 0.f ? d.w * drop_scale : 0.f;
+          float gh[4], gl[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) split_tf32(g[e], gh[e], gl[e]);
+#pragma unroll
+          for (int ph = 0; ph < 4; ++ph) {
+            float4 h4, l4;
+            h4.x = ((ids) & 3u) == unsigned(ph) ? gh[0] : 0.f;        l4.x = ((ids) & 3u) == unsigned(ph) ? gl[0] : 0.f;
+            h4.y = ((ids >> 8) & 3u) == unsigned(ph) ? gh[1] : 0.f;   l4.y = ((ids >> 8) & 3u) == unsigned(ph) ? gl[1] : 0.f;
+            h4.z = ((ids >> 16) & 3u) == unsigned(ph) ? gh[2] : 0.f;  l4.z = ((ids >> 16) & 3u) == unsigned(ph) ? gl[2] : 0.f;
+            h4.w = ((ids >> 24) & 3u) == unsigned(ph) ? gh[3] : 0.f;  l4.w = ((ids >> 24) & 3u) == unsigned(ph) ? gl[3] : 0.f;
+            const int off = bplane * B_PLANE + (ph * C2 + bco) * 16;
+            *reinterpret_cast<float4*>(st + off) = h4;
+            *reinterpret_cast<float4*>(st + B_HL + off) = l4;
+          }
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        }
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+        asm volatile("tcgen05.fence::before_thread_sync;");
         mbar_arrive(&full_bar[slot]);
       }
       if (tid < C2) {
@@ -191,16 +220,15 @@ conv2_wgrad_tc_kernel(const float* __restrict__ da2, const float* __restrict__ a
       mbar_wait(&full_bar[slot], (it / STAGES) & 1);
       asm volatile("tcgen05.fence::after_thread_sync;");
       const uint32_t sb = ring_base + slot * STAGE_BYTES;
-      const uint64_t b_hi = make_desc(sb + 2 * A_HL, B_PLANE, 128);
-      const uint64_t b_lo = make_desc(sb + 2 * A_HL + B_HL, B_PLANE, 128);
+      const uint64_t b_hi = make_desc(sb, B_PLANE, 128);
+      const uint64_t b_lo = make_desc(sb + B_HL, B_PLANE, 128);
 #pragma unroll
       for (int t = 0; t < MT; ++t) {
-        const uint64_t a_hi = make_desc(sb + t * 128 * 16, A_PLANE, 128);
-        const uint64_t a_lo = make_desc(sb + A_HL + t * 128 * 16, A_PLANE, 128);
+        const uint32_t a_hi = tmem + uint32_t(ACOL0 + (slot * MT + t) * 16), a_lo = a_hi + 8;
         const uint32_t d = tmem + uint32_t(t * TCOL);
-        umma_tf32(d, a_hi, b_hi, idesc, it ? 1u : 0u);
-        umma_tf32(d, a_hi, b_lo, idesc, 1u);
-        umma_tf32(d, a_lo, b_hi, idesc, 1u);
+        umma_tf32_ts(d, a_hi, b_hi, idesc, it ? 1u : 0u);
+        umma_tf32_ts(d, a_hi, b_lo, idesc, 1u);
+        umma_tf32_ts(d, a_lo, b_hi, idesc, 1u);
       }
       umma_commit(&empty_bar[slot]);             // stage reusable once these MMAs have read it
     }
