@@ -30,7 +30,7 @@ bool pdl_enabled() {
 
 bool wgrad2_tc() {
   static int v = -1;
-  if (v < 0) { const char* e = getenv("DDP_W2_SPARSE"); v = (e && e[0] == '1') ? 0 : 1; }
+  if (v < 0) { const char* e = getenv("DDP_W2_TC"); v = (e && e[0] == '1') ? 1 : 0; }
   return v == 1;
 }
 

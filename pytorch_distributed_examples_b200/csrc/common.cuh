@@ -106,7 +106,7 @@ int launch_conv2_dgrad_sp(const float* params, const float* da2, const float* a2
                           float drop_scale, float* dp1, int B, cudaStream_t stream);
 int launch_conv2_wgrad_tc(const float* da2, const float* a2, const uint8_t* idx2, const float* a1, float drop_scale,
                           float* partials, int B, int* parts_out, cudaStream_t stream, bool pdl);   // conv2_wgrad_tc.cu
-bool wgrad2_tc();                        // api.cu: false when DDP_W2_SPARSE=1 (A/B switch: the sparse FFMA2 conv2 weight gradient)
+bool wgrad2_tc();                        // api.cu: true when DDP_W2_TC=1 (A/B switch: the tcgen05 conv2 weight gradient; default is the sparse FFMA2 kernel, which is faster)
 bool bwd_dense();                        // api.cu: true when DDP_BWD_DENSE=1 (A/B switch: the dense conv2 backward kernels)
 // per-kernel event timing (api.cu); mark(i) records event i on `stream` when profiling is on
 void prof_mark(int idx, cudaStream_t stream);
@@ -169,6 +169,16 @@ __device__ __forceinline__ void mbarrier_wait(uint64_t* bar, uint32_t parity) {
     if (++spins > (1u << 26)) __trap();
   }
 }
+
+// ---- packed fp32 pairs: fma.rn.f32x2 does two IEEE fp32 FMAs in ONE issue slot (same FMA pipe throughput) -------------
+__device__ __forceinline__ void fma2(unsigned long long& d, unsigned long long a, unsigned long long b) {
+  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b));
+}
+__device__ __forceinline__ unsigned long long pack2(float a, float b) {
+  return (unsigned long long)__float_as_uint(a) | ((unsigned long long)__float_as_uint(b) << 32);
+}
+__device__ __forceinline__ float lo_f(unsigned long long v) { return __uint_as_float(unsigned(v)); }
+__device__ __forceinline__ float hi_f(unsigned long long v) { return __uint_as_float(unsigned(v >> 32)); }
 
 // ---- Philox4x32-10 (counter-based; same constants as Random123 / curand) ------
 struct Philox4 { uint32_t x, y, z, w; };

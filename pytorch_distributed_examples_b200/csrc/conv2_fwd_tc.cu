@@ -3,22 +3,24 @@
 // result stays within the fp32 parity bar (ref: horovod/mnist_horovod.py:20;  SURVEY §7.3 H1).
 //
 // GEMM view, per group of 4 samples:
-//   A'[r][k]   r = s*96 + y*8 + ox   (s<4, y<12, ox<8)        k = kw*10 + ci  (50, zero-padded to 56)
+//   A'[r][k]   r = y*32 + s*8 + ox   (y<12, s<4, ox<8)        k = kw*10 + ci  (50, zero-padded to 56)
 //              = a1[s][ci][y][ox+kw]          -- im2col along kw only (5x duplication, built on the fly)
 //   B[kh][k][n] = W[n][ci][kh][kw]            n = output channel (20, zero-padded to 32)
-//   D[m][n] = sum_kh  A'[m + 8*kh][:] . B[kh][:, n]          m = s*96 + oy*8 + ox
-// The kh taps are NOT materialised: shifting the conv window down by one row is a shift of 8 rows of A',
-// i.e. +128 bytes on the start address of the (un-swizzled, K-major) shared-memory descriptor.  Rows with
-// oy >= 8 are computed and discarded (M efficiency 2/3) so that every tile is a plain 128-row MMA.
+//   D[m][n] = sum_kh  A'[m + 32*kh][:] . B[kh][:, n]         m = oy*32 + s*8 + ox,  oy < 8
+// The kh taps are NOT materialised: shifting the conv window down by one row is a shift of 32 rows of A',
+// i.e. +512 bytes on the start address of the (un-swizzled, K-major) shared-memory descriptor.  With the image row
+// as the SLOWEST row index the 8 valid output rows of the 4 samples are rows 0..255 of D: two full 128-row tiles,
+// no discarded rows (a sample-major order needs three tiles per group, a third of them garbage).
 // 3xTF32 with two MMAs per (kh, k-step): A_hi x [B_hi | B_lo] (N=64: hi*hi in columns 0-31, hi*lo in 32-63) and
 // A_lo x B_hi (N=32, accumulating into columns 0-31); the epilogue adds the two column groups.  The MMAs are bound
 // by the shared-memory fetch of the 4 KB A tile (N is tiny), so reading A_hi once instead of twice is worth 27%.
 //
 // Warp roles (352 threads, 1 CTA/SM, persistent over groups):
-//   warps 0-3  epilogue: tcgen05.ld accumulators -> bias, dropout, 2x2 max-pool by warp shuffles, ReLU -> a2, idx2
+//   warps 0-3  epilogue: tcgen05.ld accumulators -> bias, dropout, 2x2 max-pool (rows oy, oy+1 live in neighbouring warps:
+//              exchanged through shared memory), ReLU -> a2, idx2
 //   warps 4-7  producers: the group's raw a1 (23 KB) arrives by ONE cp.async.bulk (TMA engine, mbarrier complete_tx),
 //              prefetched a group ahead; producers read it from smem, split into tf32 hi / lo, 16-byte STS into the ring
-//   warps 8-10 one elected lane each issues the tcgen05.mma / tcgen05.commit of one M-tile; warp 8 owns the TMEM allocation
+//   warps 8-9  one elected lane each issues the tcgen05.mma / tcgen05.commit of one M-tile; warp 8 owns the TMEM allocation
 // Pipelines: full/empty mbarriers over a 3-stage ring of k-steps (producer <-> MMA) and tmem_full/tmem_empty
 // over two accumulator buffers (MMA <-> epilogue), so the epilogue of group g overlaps the MMAs of group g+1.
 #include "common.cuh"
@@ -39,10 +41,10 @@ __device__ unsigned long long g_tc_dbg[160 * 16];
 #endif
 
 constexpr int G = 4;                        // samples per group
-constexpr int ROWS_PER_S = 96;              // 12 rows x 8 columns of A' per sample
-constexpr int ROWS = G * ROWS_PER_S;        // 384 = 3 M-tiles
-constexpr int ROWS_PAD = ROWS + 32;         // + the deepest kh shift (4*8 rows)
-constexpr int MT = ROWS / 128;              // 3 M-tiles per group
+constexpr int ROWS = 12 * G * 8;            // rows of A': (y, s, ox) = 384
+constexpr int ROWS_PAD = ROWS;              // the deepest kh shift (4*32 rows) of the last D row (255) is row 383
+constexpr int KH_ROWS = G * 8;              // one conv row down = 32 rows of A'
+constexpr int MT = 2;                       // M-tiles per group: D rows (oy < 8, s, ox) = 256
 constexpr int KSTEPS = 7;                   // 56 / 8
 constexpr int NPAD = 32;                    // output channels padded to the MMA N
 constexpr int STAGES = 3;
@@ -57,10 +59,11 @@ constexpr int SMEM_B = 5 * KSTEPS * B_TILE; // 71,680
 constexpr int RAW_BYTES = G * A1_PER * 4;    // one group's a1: 23,040 B
 constexpr int SMEM_RAW = 2 * RAW_BYTES;     // double-buffered
 constexpr int SMEM_MISC = 1024;             // barriers, tmem pointer, bias, noise
-constexpr int SMEM_BYTES = SMEM_A + SMEM_B + SMEM_RAW + SMEM_MISC;
-constexpr int THREADS = 352;                // 4 epilogue + 4 producer + 3 MMA-issuer warps
+constexpr int SMEM_XCH = 4 * C2 * 32 * 4;   // pooling exchange: [epilogue warp][channel][lane]
+constexpr int SMEM_BYTES = SMEM_A + SMEM_B + SMEM_RAW + SMEM_MISC + SMEM_XCH;
+constexpr int THREADS = 320;                // 4 epilogue + 4 producer + 2 MMA-issuer warps
 constexpr int DCOLS = 2 * NPAD;              // accumulator columns per tile: [hi*hi + lo*hi | hi*lo]
-constexpr int TMEM_COLS = 512;              // 2 buffers x 3 tiles x 64 columns = 384 -> next power of two
+constexpr int TMEM_COLS = 256;              // 2 buffers x 2 tiles x 64 columns
 
 using namespace ::ddp::tc;
 
@@ -83,6 +86,7 @@ conv2_fwd_tc_kernel(const float* __restrict__ params, const float* __restrict__ 
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(rempty_bar + 2);
   float* bias_s = reinterpret_cast<float*>(misc + 128);              // [32]
   float* noise_s = bias_s + 32;                                      // [2 buffers][G][20]
+  float* xch_s = reinterpret_cast<float*>(misc + SMEM_MISC);         // [4 warps][20][32]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   pdl_trigger();
@@ -137,9 +141,9 @@ conv2_fwd_tc_kernel(const float* __restrict__ params, const float* __restrict__ 
 #pragma unroll
     for (int q = 0; q < 3; ++q) {
       const int r = pt + 128 * q;
-      const int sidx = r / ROWS_PER_S, rem = r % ROWS_PER_S;
+      const int y = r / KH_ROWS, sidx = (r % KH_ROWS) >> 3, ox = r & 7;
       row_s[q] = sidx;
-      row_src[q] = sidx * A1_PER + (rem >> 3) * P1 + (rem & 7);     // + ci*144 + kw per k
+      row_src[q] = sidx * A1_PER + y * P1 + ox;                     // + ci*144 + kw per k
     }
     auto issue_raw = [&](int grp, int rb) {         // one elected thread: bulk-copy the group's a1 into raw_s[rb]
       const int b0 = grp * G;
@@ -221,7 +225,7 @@ conv2_fwd_tc_kernel(const float* __restrict__ params, const float* __restrict__ 
           {
 #pragma unroll
             for (int kh = 0; kh < 5; ++kh) {
-              const uint64_t rows = uint64_t(t * 128 + kh * 8);
+              const uint64_t rows = uint64_t(t * 128 + kh * KH_ROWS);
               const uint64_t bsel = uint64_t((kh * KSTEPS * B_TILE) >> 4);
               umma_tf32(d, a_hi0 + rows, b0 + bsel, idesc64, (j | kh) ? 1u : 0u);   // hi*hi | hi*lo
               umma_tf32(d, a_lo0 + rows, b0 + bsel, idesc32, 1u);                   // + lo*hi into columns 0-31
@@ -260,19 +264,28 @@ conv2_fwd_tc_kernel(const float* __restrict__ params, const float* __restrict__ 
         const uint32_t taddr = tmem + (uint32_t(warp * 32) << 16) + uint32_t((buf * MT + t) * DCOLS);
         tmem_ld32(taddr, acc);
         tmem_ld32(taddr + NPAD, acc_hl);
-        const int m = t * 128 + warp * 32 + lane;
-        const int s = m / ROWS_PER_S, rem = m % ROWS_PER_S, oy = rem >> 3, ox = rem & 7;
+        // this warp's 32 lanes are conv row oy = 4t + warp of the 4 samples: lane = s*8 + ox
+        const int s = lane >> 3, ox = lane & 7;
         const int b = b0 + s;
-        const bool writer = (oy < 8) && !(oy & 1) && !(ox & 1) && (b < B);
-        const int pp = (oy >> 1) * 4 + (ox >> 1);
         const float* nzs = nz + s * C2;
+        float* mine = xch_s + warp * (C2 * 32);
 #pragma unroll
-        for (int co = 0; co < C2; ++co) {
-          const float v00 = (__uint_as_float(acc[co]) + __uint_as_float(acc_hl[co]) + bias_s[co]) * nzs[co];
-          const float v01 = __shfl_xor_sync(0xffffffffu, v00, 1);    // (oy, ox+1)
-          const float v10 = __shfl_xor_sync(0xffffffffu, v00, 8);    // (oy+1, ox)
-          const float v11 = __shfl_xor_sync(0xffffffffu, v00, 9);    // (oy+1, ox+1)
-          float best = v00; int bi = 0;                              // first-max in window scan order
+        for (int co = 0; co < C2; ++co)
+          mine[co * 32 + lane] = (__uint_as_float(acc[co]) + __uint_as_float(acc_hl[co]) + bias_s[co]) * nzs[co];
+        // the pool partner row lives in the neighbouring warp (warps 0|1 and 2|3 pair up); each warp of a pair pools
+        // half of the channels: first-max in window scan order (oy,ox), (oy,ox+1), (oy+1,ox), (oy+1,ox+1)
+        asm volatile("bar.sync %0, 64;" :: "r"(2 + (warp >> 1)) : "memory");
+        const float* top = xch_s + (warp & ~1) * (C2 * 32);
+        const float* bot = top + C2 * 32;
+        const bool writer = !(ox & 1) && (b < B);
+        const int pp = (2 * t + (warp >> 1)) * 4 + (ox >> 1);
+        const int c0 = (warp & 1) * (C2 / 2);
+#pragma unroll
+        for (int cc = 0; cc < C2 / 2; ++cc) {
+          const int co = c0 + cc;
+          const float v00 = top[co * 32 + lane], v01 = top[co * 32 + (lane ^ 1)];
+          const float v10 = bot[co * 32 + lane], v11 = bot[co * 32 + (lane ^ 1)];
+          float best = v00; int bi = 0;
           if (v01 > best) { best = v01; bi = 1; }
           if (v10 > best) { best = v10; bi = 2; }
           if (v11 > best) { best = v11; bi = 3; }
@@ -282,6 +295,7 @@ conv2_fwd_tc_kernel(const float* __restrict__ params, const float* __restrict__ 
             idx2[o] = uint8_t(bi);
           }
         }
+        asm volatile("bar.sync %0, 64;" :: "r"(2 + (warp >> 1)) : "memory");   // exchange buffers are free again
       }
       asm volatile("tcgen05.fence::before_thread_sync;");
       mbar_arrive(&tempty_bar[buf]);

@@ -18,14 +18,6 @@
 
 namespace ddp {
 
-__device__ __forceinline__ void fma2(unsigned long long& d, unsigned long long a, unsigned long long b) {
-  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b));
-}
-__device__ __forceinline__ unsigned long long pack2(float a, float b) {
-  return (unsigned long long)__float_as_uint(a) | ((unsigned long long)__float_as_uint(b) << 32);
-}
-__device__ __forceinline__ float lo_f(unsigned long long v) { return __uint_as_float(unsigned(v)); }
-__device__ __forceinline__ float hi_f(unsigned long long v) { return __uint_as_float(unsigned(v >> 32)); }
 __device__ __forceinline__ void mbarrier_arrive(uint64_t* bar) {
   asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" :: "r"(smem_addr_u32(bar)) : "memory");
 }

@@ -68,32 +68,36 @@ conv1_fwd_kernel(const float* __restrict__ params, const float* __restrict__ x,
         float2 v = *reinterpret_cast<const float2*>(ip + r * IMG + 2 * j);
         patch[r][2 * j] = v.x; patch[r][2 * j + 1] = v.y;
       }
-    float acc[4][C1];
+    // accumulators as packed channel pairs: one FFMA2 (fma.rn.f32x2) updates channels (2p, 2p+1) of a position
+    unsigned long long acc[4][5];
 #pragma unroll
     for (int q = 0; q < 4; ++q)
 #pragma unroll
-      for (int c = 0; c < C1; ++c) acc[q][c] = b_s[c];
+      for (int p2 = 0; p2 < 5; ++p2) acc[q][p2] = pack2(b_s[2 * p2], b_s[2 * p2 + 1]);
 #pragma unroll
     for (int kh = 0; kh < 5; ++kh)
 #pragma unroll
       for (int kw = 0; kw < 5; ++kw) {
-        const float4* wp = reinterpret_cast<const float4*>(w_s + (kh * 5 + kw) * 12);
-        float4 w0 = wp[0], w1 = wp[1], w2 = wp[2];
-        float w[C1] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w, w2.x, w2.y};
+        const ulonglong2* wp = reinterpret_cast<const ulonglong2*>(w_s + (kh * 5 + kw) * 12);
+        const ulonglong2 w01 = wp[0], w23 = wp[1];
+        const unsigned long long w4 = *reinterpret_cast<const unsigned long long*>(w_s + (kh * 5 + kw) * 12 + 8);
+        const unsigned long long w[5] = {w01.x, w01.y, w23.x, w23.y, w4};
 #pragma unroll
         for (int dy = 0; dy < 2; ++dy)
 #pragma unroll
           for (int dx = 0; dx < 2; ++dx) {
-            float v = patch[dy + kh][dx + kw];
+            const float v = patch[dy + kh][dx + kw];
+            const unsigned long long v2 = pack2(v, v);
 #pragma unroll
-            for (int c = 0; c < C1; ++c) acc[dy * 2 + dx][c] = fmaf(v, w[c], acc[dy * 2 + dx][c]);
+            for (int p2 = 0; p2 < 5; ++p2) fma2(acc[dy * 2 + dx][p2], v2, w[p2]);
           }
       }
     const size_t ob = size_t(b0 + s) * A1_PER + p;
 #pragma unroll
     for (int c = 0; c < C1; ++c) {
       float best; int bi;
-      pool4(acc[0][c], acc[1][c], acc[2][c], acc[3][c], best, bi);
+      if (c & 1) pool4(hi_f(acc[0][c >> 1]), hi_f(acc[1][c >> 1]), hi_f(acc[2][c >> 1]), hi_f(acc[3][c >> 1]), best, bi);
+      else pool4(lo_f(acc[0][c >> 1]), lo_f(acc[1][c >> 1]), lo_f(acc[2][c >> 1]), lo_f(acc[3][c >> 1]), best, bi);
       a1[ob + c * 144] = fmaxf(best, 0.f);
       idx1[ob + c * 144] = uint8_t(bi);
     }
