@@ -101,6 +101,20 @@ int ddp_net_backward(const float* params, const float* x, const float* logp,
                      int training, int64_t batch, const void* workspace,
                      void* scratch, float* grad_bucket, void* stream);
 
+/* Forward + backward of ONE training step in a single call: what the reference loop does between zero_grad() and
+ * optimizer.step() when the loss is F.nll_loss(output, target) --
+ * ref: horovod/mnist_horovod.py:61-63 (output = model(data); loss = F.nll_loss(output, target); loss.backward());
+ *      pytorch_elastic/mnist_ddp_elastic.py:72-74 (Trainer._run_batch).
+ * Same results as ddp_net_forward(training = 1, out_loss) followed by ddp_net_backward(dlogp = NULL, target), but the
+ * head (fc1 .. NLL and its backward) runs as ONE kernel: fc1.weight and the a2 tile are staged once, h / logp are not
+ * re-read, one launch less.  loss_scale multiplies the loss gradient (1.0 for the plain mean loss).
+ * out_argmax / out_correct / mask2d / mask1d / offset_dev may be NULL. */
+int ddp_net_train_fwdbwd(const float* params, const float* x, const int64_t* target,
+                         const float* mask2d, const float* mask1d, uint64_t seed, uint64_t offset,
+                         const int64_t* offset_dev, float loss_scale, int64_t batch, void* workspace,
+                         float* out_logp, float* out_loss, int64_t* out_argmax, int64_t* out_correct,
+                         void* scratch, float* grad_bucket, void* stream);
+
 /* ---- flatten-into-bucket (DDP Reducer copy / Horovod fusion buffer) ---------
  * torch: nn/parallel/distributed.py:1255-1280 (Reducer buckets);
  * ref: pytorch_elastic/mnist_ddp_elastic.py:58 (DDP wrap), horovod/mnist_horovod.py:53.

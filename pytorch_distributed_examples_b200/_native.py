@@ -47,6 +47,8 @@ SIGNATURES = {
     "ddp_net_scratch_bytes": (c_int64, [c_int64]),
     "ddp_net_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_uint64, c_uint64, c_void_p, c_int,
                                 c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "ddp_net_train_fwdbwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_uint64, c_uint64, c_void_p, c_float,
+                                     c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "ddp_net_backward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_int, c_int64,
                                  c_void_p, c_void_p, c_void_p, c_void_p]),
     "ddp_bucket_copy": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int,
@@ -179,6 +181,19 @@ class Native:
             _ptr(out_loss, "out_loss", torch.float32), _ptr(out_argmax, "out_argmax", torch.int64),
             _ptr(out_correct, "out_correct", torch.int64), _ptr(scratch, "scratch"), _stream())
         self._check(rc, "ddp_net_forward")
+
+    def net_train_fwdbwd(self, params, x, target, mask2d, mask1d, seed, offset, workspace, out_logp, out_loss, scratch,
+                         grad_bucket, loss_scale=1.0, out_argmax=None, out_correct=None, offset_dev=None):
+        """Forward + backward of one training step (fused head kernel); gradients land in ``grad_bucket``."""
+        rc = self.lib.ddp_net_train_fwdbwd(
+            _ptr(params, "params", torch.float32), _ptr(x, "x", torch.float32), _ptr(target, "target", torch.int64),
+            _ptr(mask2d, "mask2d", torch.float32), _ptr(mask1d, "mask1d", torch.float32),
+            int(seed) & (2 ** 64 - 1), int(offset) & (2 ** 64 - 1), _ptr(offset_dev, "offset_dev", torch.int64),
+            float(loss_scale), x.shape[0], _ptr(workspace, "workspace"), _ptr(out_logp, "out_logp", torch.float32),
+            _ptr(out_loss, "out_loss", torch.float32), _ptr(out_argmax, "out_argmax", torch.int64),
+            _ptr(out_correct, "out_correct", torch.int64), _ptr(scratch, "scratch"),
+            _ptr(grad_bucket, "grad_bucket", torch.float32), _stream())
+        self._check(rc, "ddp_net_train_fwdbwd")
 
     def net_backward(self, params, x, logp, dlogp, target, loss_scale, training, workspace, scratch, grad_bucket):
         rc = self.lib.ddp_net_backward(

@@ -99,6 +99,11 @@ int sm_count();
 // tensor-core conv2 forward (conv2_fwd_tc.cu)
 int launch_conv2_fwd_tc(const float* params, const float* a1, const float* mask2d, uint64_t seed, uint64_t offset,
                         const int64_t* offset_dev, int training, float* a2, uint8_t* idx2, int B, cudaStream_t stream);
+// launch helpers shared by ddp_net_forward / ddp_net_backward and the fused training entry point (head_fused.cu)
+int launch_fwd_convs(const float* params, const float* x, const float* mask2d, uint64_t seed, uint64_t offset,
+                     const int64_t* offset_dev, int training, const Workspace& ws, int B, cudaStream_t stream);
+int launch_bwd_after_head(const float* params, const float* x, int training, int B, const Workspace& ws, const Scratch& sc,
+                          int parts_head, float* grad_bucket, cudaStream_t stream);
 // sparse conv2 backward (net_bwd_sparse.cu): one visit per live (channel, pool cell) entry instead of dense 8x8 planes
 int launch_conv2_wgrad_sp(const float* da2, const float* a2, const uint8_t* idx2, const float* a1, float drop_scale,
                           float* partials, int B, int* parts_out, cudaStream_t stream, bool pdl);

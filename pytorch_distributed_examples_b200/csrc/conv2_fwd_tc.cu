@@ -56,7 +56,9 @@ constexpr int B_PLANE = B_ROWS * 16;        // one k-chunk plane: 1 KB
 constexpr int B_TILE = 2 * B_PLANE;         // one (kh, kstep): 2 KB
 constexpr int SMEM_A = STAGES * A_STAGE;    // 79,872
 constexpr int SMEM_B = 5 * KSTEPS * B_TILE; // 71,680
-constexpr int RAW_BYTES = G * A1_PER * 4;    // one group's a1: 23,040 B
+constexpr int RAW_S = A1_PER + 8;             // per-sample stride of the raw tile (floats): == 8 mod 32, so the 32 lanes
+                                             // (s, ox) of a producer warp read 32 distinct banks
+constexpr int RAW_BYTES = G * RAW_S * 4;     // one group's a1: 23,168 B
 constexpr int SMEM_RAW = 2 * RAW_BYTES;     // double-buffered
 constexpr int SMEM_MISC = 1024;             // barriers, tmem pointer, bias, noise
 constexpr int SMEM_XCH = 4 * C2 * 32 * 4;   // pooling exchange: [epilogue warp][channel][lane]
@@ -75,7 +77,7 @@ conv2_fwd_tc_kernel(const float* __restrict__ params, const float* __restrict__ 
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   unsigned char* a_ring = smem_raw;
   unsigned char* b_mat = smem_raw + SMEM_A;
-  float* raw_s = reinterpret_cast<float*>(b_mat + SMEM_B);          // [2][G*1440]
+  float* raw_s = reinterpret_cast<float*>(b_mat + SMEM_B);          // [2][G][RAW_S]
   unsigned char* misc = b_mat + SMEM_B + SMEM_RAW;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(misc);            // [STAGES]
   uint64_t* empty_bar = full_bar + STAGES;                           // [STAGES]
@@ -143,16 +145,17 @@ conv2_fwd_tc_kernel(const float* __restrict__ params, const float* __restrict__ 
       const int r = pt + 128 * q;
       const int y = r / KH_ROWS, sidx = (r % KH_ROWS) >> 3, ox = r & 7;
       row_s[q] = sidx;
-      row_src[q] = sidx * A1_PER + y * P1 + ox;                     // + ci*144 + kw per k
+      row_src[q] = sidx * RAW_S + y * P1 + ox;                      // + ci*144 + kw per k
     }
     auto issue_raw = [&](int grp, int rb) {         // one elected thread: bulk-copy the group's a1 into raw_s[rb]
       const int b0 = grp * G;
-      const uint32_t bytes = uint32_t(min(G, B - b0)) * (A1_PER * 4);
+      const int nv = min(G, B - b0);
       asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}"
-                   :: "r"(smem_u32(&rfull_bar[rb])), "r"(bytes) : "memory");
-      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                   :: "r"(smem_u32(raw_s + rb * (G * A1_PER))), "l"(a1 + size_t(b0) * A1_PER), "r"(bytes),
-                      "r"(smem_u32(&rfull_bar[rb])) : "memory");
+                   :: "r"(smem_u32(&rfull_bar[rb])), "r"(uint32_t(nv) * (A1_PER * 4)) : "memory");
+      for (int sm = 0; sm < nv; ++sm)               // one copy per sample into its padded slot
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     :: "r"(smem_u32(raw_s + rb * (G * RAW_S) + sm * RAW_S)), "l"(a1 + size_t(b0 + sm) * A1_PER),
+                        "r"(uint32_t(A1_PER * 4)), "r"(smem_u32(&rfull_bar[rb])) : "memory");
     };
     if (pt == 0 && blockIdx.x < ngroups) issue_raw(blockIdx.x, 0);
     for (int grp = blockIdx.x; grp < ngroups; grp += gridDim.x, ++gi) {
@@ -164,7 +167,7 @@ conv2_fwd_tc_kernel(const float* __restrict__ params, const float* __restrict__ 
         issue_raw(grp + gridDim.x, rb ^ 1);
       }
       { TC_T0(tw); mbar_wait(&rfull_bar[rb], (gi >> 1) & 1); if (pt == 0) TC_ACC(1, tw); }   // slot 1: producer waits raw tile
-      const float* raw = raw_s + rb * (G * A1_PER);
+      const float* raw = raw_s + rb * (G * RAW_S);
       for (int j = 0; j < KSTEPS; ++j, ++it) {
         const int slot = it % STAGES;
         { TC_T0(tw); if (it >= STAGES) mbar_wait(&empty_bar[slot], ((it / STAGES) - 1) & 1); if (pt == 0) TC_ACC(2, tw); }  // slot 2: producer waits empty

@@ -653,49 +653,31 @@ reduce_partials_kernel(const float* __restrict__ partials, int parts_c1, int par
   }
 }
 
-}  // namespace ddp
 
-using namespace ddp;
+static int set_bwd_attrs() {   // function attributes are per device: a process may drive several GPUs (ddp_set_device per host thread)
+  static bool attr_done[64] = {false};
+  int dev = 0;
+  DDP_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 64 && !attr_done[dev]) {
+    DDP_CUDA(cudaFuncSetAttribute(head_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HB_SMEM));
+    DDP_CUDA(cudaFuncSetAttribute(conv2_dgrad_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, D2_SMEM));
+    DDP_CUDA(cudaFuncSetAttribute(conv2_dgrad_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, D2_SMEM));
+    DDP_CUDA(cudaFuncSetAttribute(conv2_dgrad_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, D2_SMEM));
+    DDP_CUDA(cudaFuncSetAttribute(conv2_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, W2_SMEM));
+    DDP_CUDA(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, W1_SMEM));
+    attr_done[dev] = true;
+  }
+  return 0;
+}
 
-extern "C" int ddp_net_backward(const float* params, const float* x, const float* logp,
-                                const float* dlogp, const int64_t* target, float loss_scale,
-                                int training, int64_t batch, const void* workspace, void* scratch,
-                                float* grad_bucket, void* stream_) {
-  DDP_REQUIRE(params && x && logp && workspace && scratch && grad_bucket, "null required pointer");
-  DDP_REQUIRE(dlogp || target, "either dlogp or target must be given");
-  DDP_REQUIRE(batch >= 1 && batch <= (int64_t(1) << 24), "batch out of range");
-  DDP_REQUIRE(aligned16(params) && aligned16(x) && aligned16(workspace) && aligned16(scratch),
-              "params/x/workspace/scratch must be 16-byte aligned");
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  const int B = int(batch);
+// Everything behind the head: conv2 dgrad / wgrad, conv1 wgrad, fixed-order reduction of the partial rows into the
+// bucket.  `parts_head` = number of partial rows the head kernel (K_B3 or the fused training head) wrote.
+int launch_bwd_after_head(const float* params, const float* x, int training, int B, const Workspace& ws, const Scratch& sc,
+                          int parts_head, float* grad_bucket, cudaStream_t stream) {
+  if (int rc = set_bwd_attrs()) return rc;
   const int sms = sm_count();
-  Workspace ws = carve_workspace(const_cast<void*>(workspace), batch);
-  Scratch sc = carve_scratch(scratch, batch);
   const float drop_scale = training ? 2.f : 1.f;
-  const float nll_coef = -loss_scale / float(B);
-
-  {   // function attributes are per device: a process may drive several GPUs (ddp_set_device per host thread)
-    static bool attr_done[64] = {false};
-    int dev = 0;
-    DDP_CUDA(cudaGetDevice(&dev));
-    if (dev >= 0 && dev < 64 && !attr_done[dev]) {
-      DDP_CUDA(cudaFuncSetAttribute(head_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HB_SMEM));
-      DDP_CUDA(cudaFuncSetAttribute(conv2_dgrad_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, D2_SMEM));
-      DDP_CUDA(cudaFuncSetAttribute(conv2_dgrad_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, D2_SMEM));
-      DDP_CUDA(cudaFuncSetAttribute(conv2_dgrad_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, D2_SMEM));
-      DDP_CUDA(cudaFuncSetAttribute(conv2_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, W2_SMEM));
-      DDP_CUDA(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, W1_SMEM));
-      attr_done[dev] = true;
-    }
-  }
-  int parts_head, parts_c2, parts_c1;
-  prof_mark(4, stream);
-  {
-    int ntiles = (B + HT - 1) / HT;
-    parts_head = ntiles < sms ? ntiles : sms;
-    DDP_CUDA(launch_pdl(head_bwd_kernel, dim3(parts_head), dim3(HB_THREADS), HB_SMEM, stream, true, params, ws.a2, ws.h, logp,
-                        dlogp, target, nll_coef, drop_scale, sc.da2, sc.partials, B));
-  }
+  int parts_c2, parts_c1;
   prof_mark(5, stream);
   // conv2_wgrad depends on head_bwd only, not on dgrad -> conv1_wgrad.  At large batches every kernel fills the SMs
   // by itself (forking was tried there: the CTAs do not co-reside, and shrinking the grids to make them fit lost 30 %),
@@ -758,4 +740,35 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
   prof_mark(9, stream);
   DDP_CUDA(cudaGetLastError());
   return 0;
+}
+}  // namespace ddp
+
+using namespace ddp;
+
+extern "C" int ddp_net_backward(const float* params, const float* x, const float* logp,
+                                const float* dlogp, const int64_t* target, float loss_scale,
+                                int training, int64_t batch, const void* workspace, void* scratch,
+                                float* grad_bucket, void* stream_) {
+  DDP_REQUIRE(params && x && logp && workspace && scratch && grad_bucket, "null required pointer");
+  DDP_REQUIRE(dlogp || target, "either dlogp or target must be given");
+  DDP_REQUIRE(batch >= 1 && batch <= (int64_t(1) << 24), "batch out of range");
+  DDP_REQUIRE(aligned16(params) && aligned16(x) && aligned16(workspace) && aligned16(scratch),
+              "params/x/workspace/scratch must be 16-byte aligned");
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int B = int(batch);
+  const int sms = sm_count();
+  Workspace ws = carve_workspace(const_cast<void*>(workspace), batch);
+  Scratch sc = carve_scratch(scratch, batch);
+  const float drop_scale = training ? 2.f : 1.f;
+  const float nll_coef = -loss_scale / float(B);
+  if (int rc = set_bwd_attrs()) return rc;
+  int parts_head;
+  prof_mark(4, stream);
+  {
+    int ntiles = (B + HT - 1) / HT;
+    parts_head = ntiles < sms ? ntiles : sms;
+    DDP_CUDA(launch_pdl(head_bwd_kernel, dim3(parts_head), dim3(HB_THREADS), HB_SMEM, stream, true, params, ws.a2, ws.h, logp,
+                        dlogp, target, nll_coef, drop_scale, sc.da2, sc.partials, B));
+  }
+  return launch_bwd_after_head(params, x, training, B, ws, sc, parts_head, grad_bucket, stream);
 }

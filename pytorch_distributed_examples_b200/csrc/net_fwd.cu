@@ -317,6 +317,25 @@ head_fwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
 
 }  // namespace ddp
 
+namespace ddp {
+// K_F1 + K_F2: x -> a1, idx1 -> a2, idx2 (shared by ddp_net_forward and the fused training entry point)
+int launch_fwd_convs(const float* params, const float* x, const float* mask2d, uint64_t seed, uint64_t offset,
+                     const int64_t* offset_dev, int training, const Workspace& ws, int B, cudaStream_t stream) {
+  const int sms = sm_count();
+  prof_mark(0, stream);
+  {
+    int npairs = (B + 1) / 2;
+    int grid = npairs < sms * 2 ? npairs : sms * 2;
+    DDP_CUDA(launch_pdl(conv1_fwd_kernel, dim3(grid), dim3(F1_THREADS), 0, stream, true, params, x, ws.a1, ws.idx1, B));
+  }
+  prof_mark(1, stream);
+  if (int rc = launch_conv2_fwd_tc(params, ws.a1, mask2d, seed, offset, offset_dev, training, ws.a2, ws.idx2, B, stream))
+    return rc;
+  prof_mark(2, stream);
+  return 0;
+}
+}  // namespace ddp
+
 using namespace ddp;
 
 extern "C" int ddp_net_forward(const float* params, const float* x, const int64_t* target,
@@ -335,25 +354,18 @@ extern "C" int ddp_net_forward(const float* params, const float* x, const int64_
   const int sms = sm_count();
   Workspace ws = carve_workspace(workspace, batch);
 
-  prof_mark(0, stream);
-  {
-    int npairs = (B + 1) / 2;
-    int grid = npairs < sms * 2 ? npairs : sms * 2;
-    DDP_CUDA(launch_pdl(conv1_fwd_kernel, dim3(grid), dim3(F1_THREADS), 0, stream, true, params, x, ws.a1, ws.idx1, B));
-  }
-  prof_mark(1, stream);
-  if (int rc = launch_conv2_fwd_tc(params, ws.a1, mask2d, seed, offset, offset_dev, training, ws.a2, ws.idx2, B, stream))
-    return rc;
-  prof_mark(2, stream);
+  if (int rc = launch_fwd_convs(params, x, mask2d, seed, offset, offset_dev, training, ws, B, stream)) return rc;
   {
     int ntiles = (B + HT - 1) / HT;
     int grid = ntiles < MAX_PARTS ? ntiles : MAX_PARTS;   // one loss partial per CTA
     Scratch sc{};
     if (scratch) sc = carve_scratch(scratch, batch);
-    static bool attr_done = false;
-    if (!attr_done) {
+    static bool attr_done[64] = {false};       // function attributes are per device
+    int dev = 0;
+    DDP_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !attr_done[dev]) {
       DDP_CUDA(cudaFuncSetAttribute(head_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HF_SMEM));
-      attr_done = true;
+      attr_done[dev] = true;
     }
     DDP_CUDA(launch_pdl(head_fwd_kernel, dim3(grid), dim3(HF_THREADS), HF_SMEM, stream, true,
                         params, ws.a2, target, mask1d, seed, offset, offset_dev, training, ws.h, out_logp, out_loss, out_argmax,

@@ -16,13 +16,15 @@ more input bytes than the L2 holds.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from . import _native
 from .net import Net
 from .optim import FusedUpdater
 
-KERNELS_PER_STEP = 3 + 5 + 1   # forward, backward(+reduce), fused update (which also advances the step counter)
+KERNELS_PER_STEP = 2 + 1 + 4 + 1   # conv forward x2, fused head, backward x3 + reduce, fused update (also advances the step counter)
 
 
 class TrainStep:
@@ -63,6 +65,7 @@ class TrainStep:
         self._consumed = [None] * slots    # event: last step that read the slot finished
         self._u8 = None                    # per-slot uint8 staging buffers (stage_u8)
         self.use_graph = use_graph
+        self.fused_head = os.environ.get("DDP_SPLIT_HEAD", "0") != "1"    # A/B switch: separate head_fwd / head_bwd kernels
         self.graphs = None
         self._fingerprint = None
         self.kernel_launches_per_step = KERNELS_PER_STEP
@@ -80,9 +83,13 @@ class TrainStep:
         nat = _native.get()
         m, g = self.model, self.group
         x, y = self.xs[slot], self.ys[slot]
-        nat.net_forward(m._arena, x, y, None, None, m.dropout_seed, 0, True, self.ws, self.logp,
-                        out_loss=self.losses[slot], scratch=self.scratch, offset_dev=g.step_dev)
-        nat.net_backward(m._arena, x, self.logp, None, y, 1.0, True, self.ws, self.scratch, m._grad_arena)
+        if self.fused_head:      # forward + backward in one call, the head as ONE kernel (ddp_net_train_fwdbwd)
+            nat.net_train_fwdbwd(m._arena, x, y, None, None, m.dropout_seed, 0, self.ws, self.logp, self.losses[slot],
+                                 self.scratch, m._grad_arena, offset_dev=g.step_dev)
+        else:
+            nat.net_forward(m._arena, x, y, None, None, m.dropout_seed, 0, True, self.ws, self.logp,
+                            out_loss=self.losses[slot], scratch=self.scratch, offset_dev=g.step_dev)
+            nat.net_backward(m._arena, x, self.logp, None, y, 1.0, True, self.ws, self.scratch, m._grad_arena)
         g.bucket = m._grad_arena
         g.adopted = True
         if self.use_peer:

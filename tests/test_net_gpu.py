@@ -11,7 +11,7 @@ from oracle import net_oracle, synth_oracle
 pytestmark = pytest.mark.gpu
 
 
-def _run_fwd_bwd(nat, sd, x, y, m2, m1, training=True, use_dlogp=False, want_ws=False):
+def _run_fwd_bwd(nat, sd, x, y, m2, m1, training=True, use_dlogp=False, want_ws=False, fused=False):
     dev = "cuda"
     B = x.shape[0]
     arena = arena_from_state_dict(nat, sd)
@@ -21,10 +21,17 @@ def _run_fwd_bwd(nat, sd, x, y, m2, m1, training=True, use_dlogp=False, want_ws=
     logp = torch.empty(B, 10, device=dev)
     loss = torch.zeros(1, device=dev)
     am = torch.empty(B, dtype=torch.int64, device=dev)
+    bucket = torch.full((21848,), float("nan"), device=dev)
+    if fused:            # ddp_net_train_fwdbwd: forward + backward in one call, the head as one kernel
+        nat.net_train_fwdbwd(arena, xg, yg, None if m2 is None else m2.to(dev).contiguous(),
+                             None if m1 is None else m1.to(dev).contiguous(), 0, 0, ws, logp, loss, sc, bucket, out_argmax=am)
+        torch.cuda.synchronize()
+        if want_ws:
+            return logp, loss, am, bucket, saved_routing(ws, B)
+        return logp, loss, am, bucket
     nat.net_forward(arena, xg, yg, None if m2 is None else m2.to(dev).contiguous(),
                     None if m1 is None else m1.to(dev).contiguous(), 0, 0, training, ws, logp,
                     out_loss=loss, out_argmax=am, scratch=sc)
-    bucket = torch.full((21848,), float("nan"), device=dev)
     if use_dlogp:
         dlogp = torch.zeros(B, 10, device=dev)
         dlogp[torch.arange(B), yg] = -1.0 / B
@@ -38,11 +45,11 @@ def _run_fwd_bwd(nat, sd, x, y, m2, m1, training=True, use_dlogp=False, want_ws=
 
 
 @pytest.mark.parametrize("name", ["fwdbwd_b1.pt", "fwdbwd_b8.pt", "fwdbwd_b48.pt", "fwdbwd_b64.pt"])
-@pytest.mark.parametrize("use_dlogp", [False, True])
-def test_forward_backward_vs_reference_golden(native, name, use_dlogp):
+@pytest.mark.parametrize("mode", ["target", "dlogp", "fused"])
+def test_forward_backward_vs_reference_golden(native, name, mode):
     fx = load_golden(name)
     logp, loss, am, bucket = _run_fwd_bwd(native, fx["state_dict"], fx["x"], fx["y"], fx["mask2d"], fx["mask1d"],
-                                          use_dlogp=use_dlogp)
+                                          use_dlogp=mode == "dlogp", fused=mode == "fused")
     assert_close_scaled(logp, fx["logp"], name="logp")
     assert abs(loss.item() - fx["loss"].item()) <= RTOL * abs(fx["loss"].item())
     grads = split_arena(native, bucket)
@@ -90,6 +97,26 @@ def test_forward_backward_vs_oracle_ragged_sizes(native, B):
     flips, bad = count_routing_flips(saved, net_oracle.routing(sd, x, m2, m1), m2, m1)
     assert bad == 0, f"B={B}: {bad} gradient routes differ from the fp64 oracle away from any tie"
     assert flips <= 4, f"B={B}: {flips} routing flips"
+
+
+@pytest.mark.parametrize("B", [1, 15, 16, 17, 100, 1024, 4096])
+def test_fused_training_entry_point_equals_separate_calls(native, B):
+    """ddp_net_train_fwdbwd == ddp_net_forward + ddp_net_backward(target): same arithmetic, fused head kernel."""
+    torch.manual_seed(300 + B)
+    sd = {k: v.detach().clone() for k, v in net_oracle.OracleNet().state_dict().items()}
+    xn, yn = synth_oracle.synth_batch(5, np.arange(B) + 7 * B)
+    x, y = torch.from_numpy(xn), torch.from_numpy(yn)
+    g = torch.Generator().manual_seed(B)
+    m2 = torch.empty(B, 20).bernoulli_(0.5, generator=g)
+    m1 = torch.empty(B, 50).bernoulli_(0.5, generator=g)
+    lp_s, loss_s, am_s, bk_s = _run_fwd_bwd(native, sd, x, y, m2, m1)
+    lp_f, loss_f, am_f, bk_f = _run_fwd_bwd(native, sd, x, y, m2, m1, fused=True)
+    assert torch.equal(lp_s, lp_f) and torch.equal(am_s, am_f), "the fused head's forward must be bit-identical"
+    assert abs(loss_s.item() - loss_f.item()) <= 1e-6 * abs(loss_s.item())
+    assert_close_scaled(bk_f, bk_s, rtol=2e-6, name="fused vs separate gradients")     # partial-sum order differs only
+    # and it is deterministic
+    _, loss_f2, _, bk_f2 = _run_fwd_bwd(native, sd, x, y, m2, m1, fused=True)
+    assert torch.equal(bk_f, bk_f2) and torch.equal(loss_f, loss_f2)
 
 
 def test_full_size_batch_4096_properties(native):
