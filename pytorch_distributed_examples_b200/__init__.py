@@ -9,7 +9,7 @@ Drop-in surface:
     DistributedSampler       shard indices, bit-exact with torch          (sampler.py)
     hvd                      horovod.torch-compatible module              (hvd.py, elastic.py)
     allreduce_hook / HookState   DDP register_comm_hook seam              (ddp_hook.py)
-    save_snapshot / load_snapshot  snapshot.pt interchange                (snapshot.py)
+    save_snapshot / load_snapshot / AsyncSnapshotWriter  snapshot.pt interchange   (snapshot.py)
     evaluate                 Trainer.test / test(): fused count, all ranks  (evaluate.py)
 plus TrainStep (the graph-captured fast path), FusedOptimizer, SyntheticMNIST / DeviceLoader.
 """
@@ -20,12 +20,12 @@ from .sampler import DistributedSampler
 from .optim import FusedOptimizer, FusedUpdater
 from .data import SyntheticMNIST, DeviceLoader
 from .step import TrainStep
-from .snapshot import save_snapshot, load_snapshot
+from .snapshot import save_snapshot, load_snapshot, AsyncSnapshotWriter
 from .evaluate import evaluate
-from .ddp_hook import HookState, allreduce_hook, FusedUpdateHook
+from .ddp_hook import HookState, allreduce_hook, FusedUpdateHook, BufferBroadcast
 from . import hvd
 from . import elastic
 
 __all__ = ["Net", "Model", "DistributedSampler", "FusedOptimizer", "FusedUpdater", "SyntheticMNIST", "DeviceLoader",
-           "TrainStep", "save_snapshot", "load_snapshot", "evaluate", "HookState", "allreduce_hook", "FusedUpdateHook",
+           "TrainStep", "save_snapshot", "load_snapshot", "AsyncSnapshotWriter", "evaluate", "HookState", "allreduce_hook", "FusedUpdateHook", "BufferBroadcast",
            "hvd", "elastic"]

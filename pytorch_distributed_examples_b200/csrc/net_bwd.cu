@@ -622,37 +622,44 @@ __device__ __forceinline__ bool arena_is_pad(int e) {
          (e >= OFF_F1B + 50 && e < OFF_F2W) || (e >= OFF_F2B + 10);
 }
 constexpr int RP_WARPS = 32;
+// 1024 threads = 32 warps x 32 lanes; lane <-> one float4 (4 consecutive arena elements), warp w sums the partial rows
+// w, w+32, ... (all its 128-bit loads in flight at once), then warp 0 adds the 32 warp sums in order.
 __global__ void __launch_bounds__(RP_WARPS * 32)
 reduce_partials_kernel(const float* __restrict__ partials, int parts_c1, int parts_c2,
                        int parts_head, float* __restrict__ bucket) {
-  __shared__ float red[RP_WARPS][33];
+  __shared__ float4 red[RP_WARPS][33];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   pdl_trigger();
   pdl_wait();
-  const int e = blockIdx.x * 32 + lane;
-  float s = 0.f;
-  if (e < P_ARENA && !arena_is_pad(e)) {
+  const int e = (blockIdx.x * 32 + lane) * 4;          // every tensor starts at a multiple of 4 floats: no float4 straddles two
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (e < P_ARENA) {
     const int parts = e < OFF_C2W ? parts_c1 : (e < OFF_F1W ? parts_c2 : parts_head);
     const float* p = partials + e;
-    float v[(MAX_PARTS + RP_WARPS - 1) / RP_WARPS];
+    constexpr int Q = (MAX_PARTS + RP_WARPS - 1) / RP_WARPS;
+    float4 v[Q];
 #pragma unroll
-    for (int q = 0; q < (MAX_PARTS + RP_WARPS - 1) / RP_WARPS; ++q) {
+    for (int q = 0; q < Q; ++q) {
       const int i = warp + q * RP_WARPS;
-      v[q] = i < parts ? __ldcg(p + size_t(i) * P_ARENA) : 0.f;
+      v[q] = i < parts ? __ldcg(reinterpret_cast<const float4*>(p + size_t(i) * P_ARENA)) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
 #pragma unroll
-    for (int q = 0; q < (MAX_PARTS + RP_WARPS - 1) / RP_WARPS; ++q) s += v[q];
+    for (int q = 0; q < Q; ++q) { s.x += v[q].x; s.y += v[q].y; s.z += v[q].z; s.w += v[q].w; }
   }
   red[warp][lane] = s;
   __syncthreads();
   if (warp == 0 && e < P_ARENA) {
-    float t = 0.f;
+    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-    for (int w = 0; w < RP_WARPS; ++w) t += red[w][lane];
-    bucket[e] = t;
+    for (int w = 0; w < RP_WARPS; ++w) { const float4 r = red[w][lane]; t.x += r.x; t.y += r.y; t.z += r.z; t.w += r.w; }
+    // padding slots of the arena are never written by the producers: keep them zero
+    if (arena_is_pad(e)) t.x = 0.f;
+    if (arena_is_pad(e + 1)) t.y = 0.f;
+    if (arena_is_pad(e + 2)) t.z = 0.f;
+    if (arena_is_pad(e + 3)) t.w = 0.f;
+    *reinterpret_cast<float4*>(bucket + e) = t;
   }
 }
-
 
 static int set_bwd_attrs() {   // function attributes are per device: a process may drive several GPUs (ddp_set_device per host thread)
   static bool attr_done[64] = {false};
@@ -735,7 +742,7 @@ int launch_bwd_after_head(const float* params, const float* x, int training, int
   }
   prof_mark(8, stream);
   if (fork) DDP_CUDA(cudaStreamWaitEvent(stream, join_ev, 0));
-  DDP_CUDA(launch_pdl(reduce_partials_kernel, dim3((P_ARENA + 31) / 32), dim3(RP_WARPS * 32), 0, stream, true, sc.partials, parts_c1,
+  DDP_CUDA(launch_pdl(reduce_partials_kernel, dim3((P_ARENA / 4 + 31) / 32), dim3(RP_WARPS * 32), 0, stream, true, sc.partials, parts_c1,
                       parts_c2, parts_head, grad_bucket));
   prof_mark(9, stream);
   DDP_CUDA(cudaGetLastError());

@@ -4,75 +4,71 @@
 //   pixels  u8[784]: bytes of Philox4x32-10(counter=(i_lo, i_hi, blk, 0), key=seed), blk=0..48
 //   x = (float(u8) / 255 - 0.1307) / 0.3081      (IEEE fp32, same op order as torchvision)
 //   label   Philox(counter=(i_lo, i_hi, 49, 0)).x % 10
-// HBM-bound writer: 3,136 + 8 bytes per sample, 64 contiguous bytes per thread.
+// HBM-bound writer: 3,136 + 8 bytes per sample, 64 contiguous bytes per thread and loop trip.
 #include "common.cuh"
 
 namespace ddp {
 
-// the 16 pixels of block `blk` of sample `idx`, packed little-endian in 4 words; label returned via ref
-__device__ __forceinline__ void synth_block(uint64_t seed, uint64_t idx, int blk, uint32_t w[4], uint32_t& label) {
+// One CTA generates groups of SY_S samples.  What does not depend on the pixel is computed once and shared:
+//   * the stroke masks -- a function of (label, block) only: a 10 x 49 table per CTA (490 Philox calls, once);
+//   * the sample's label (one Philox call per sample instead of one per 64 bytes);
+//   * the ToTensor + Normalize value of each of the 256 possible pixel bytes (two IEEE divisions each, once),
+// so the streaming part is ONE Philox call, 16 table look-ups and four 128-bit stores per 64 bytes written.
+constexpr int SY_S = 32;                  // samples per group
+constexpr int SY_THREADS = 256;
+template <bool F32>
+__global__ void __launch_bounds__(SY_THREADS)
+synth_kernel(uint64_t seed, const int64_t* __restrict__ indices, int64_t base_index, int64_t batch,
+             float* __restrict__ out_x, uint8_t* __restrict__ out_px, int64_t* __restrict__ out_y) {
+  __shared__ uint32_t stroke_s[10 * 49];
+  __shared__ float lut_s[256];
+  __shared__ uint32_t label_s[SY_S];
   const uint32_t k0 = uint32_t(seed), k1 = uint32_t(seed >> 32);
-  label = philox4x32_10(uint32_t(idx), uint32_t(idx >> 32), 49u, 0u, k0, k1).x % 10u;
-  if (blk >= 49) return;
-  const Philox4 n = philox4x32_10(uint32_t(idx), uint32_t(idx >> 32), uint32_t(blk), 0u, k0, k1);
-  const uint32_t stroke = philox4x32_10(label, uint32_t(blk), 0x7E3Du, 0x5EEDu, k0, k1).x;
-  const uint32_t nz[4] = {n.x, n.y, n.z, n.w};
-#pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    uint32_t out = 0u;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const uint32_t noise = (nz[q] >> (8 * k)) & 0xffu;
-      const uint32_t px = (noise >> 1) + (((stroke >> (4 * q + k)) & 1u) ? 112u : 0u);
-      out |= px << (8 * k);
+  const int tid = threadIdx.x;
+  for (int i = tid; i < 10 * 49; i += SY_THREADS)
+    stroke_s[i] = philox4x32_10(uint32_t(i / 49), uint32_t(i % 49), 0x7E3Du, 0x5EEDu, k0, k1).x;
+  if (F32) lut_s[tid] = (float(tid) / 255.0f - 0.1307f) / 0.3081f;      // torchvision's op order, IEEE fp32
+  const int64_t ngroups = (batch + SY_S - 1) / SY_S;
+  for (int64_t grp = blockIdx.x; grp < ngroups; grp += gridDim.x) {
+    const int64_t b0 = grp * SY_S;
+    const int nvalid = int(batch - b0 < SY_S ? batch - b0 : SY_S);
+    __syncthreads();                                  // tables ready / the previous group's labels consumed
+    if (tid < nvalid) {
+      const uint64_t idx = uint64_t(indices ? indices[b0 + tid] : base_index + b0 + tid);
+      const uint32_t label = philox4x32_10(uint32_t(idx), uint32_t(idx >> 32), 49u, 0u, k0, k1).x % 10u;
+      label_s[tid] = label;
+      if (out_y) out_y[b0 + tid] = int64_t(label);
     }
-    w[q] = out;
-  }
-}
-
-__global__ void __launch_bounds__(256)
-synth_batch_kernel(uint64_t seed, const int64_t* __restrict__ indices, int64_t base_index, int64_t batch,
-                   float* __restrict__ out_x, int64_t* __restrict__ out_y) {
-  const int64_t t = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-  const int64_t b = t / 50;
-  const int blk = int(t % 50);
-  if (b >= batch) return;
-  const uint64_t idx = uint64_t(indices ? indices[b] : base_index + b);
-  uint32_t w[4], label;
-  synth_block(seed, idx, blk, w, label);
-  if (blk == 49) {
-    if (out_y) out_y[b] = int64_t(label);
-    return;
-  }
-  float4* o = reinterpret_cast<float4*>(out_x + b * IMG_PIX + blk * 16);
+    __syncthreads();
+    for (int t = tid; t < nvalid * 49; t += SY_THREADS) {
+      const int sl = t / 49, blk = t % 49;
+      const int64_t b = b0 + sl;
+      const uint64_t idx = uint64_t(indices ? indices[b] : base_index + b);
+      const Philox4 n = philox4x32_10(uint32_t(idx), uint32_t(idx >> 32), uint32_t(blk), 0u, k0, k1);
+      const uint32_t stroke = stroke_s[label_s[sl] * 49 + blk];
+      const uint32_t nz[4] = {n.x, n.y, n.z, n.w};
+      uint32_t w[4];
 #pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    float v[4];
+      for (int q = 0; q < 4; ++q) {
+        uint32_t out = 0u;
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      float u = float((w[q] >> (8 * k)) & 0xffu);
-      v[k] = (u / 255.0f - 0.1307f) / 0.3081f;
+        for (int k = 0; k < 4; ++k) {
+          const uint32_t noise = (nz[q] >> (8 * k)) & 0xffu;
+          const uint32_t px = (noise >> 1) + (((stroke >> (4 * q + k)) & 1u) ? 112u : 0u);
+          out |= px << (8 * k);
+        }
+        w[q] = out;
+      }
+      if (F32) {
+        float4* o = reinterpret_cast<float4*>(out_x + b * IMG_PIX + blk * 16);
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          o[q] = make_float4(lut_s[w[q] & 0xffu], lut_s[(w[q] >> 8) & 0xffu], lut_s[(w[q] >> 16) & 0xffu], lut_s[w[q] >> 24]);
+      } else {
+        *reinterpret_cast<uint4*>(out_px + b * IMG_PIX + blk * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+      }
     }
-    o[q] = make_float4(v[0], v[1], v[2], v[3]);
   }
-}
-
-// Raw-pixel variant: the 784 bytes of each sample as the dataset stores them (MNIST is uint8 on disk).
-__global__ void __launch_bounds__(256)
-synth_batch_u8_kernel(uint64_t seed, const int64_t* __restrict__ indices, int64_t base_index, int64_t batch,
-                      uint8_t* __restrict__ out_px, int64_t* __restrict__ out_y) {
-  const int64_t t = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-  const int64_t b = t / 50;
-  const int blk = int(t % 50);
-  if (b >= batch) return;
-  const uint64_t idx = uint64_t(indices ? indices[b] : base_index + b);
-  uint32_t w[4], label;
-  synth_block(seed, idx, blk, w, label);
-  if (blk == 49) {
-    if (out_y) out_y[b] = int64_t(label);
-    return;
-  }
-  *reinterpret_cast<uint4*>(out_px + b * IMG_PIX + blk * 16) = make_uint4(w[0], w[1], w[2], w[3]);
 }
 
 // ToTensor + Normalize on the device (ref: horovod/mnist_horovod.py:34-37): out = (u8/255 - mean)/std,
@@ -108,9 +104,10 @@ extern "C" int ddp_synth_batch_u8(uint64_t seed, const int64_t* indices, int64_t
   DDP_REQUIRE(batch >= 0, "negative batch");
   if (batch == 0) return 0;
   DDP_REQUIRE(out_px && aligned16(out_px), "out_px must be non-null and 16-byte aligned");
-  const int64_t threads = batch * 50;
-  synth_batch_u8_kernel<<<int((threads + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
-      seed, indices, base_index, batch, out_px, out_y);
+  const int64_t ngroups = (batch + SY_S - 1) / SY_S;
+  const int cap = sm_count() * 8;
+  synth_kernel<false><<<int(ngroups < cap ? ngroups : cap), SY_THREADS, 0, static_cast<cudaStream_t>(stream_)>>>(
+      seed, indices, base_index, batch, nullptr, out_px, out_y);
   DDP_CUDA(cudaGetLastError());
   return 0;
 }
@@ -133,9 +130,10 @@ extern "C" int ddp_synth_batch(uint64_t seed, const int64_t* indices, int64_t ba
   DDP_REQUIRE(batch >= 0, "negative batch");
   if (batch == 0) return 0;
   DDP_REQUIRE(out_x && aligned16(out_x), "out_x must be non-null and 16-byte aligned");
-  const int64_t threads = batch * 50;
-  synth_batch_kernel<<<int((threads + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
-      seed, indices, base_index, batch, out_x, out_y);
+  const int64_t ngroups = (batch + SY_S - 1) / SY_S;
+  const int cap = sm_count() * 8;
+  synth_kernel<true><<<int(ngroups < cap ? ngroups : cap), SY_THREADS, 0, static_cast<cudaStream_t>(stream_)>>>(
+      seed, indices, base_index, batch, out_x, nullptr, out_y);
   DDP_CUDA(cudaGetLastError());
   return 0;
 }

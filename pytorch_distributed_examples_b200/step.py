@@ -65,7 +65,11 @@ class TrainStep:
         self._consumed = [None] * slots    # event: last step that read the slot finished
         self._u8 = None                    # per-slot uint8 staging buffers (stage_u8)
         self.use_graph = use_graph
-        self.fused_head = os.environ.get("DDP_SPLIT_HEAD", "0") != "1"    # A/B switch: separate head_fwd / head_bwd kernels
+        # the fused head kernel (ddp_net_train_fwdbwd) removes a launch, a second staging of fc1.weight and the h / logp
+        # round trip: worth 8 us of an 80 us step at B = 64; from B = 4096 up the two separately tuned kernels are
+        # ~3 us faster (measured), so large batches keep them.  DDP_SPLIT_HEAD=1 / DDP_FUSED_HEAD=1 force either.
+        self.fused_head = (self.batch <= 2048 or os.environ.get("DDP_FUSED_HEAD", "0") == "1") \
+            and os.environ.get("DDP_SPLIT_HEAD", "0") != "1"
         self.graphs = None
         self._fingerprint = None
         self.kernel_launches_per_step = KERNELS_PER_STEP

@@ -167,7 +167,30 @@ def main():
         ms = mlp_run("sym")
         assert (ms - mb).abs().max().item() <= 1e-5 * mb.abs().max().item() + 1e-2 * 1e-3, "symmetric FusedUpdateHook != DDP + Adam"
         same_on_all_ranks(ms, "fused hook (symmetric)")
-    log("DDP comm hooks ok")
+    # BatchNorm buffers broadcast through our communicator (N4) == stock DDP broadcast_buffers=True; the ranks start
+    # from DIFFERENT running statistics, so the sync has something to do
+    def bn_run(ours):
+        torch.manual_seed(12)
+        m = torch.nn.Sequential(torch.nn.Conv2d(1, 8, 3), torch.nn.BatchNorm2d(8), torch.nn.ReLU(), torch.nn.AdaptiveAvgPool2d(1),
+                                torch.nn.Flatten(), torch.nn.Linear(8, 10)).cuda()
+        with torch.no_grad():
+            m[1].running_mean.add_(float(R)); m[1].running_var.mul_(1.0 + R)
+        bb = pkg.BufferBroadcast(m) if ours else None
+        d = DDP(m, device_ids=[local], broadcast_buffers=not ours)
+        o = torch.optim.SGD(d.parameters(), lr=0.05)
+        ds = pkg.SyntheticMNIST(length=4096, seed=6)
+        for k in range(3):
+            x, y = ds.batch(base_index=(k * W + R) * 32, count=32)
+            o.zero_grad(); F.cross_entropy(d(x), y).backward(); o.step()
+        d.eval()
+        with torch.no_grad():
+            d(ds.batch(base_index=0, count=8)[0])       # one more forward: buffers synced again, as DDP does
+        torch.cuda.synchronize()
+        return torch.cat([v.detach().reshape(-1).float() for v in m.state_dict().values()]).clone()
+
+    bn_base, bn_ours = bn_run(False), bn_run(True)
+    assert torch.equal(bn_base, bn_ours), "BufferBroadcast != DDP broadcast_buffers=True"
+    log("DDP comm hooks + BatchNorm buffer broadcast ok")
 
     # 3b. the DDP script's own model with native kernels: pkg.Model under stock DDP + our hook, the reference loop body
     #     (ref: pytorch_elastic/mnist_ddp_elastic.py:58,70-75,172-174).  Two sharp checks (neither can pass with wrong

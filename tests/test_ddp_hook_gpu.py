@@ -141,3 +141,34 @@ def test_fused_update_hook_matches_ddp_plus_torch_optimizer(world1, opt_kind):
     # (+ 1e-2 of one Adam step for elements whose |g| ~ eps)
     extra = 1e-2 * 1e-3 if opt_kind == "adam" else 0.0
     assert (fused - base).abs().max().item() <= RTOL * scale + extra
+
+
+def test_buffer_broadcast_rehomes_batchnorm_buffers_without_changing_the_model(world1):
+    """N4: BatchNorm buffers live in one flat arena per dtype and are synced by a forward pre-hook; at W = 1 the sync is a
+    no-op, so a conv+BN model under DDP(broadcast_buffers=False) + BufferBroadcast must train exactly like stock DDP."""
+    pkg = world1
+
+    def run(ours):
+        torch.manual_seed(12)
+        m = torch.nn.Sequential(torch.nn.Conv2d(1, 8, 3), torch.nn.BatchNorm2d(8), torch.nn.ReLU(), torch.nn.Conv2d(8, 8, 3),
+                                torch.nn.BatchNorm2d(8), torch.nn.ReLU(), torch.nn.AdaptiveAvgPool2d(1), torch.nn.Flatten(),
+                                torch.nn.Linear(8, 10)).cuda()
+        keys = list(m.state_dict().keys())
+        bb = pkg.BufferBroadcast(m) if ours else None
+        assert list(m.state_dict().keys()) == keys
+        from torch.nn.parallel import DistributedDataParallel as DDP
+        d = DDP(m, device_ids=[0], broadcast_buffers=not ours)
+        o = torch.optim.SGD(d.parameters(), lr=0.05)
+        ds = pkg.SyntheticMNIST(length=4096, seed=6)
+        for k in range(4):
+            x, y = ds.batch(base_index=k * 32, count=32)
+            o.zero_grad(); F.cross_entropy(d(x), y).backward(); o.step()
+        torch.cuda.synchronize()
+        if ours:
+            assert bb.calls == 4 and len(bb.arenas) == 2          # float32 statistics + int64 num_batches_tracked
+            assert all(b.untyped_storage().data_ptr() in {a.untyped_storage().data_ptr() for a in bb.arenas} for b in m.buffers())
+        return {k: v.detach().clone() for k, v in m.state_dict().items()}
+
+    base, mine = run(False), run(True)
+    for k in base:
+        assert torch.equal(base[k], mine[k]), k

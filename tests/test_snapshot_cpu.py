@@ -37,3 +37,16 @@ def test_snapshot_round_trip_and_reference_reader(tmp_path):
     # a file written the reference's way (no optimizer key) loads as well
     torch.save({"MODEL_STATE": model.state_dict(), "EPOCHS_RUN": 3}, path)
     assert load_snapshot(m2, path, optimizer=o2) == 3
+
+
+def test_async_writer_falls_back_to_a_synchronous_write_for_cpu_modules(tmp_path):
+    from pytorch_distributed_examples_b200.snapshot import AsyncSnapshotWriter
+    torch.manual_seed(1)
+    model = mlp_oracle.OracleMLP(1, 16)
+    path = os.path.join(tmp_path, "snapshot.pt")
+    w = AsyncSnapshotWriter(path)
+    w.save(model, 4)
+    w.flush()
+    snap = torch.load(path)
+    assert snap["EPOCHS_RUN"] == 4 and all(torch.equal(snap["MODEL_STATE"][k], v) for k, v in model.state_dict().items())
+    w.close()

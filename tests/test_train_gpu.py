@@ -243,3 +243,33 @@ def test_evaluate_matches_reference_test_loop(native):
     undecided = int(((top2[:, 0] - top2[:, 1]) < 1e-5).sum())                              # ties within rounding may go either way
     ref_m = sum(int((l.max(1)[1] == by).sum()) for l, (_, by) in zip(lg, mb))
     assert total_m == 384 and abs(correct_m - ref_m) <= undecided
+
+
+def test_async_snapshot_writer_captures_the_state_at_save_time(native, tmp_path):
+    """N3: device -> pinned host -> disk off the training stream (ref: mnist_ddp_elastic.py:95-104).  The file must hold
+    the parameters as they were when save() was called even though training continued while it was being written,
+    and the reference's reader must be able to load it."""
+    import pytorch_distributed_examples_b200 as pkg
+    torch.manual_seed(3)
+    model = pkg.Net().cuda().train()
+    opt = pkg.FusedOptimizer(torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9))
+    ds = pkg.SyntheticMNIST(length=4096, seed=2)
+    path = os.path.join(tmp_path, "snapshot.pt")
+    w = pkg.AsyncSnapshotWriter(path)
+    kept = []
+    for epoch in range(3):
+        for k in range(4):
+            x, y = ds.batch(base_index=(epoch * 4 + k) * 64, count=64)
+            opt.zero_grad(); F.nll_loss(model(x), y).backward(); opt.step()
+        w.save(model, epoch)                                  # returns immediately; training goes on
+        kept.append({k: v.detach().clone() for k, v in model.state_dict().items()})
+    x, y = ds.batch(base_index=0, count=64)
+    opt.zero_grad(); F.nll_loss(model(x), y).backward(); opt.step()   # mutate the parameters while the last write is in flight
+    w.flush()
+    snap = torch.load(path)                                   # the reference's reader (ref :61-68)
+    assert snap["EPOCHS_RUN"] == 2
+    for k, v in kept[2].items():
+        assert torch.equal(snap["MODEL_STATE"][k], v.cpu()), k
+    ref = net_oracle.OracleNet(); ref.load_state_dict(snap["MODEL_STATE"])
+    assert not os.path.exists(path + ".tmp")
+    w.close()
