@@ -1,0 +1,60 @@
+"""The switched-over reference scripts (examples/) run end to end for a few batches on one GPU: the reference CLI is
+kept (ref: pytorch_elastic/mnist_ddp_elastic.py:202-213), the every-5-batches loss print of mnist_horovod.py:65-67,
+the commit cadence + final test() of horovod_mnist_elastic.py, the per-epoch test() and snapshot of the DDP script,
+and its resume-from-snapshot.pt after a relaunch (ref :54-56)."""
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EX = os.path.join(ROOT, "examples")
+
+
+def _run(cmd, cwd, timeout=300):
+    env = dict(os.environ)
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT"):
+        env.pop(k, None)
+    r = subprocess.run(cmd, cwd=cwd, env=env, capture_output=True, text=True, timeout=timeout)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    return r.stdout
+
+
+def test_mnist_horovod_example_trains(tmp_path):
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    out = _run([sys.executable, os.path.join(EX, "mnist_horovod.py"), "--epochs", "2", "--batch_size", "256",
+                "--train_samples", "8192"], tmp_path)
+    losses = [float(m) for m in re.findall(r"Loss: ([0-9.eE+-]+)", out)]
+    assert len(losses) == 2 * 7                       # 32 batches per epoch, printed at 0, 5, ..., 30
+    assert losses[-1] < 0.5 * losses[0], losses       # the synthetic digits are learnable: the loss must fall
+
+
+def test_horovod_mnist_elastic_example_trains_and_tests(tmp_path):
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    out = _run([sys.executable, os.path.join(EX, "horovod_mnist_elastic.py"), "--epochs", "1", "--train_samples", "8192",
+                "--test_samples", "2048", "--batches_per_commit", "16"], tmp_path)
+    assert len(re.findall(r"Worker: 0/1 \| Batch", out)) >= 3
+    acc = float(re.search(r"Accuracy: ([0-9.]+)%", out).group(1))
+    assert acc > 50.0, out[-1000:]
+
+
+def test_mnist_ddp_elastic_example_cli_snapshot_and_resume(tmp_path):
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    base = [sys.executable, "-m", "torch.distributed.run", "--standalone", "--nnodes=1", "--nproc-per-node=1",
+            "--local-addr", "127.0.0.1", os.path.join(EX, "mnist_ddp_elastic.py")]
+    small = ["--batch_size", "128", "--train_samples", "4096", "--test_samples", "1024", "--hidden_layers", "2",
+             "--features", "256"]
+    out = _run(base + ["2", "1"] + small, tmp_path)                      # total_epochs=2 save_every=1
+    assert len(re.findall(r"Test accuracy: ([0-9.]+)%", out)) == 2 and "Execution time" in out
+    snap = torch.load(os.path.join(tmp_path, "snapshot.pt"))
+    assert snap["EPOCHS_RUN"] == 1 and "input_layer.weight" in snap["MODEL_STATE"]
+    out2 = _run(base + ["3", "1"] + small, tmp_path)                     # relaunch: resumes, runs the remaining epochs
+    assert "Resuming training from snapshot at Epoch 1" in out2
+    assert len(re.findall(r"Test accuracy", out2)) == 2                  # epochs 1 and 2
