@@ -64,7 +64,7 @@ def main():
             param_group["lr"] = args.lr / math.sqrt(hvd.size())
 
     def test():                                                                                     # ref :85-102
-        test_dataset = SyntheticMNIST(args.test_samples, seed=4321)
+        test_dataset = SyntheticMNIST(args.test_samples, seed=1234, first_index=args.train_samples)   # held-out samples of the same stream
         model.eval()
         correct = total = 0
         with torch.no_grad():

@@ -82,7 +82,7 @@ class Trainer:                                                               # r
 
 def load_train_objs(args):                                                   # ref :162-175
     train_set = SyntheticMNIST(args.train_samples, seed=1234)
-    test_set = SyntheticMNIST(args.test_samples, seed=4321)
+    test_set = SyntheticMNIST(args.test_samples, seed=1234, first_index=args.train_samples)   # held-out samples of the same stream
     model = Model(hidden_layers=args.hidden_layers, features=args.features)
     optimizer = torch.optim.Adam(model.parameters(), lr=1e-3)
     criterion = nn.CrossEntropyLoss()

@@ -242,6 +242,20 @@ int ddp_peer_allreduce(void* peer, float* bucket, int64_t n, void* stream);
 int ddp_peer_allreduce_update(void* peer, float* bucket, int64_t n, int opt, float* params,
                               float* state1, float* state2, const ddp_hyper_t* hyper, int64_t step,
                               const int64_t* step_dev, void* stream);
+/* The WHOLE training step of one rank in one call -- forward, F.nll_loss, backward, gradient exchange, averaged
+ * optimizer update -- ref: horovod/mnist_horovod.py:59-64 (zero_grad / model(data) / F.nll_loss / backward /
+ * hvd.DistributedOptimizer.step()).  Same arithmetic as ddp_net_forward + ddp_net_backward(target) +
+ * ddp_peer_allreduce_update, but the backward's per-CTA partial gradient sums are reduced straight into the peer
+ * exchange: the fc / conv2 part is pushed over NVLink by a side-stream kernel WHILE conv1's weight gradient is still
+ * being computed (batch > 1024), so only conv1's 260 gradients and one flag round trip stay exposed.
+ * params / state1 / state2 are updated in place; grad_bucket (may be NULL unless hyper->write_back_grad) receives the
+ * averaged gradient.  fused_head != 0 runs the head as one kernel (see ddp_net_train_fwdbwd).  `peer` as above. */
+int ddp_net_train_step_peer(float* params, const float* x, const int64_t* target, const float* mask2d,
+                            const float* mask1d, uint64_t seed, uint64_t offset, const int64_t* offset_dev,
+                            int64_t batch, void* workspace, float* out_logp, float* out_loss, void* scratch,
+                            float* grad_bucket, void* peer, int opt, float* state1, float* state2,
+                            const ddp_hyper_t* hyper, int64_t step, const int64_t* step_dev, int fused_head,
+                            void* stream);
 
 /* ---- two-shot allreduce for large buckets in symmetric memory (NVSwitch multicast / peer load-store) ----
  * For bandwidth-bound buckets on ONE node (ResNet-50: 102 MB fp32 / 51 MB bf16): replaces the per-bucket

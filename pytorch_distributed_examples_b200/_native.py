@@ -79,6 +79,9 @@ SIGNATURES = {
     "ddp_peer_allreduce": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "ddp_peer_allreduce_update": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p, POINTER(Hyper),
                                           c_int64, c_void_p, c_void_p]),
+    "ddp_net_train_step_peer": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_uint64, c_uint64, c_void_p, c_int64,
+                                        c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
+                                        POINTER(Hyper), c_int64, c_void_p, c_int, c_void_p]),
     "ddp_sym_flag_bytes": (c_int64, []),
     "ddp_sym_allreduce": (c_int, [POINTER(ctypes.c_uint64), ctypes.c_uint64, c_int64, c_int, c_int, c_int64, c_int64, c_int,
                                   c_float, c_int, c_int, c_void_p]),
@@ -326,6 +329,18 @@ class Native:
     def peer_allreduce(self, peer, bucket):
         self._check(self.lib.ddp_peer_allreduce(peer, _ptr(bucket, "bucket", torch.float32), bucket.numel(), _stream()),
                     "ddp_peer_allreduce", collective=True)
+
+    def net_train_step_peer(self, params, x, target, seed, offset, workspace, out_logp, out_loss, scratch, grad_bucket, peer,
+                            opt, state1, state2, hyper: Hyper, step=1, step_dev=None, offset_dev=None, fused_head=False):
+        """The whole training step of one rank (forward, loss, backward, NVLink peer exchange, averaged update)."""
+        rc = self.lib.ddp_net_train_step_peer(
+            _ptr(params, "params", torch.float32), _ptr(x, "x", torch.float32), _ptr(target, "target", torch.int64), None, None,
+            int(seed) & (2 ** 64 - 1), int(offset) & (2 ** 64 - 1), _ptr(offset_dev, "offset_dev", torch.int64), x.shape[0],
+            _ptr(workspace, "workspace"), _ptr(out_logp, "out_logp", torch.float32), _ptr(out_loss, "out_loss", torch.float32),
+            _ptr(scratch, "scratch"), _ptr(grad_bucket, "grad_bucket", torch.float32), peer, int(opt),
+            _ptr(state1, "state1", torch.float32), _ptr(state2, "state2", torch.float32), ctypes.byref(hyper), int(step),
+            _ptr(step_dev, "step_dev", torch.int64), int(bool(fused_head)), _stream())
+        self._check(rc, "ddp_net_train_step_peer", collective=True)
 
     def peer_allreduce_update(self, peer, opt, bucket, params, state1, state2, n, hyper: Hyper, step=1, step_dev=None):
         rc = self.lib.ddp_peer_allreduce_update(peer, _ptr(bucket, "bucket", torch.float32), int(n), opt,

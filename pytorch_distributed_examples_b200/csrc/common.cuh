@@ -102,8 +102,29 @@ int launch_conv2_fwd_tc(const float* params, const float* a1, const float* mask2
 // launch helpers shared by ddp_net_forward / ddp_net_backward and the fused training entry point (head_fused.cu)
 int launch_fwd_convs(const float* params, const float* x, const float* mask2d, uint64_t seed, uint64_t offset,
                      const int64_t* offset_dev, int training, const Workspace& ws, int B, cudaStream_t stream);
+// Optional tail of the backward: instead of reducing the partial gradient rows into the bucket, reduce them straight into
+// the NVLink peer-memory exchange (peer.cu) -- the fc / conv2 part while conv1_wgrad still runs -- and finish with the
+// rank-ordered sum + optimizer update.  `peer` is a ddp_peer_create context.
+struct PeerExchange {
+  void* peer;
+  int opt;
+  float* params;
+  float* state1;
+  float* state2;
+  const ddp_hyper_t* hyper;
+  int64_t step;
+  const int64_t* step_dev;
+};
+int launch_peer_early(const PeerExchange& px, const float* partials, int parts_c2, int parts_head, cudaStream_t stream);
+int launch_peer_final(const PeerExchange& px, const float* partials, int parts_c1, bool have_early, int parts_c2, int parts_head,
+                      float* grad_bucket, cudaStream_t stream);
 int launch_bwd_after_head(const float* params, const float* x, int training, int B, const Workspace& ws, const Scratch& sc,
-                          int parts_head, float* grad_bucket, cudaStream_t stream);
+                          int parts_head, float* grad_bucket, cudaStream_t stream, const PeerExchange* px = nullptr);
+int launch_head_fwd(const float* params, const Workspace& ws, const int64_t* target, const float* mask1d, uint64_t seed,
+                    uint64_t offset, const int64_t* offset_dev, int training, float* out_logp, float* out_loss,
+                    int64_t* out_argmax, int64_t* out_correct, const Scratch& sc, int B, cudaStream_t stream);
+int launch_head_bwd(const float* params, const Workspace& ws, const float* logp, const float* dlogp, const int64_t* target,
+                    float nll_coef, float drop_scale, const Scratch& sc, int B, int* parts_head, cudaStream_t stream);
 // sparse conv2 backward (net_bwd_sparse.cu): one visit per live (channel, pool cell) entry instead of dense 8x8 planes
 int launch_conv2_wgrad_sp(const float* da2, const float* a2, const uint8_t* idx2, const float* a1, float drop_scale,
                           float* partials, int B, int* parts_out, cudaStream_t stream, bool pdl);

@@ -364,3 +364,52 @@ extern "C" int ddp_net_train_fwdbwd(const float* params, const float* x, const i
   prof_mark(5, stream);
   return launch_bwd_after_head(params, x, 1, B, ws, sc, grid, grad_bucket, stream);
 }
+
+// The whole data-parallel training step of one rank in ONE call: forward, loss, backward, and -- instead of writing the
+// gradients into a bucket for a separate allreduce + update -- the partial gradient sums go straight into the NVLink
+// peer-memory exchange (peer.cu), the fc / conv2 part while conv1's weight gradient is still being computed.
+// ref: horovod/mnist_horovod.py:59-64 (the five-line loop incl. hvd.DistributedOptimizer.step()).
+extern "C" int ddp_net_train_step_peer(float* params, const float* x, const int64_t* target, const float* mask2d,
+                                       const float* mask1d, uint64_t seed, uint64_t offset, const int64_t* offset_dev,
+                                       int64_t batch, void* workspace, float* out_logp, float* out_loss, void* scratch,
+                                       float* grad_bucket, void* peer, int opt, float* state1, float* state2,
+                                       const ddp_hyper_t* hyper, int64_t step, const int64_t* step_dev, int fused_head,
+                                       void* stream_) {
+  DDP_REQUIRE(params && x && target && workspace && out_logp && out_loss && scratch && peer && hyper,
+              "params, x, target, workspace, out_logp, out_loss, scratch, peer and hyper are required");
+  DDP_REQUIRE(batch >= 1 && batch <= (int64_t(1) << 24), "batch out of range");
+  DDP_REQUIRE(aligned16(params) && aligned16(x) && aligned16(workspace) && aligned16(scratch),
+              "params/x/workspace/scratch must be 16-byte aligned");
+  DDP_REQUIRE(!hyper->write_back_grad || grad_bucket, "grad_bucket is required when hyper.write_back_grad is set");
+  DDP_REQUIRE(step >= 1 || step_dev, "step must be >= 1 unless step_dev is given");
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int B = int(batch);
+  Workspace ws = carve_workspace(workspace, batch);
+  Scratch sc = carve_scratch(scratch, batch);
+  if (int rc = launch_fwd_convs(params, x, mask2d, seed, offset, offset_dev, 1, ws, B, stream)) return rc;
+  int parts_head = 0;
+  const float nll_coef = -1.0f / float(B);
+  if (fused_head) {
+    static bool attr_done[64] = {false};
+    int dev = 0;
+    DDP_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !attr_done[dev]) {
+      DDP_CUDA(cudaFuncSetAttribute(head_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FH_SMEM));
+      attr_done[dev] = true;
+    }
+    const int ntiles = (B + FT - 1) / FT;
+    int grid = sm_count() * 2;
+    if (grid > ntiles) grid = ntiles;
+    if (grid > MAX_PARTS) grid = MAX_PARTS;
+    DDP_CUDA(launch_pdl(head_fused_kernel, dim3(grid), dim3(FH_THREADS), FH_SMEM, stream, true, params, ws.a2, target, mask1d,
+                        seed, offset, offset_dev, nll_coef, ws.h, out_logp, out_loss, (int64_t*)nullptr,
+                        (unsigned long long*)nullptr, sc.loss_part, sc.counters, sc.da2, sc.partials, B));
+    parts_head = grid;
+  } else {
+    if (int rc = launch_head_fwd(params, ws, target, mask1d, seed, offset, offset_dev, 1, out_logp, out_loss, nullptr, nullptr,
+                                 sc, B, stream)) return rc;
+    if (int rc = launch_head_bwd(params, ws, out_logp, nullptr, target, nll_coef, 2.f, sc, B, &parts_head, stream)) return rc;
+  }
+  const PeerExchange px{peer, opt, params, state1, state2, hyper, step, step_dev};
+  return launch_bwd_after_head(params, x, 1, B, ws, sc, parts_head, grad_bucket, stream, &px);
+}

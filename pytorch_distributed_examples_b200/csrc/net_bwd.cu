@@ -680,7 +680,7 @@ static int set_bwd_attrs() {   // function attributes are per device: a process 
 // Everything behind the head: conv2 dgrad / wgrad, conv1 wgrad, fixed-order reduction of the partial rows into the
 // bucket.  `parts_head` = number of partial rows the head kernel (K_B3 or the fused training head) wrote.
 int launch_bwd_after_head(const float* params, const float* x, int training, int B, const Workspace& ws, const Scratch& sc,
-                          int parts_head, float* grad_bucket, cudaStream_t stream) {
+                          int parts_head, float* grad_bucket, cudaStream_t stream, const PeerExchange* px) {
   if (int rc = set_bwd_attrs()) return rc;
   const int sms = sm_count();
   const float drop_scale = training ? 2.f : 1.f;
@@ -693,6 +693,9 @@ int launch_bwd_after_head(const float* params, const float* x, int training, int
   static int fork_max_b = -1;
   if (fork_max_b < 0) { const char* e = getenv("DDP_FORK_MAX_B"); fork_max_b = e ? atoi(e) : 1024; }
   bool fork = B <= fork_max_b && !prof_enabled();
+  // With a peer exchange attached, large batches push the fc / conv2 gradients to the peers WHILE conv1_wgrad runs
+  // (side stream, early kernel), so only conv1's 260 gradients and the flag round trip remain exposed afterwards.
+  const bool early = px != nullptr && !fork && !prof_enabled();
   cudaStream_t wstream = stream;
   cudaEvent_t join_ev = nullptr;
   if (fork) {
@@ -734,18 +737,50 @@ int launch_bwd_after_head(const float* params, const float* x, int training, int
   if (!fork)
     if (int rc = launch_wgrad2()) return rc;
   prof_mark(7, stream);
+  cudaStream_t estream = nullptr;
+  cudaEvent_t ejoin = nullptr;
+  bool early_on = early;
+  if (early_on) {                                      // fc + conv2 partial rows are final: reduce + push them beside conv1_wgrad
+    if (int rc = side_fork(stream, &estream, &ejoin)) return rc;
+    if (!estream) early_on = false;                    // first call is inside a stream capture: no side stream yet
+  }
+  if (early_on) {
+    if (int rc = launch_peer_early(*px, sc.partials, parts_c2, parts_head, estream)) return rc;
+    DDP_CUDA(cudaEventRecord(ejoin, estream));
+  }
   {
     const int nst1 = (B + W1_NS - 1) / W1_NS;
-    parts_c1 = nst1 < sms * 2 ? nst1 : sms * 2;
+    // with the early push in flight leave room for its CTAs: 16 SMs keep one conv1_wgrad CTA instead of two
+    const int cap1 = early_on ? sms * 2 - 16 : sms * 2;
+    parts_c1 = nst1 < cap1 ? nst1 : cap1;
     if (parts_c1 > MAX_PARTS) parts_c1 = MAX_PARTS;
-    DDP_CUDA(launch_pdl(conv1_wgrad_kernel, dim3(parts_c1), dim3(W1_THREADS), W1_SMEM, stream, true, sc.dp1, ws.idx1, x, sc.partials, B));
+    DDP_CUDA(launch_pdl(conv1_wgrad_kernel, dim3(parts_c1), dim3(W1_THREADS), W1_SMEM, stream, !early_on, sc.dp1, ws.idx1, x, sc.partials, B));
   }
   prof_mark(8, stream);
   if (fork) DDP_CUDA(cudaStreamWaitEvent(stream, join_ev, 0));
-  DDP_CUDA(launch_pdl(reduce_partials_kernel, dim3((P_ARENA / 4 + 31) / 32), dim3(RP_WARPS * 32), 0, stream, true, sc.partials, parts_c1,
-                      parts_c2, parts_head, grad_bucket));
+  if (early_on) {
+    DDP_CUDA(cudaStreamWaitEvent(stream, ejoin, 0));
+    if (int rc = launch_peer_final(*px, sc.partials, parts_c1, /*have_early=*/true, parts_c2, parts_head, grad_bucket, stream)) return rc;
+  } else if (px) {
+    if (int rc = launch_peer_final(*px, sc.partials, parts_c1, /*have_early=*/false, parts_c2, parts_head, grad_bucket, stream)) return rc;
+  } else {
+    DDP_CUDA(launch_pdl(reduce_partials_kernel, dim3((P_ARENA / 4 + 31) / 32), dim3(RP_WARPS * 32), 0, stream, true, sc.partials, parts_c1,
+                        parts_c2, parts_head, grad_bucket));
+  }
   prof_mark(9, stream);
   DDP_CUDA(cudaGetLastError());
+  return 0;
+}
+// K_B3 (shared by ddp_net_backward and the whole-step entry point)
+int launch_head_bwd(const float* params, const Workspace& ws, const float* logp, const float* dlogp, const int64_t* target,
+                    float nll_coef, float drop_scale, const Scratch& sc, int B, int* parts_head, cudaStream_t stream) {
+  if (int rc = set_bwd_attrs()) return rc;
+  const int sms = sm_count();
+  prof_mark(4, stream);
+  int ntiles = (B + HT - 1) / HT;
+  *parts_head = ntiles < sms ? ntiles : sms;
+  DDP_CUDA(launch_pdl(head_bwd_kernel, dim3(*parts_head), dim3(HB_THREADS), HB_SMEM, stream, true, params, ws.a2, ws.h, logp,
+                      dlogp, target, nll_coef, drop_scale, sc.da2, sc.partials, B));
   return 0;
 }
 }  // namespace ddp
@@ -770,12 +805,6 @@ extern "C" int ddp_net_backward(const float* params, const float* x, const float
   const float nll_coef = -loss_scale / float(B);
   if (int rc = set_bwd_attrs()) return rc;
   int parts_head;
-  prof_mark(4, stream);
-  {
-    int ntiles = (B + HT - 1) / HT;
-    parts_head = ntiles < sms ? ntiles : sms;
-    DDP_CUDA(launch_pdl(head_bwd_kernel, dim3(parts_head), dim3(HB_THREADS), HB_SMEM, stream, true, params, ws.a2, ws.h, logp,
-                        dlogp, target, nll_coef, drop_scale, sc.da2, sc.partials, B));
-  }
+  if (int rc = launch_head_bwd(params, ws, logp, dlogp, target, nll_coef, drop_scale, sc, B, &parts_head, stream)) return rc;
   return launch_bwd_after_head(params, x, training, B, ws, sc, parts_head, grad_bucket, stream);
 }

@@ -334,6 +334,24 @@ int launch_fwd_convs(const float* params, const float* x, const float* mask2d, u
   prof_mark(2, stream);
   return 0;
 }
+// K_F3 (shared by ddp_net_forward and the whole-step entry point)
+int launch_head_fwd(const float* params, const Workspace& ws, const int64_t* target, const float* mask1d, uint64_t seed,
+                    uint64_t offset, const int64_t* offset_dev, int training, float* out_logp, float* out_loss,
+                    int64_t* out_argmax, int64_t* out_correct, const Scratch& sc, int B, cudaStream_t stream) {
+  int ntiles = (B + HT - 1) / HT;
+  int grid = ntiles < MAX_PARTS ? ntiles : MAX_PARTS;   // one loss partial per CTA
+  static bool attr_done[64] = {false};       // function attributes are per device
+  int dev = 0;
+  DDP_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 64 && !attr_done[dev]) {
+    DDP_CUDA(cudaFuncSetAttribute(head_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HF_SMEM));
+    attr_done[dev] = true;
+  }
+  DDP_CUDA(launch_pdl(head_fwd_kernel, dim3(grid), dim3(HF_THREADS), HF_SMEM, stream, true,
+                      params, ws.a2, target, mask1d, seed, offset, offset_dev, training, ws.h, out_logp, out_loss, out_argmax,
+                      reinterpret_cast<unsigned long long*>(out_correct), sc.loss_part, sc.counters, B));
+  return 0;
+}
 }  // namespace ddp
 
 using namespace ddp;
@@ -356,20 +374,10 @@ extern "C" int ddp_net_forward(const float* params, const float* x, const int64_
 
   if (int rc = launch_fwd_convs(params, x, mask2d, seed, offset, offset_dev, training, ws, B, stream)) return rc;
   {
-    int ntiles = (B + HT - 1) / HT;
-    int grid = ntiles < MAX_PARTS ? ntiles : MAX_PARTS;   // one loss partial per CTA
     Scratch sc{};
     if (scratch) sc = carve_scratch(scratch, batch);
-    static bool attr_done[64] = {false};       // function attributes are per device
-    int dev = 0;
-    DDP_CUDA(cudaGetDevice(&dev));
-    if (dev >= 0 && dev < 64 && !attr_done[dev]) {
-      DDP_CUDA(cudaFuncSetAttribute(head_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HF_SMEM));
-      attr_done[dev] = true;
-    }
-    DDP_CUDA(launch_pdl(head_fwd_kernel, dim3(grid), dim3(HF_THREADS), HF_SMEM, stream, true,
-                        params, ws.a2, target, mask1d, seed, offset, offset_dev, training, ws.h, out_logp, out_loss, out_argmax,
-                        reinterpret_cast<unsigned long long*>(out_correct), sc.loss_part, sc.counters, B));
+    if (int rc = launch_head_fwd(params, ws, target, mask1d, seed, offset, offset_dev, training, out_logp, out_loss, out_argmax,
+                                 out_correct, sc, B, stream)) return rc;
   }
   prof_mark(3, stream);
   DDP_CUDA(cudaGetLastError());

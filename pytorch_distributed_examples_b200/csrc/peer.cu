@@ -57,13 +57,36 @@ __device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
 }
 
 // MODE 0: allreduce(sum) only, result written to `out`; MODE 1: + fused optimizer update of params/state.
+// Where this rank's contribution comes from.  mode 0: `bucket` (n floats).  mode 1: the per-CTA partial gradient rows of
+// the backward kernels (net_bwd.cu), summed here in row order -- the separate reduce_partials launch disappears.
+// mode 2: like 1, but the fc / conv2 part [OFF_C2W, P_ARENA) was already reduced and pushed by peer_early_kernel while
+// conv1_wgrad was running: only conv1's columns are left.
+struct PartialSrc {
+  int mode;
+  const float* partials;
+  int parts_c1, parts_c2, parts_head;
+};
+constexpr int PEER_C1_COLS = OFF_C2W / 4;          // float4 columns of conv1.weight + conv1.bias (incl. padding)
+__device__ __forceinline__ bool peer_is_pad(int e) {
+  return (e >= 250 && e < OFF_C1B) || (e >= OFF_C1B + 10 && e < OFF_C2W) || (e >= OFF_C2B + 20 && e < OFF_F1W) ||
+         (e >= OFF_F1B + 50 && e < OFF_F2W) || (e >= OFF_F2B + 10);
+}
+__device__ __forceinline__ float4 peer_zero_pads(float4 v, int e) {
+  if (peer_is_pad(e)) v.x = 0.f;
+  if (peer_is_pad(e + 1)) v.y = 0.f;
+  if (peer_is_pad(e + 2)) v.z = 0.f;
+  if (peer_is_pad(e + 3)) v.w = 0.f;
+  return v;
+}
+
 template <int OPT, bool HAS1, bool HAS2, bool UPDATE>
 __global__ void __launch_bounds__(PEER_THREADS, 1)
 peer_allreduce_kernel(PeerDev pd, const float* __restrict__ bucket, float* __restrict__ out, int64_t n,
                       float* __restrict__ params, float* __restrict__ state1, float* __restrict__ state2,
-                      UpdateConsts kc, int64_t step, const int64_t* __restrict__ step_dev) {
+                      UpdateConsts kc, int64_t step, const int64_t* __restrict__ step_dev, PartialSrc src) {
   __shared__ UpdateConsts ks;
   __shared__ unsigned int epoch_s;
+  __shared__ float4 wsum_s[PEER_THREADS / 32];
   const int tid = threadIdx.x;
   if (tid == 0) {
     epoch_s = *((volatile unsigned int*)pd.epoch) + 1u;   // every CTA reads it before the ticket winner bumps it
@@ -81,12 +104,63 @@ peer_allreduce_kernel(PeerDev pd, const float* __restrict__ bucket, float* __res
   const int64_t gtid = int64_t(blockIdx.x) * PEER_THREADS + tid, gthreads = int64_t(gridDim.x) * PEER_THREADS;
   const int64_t slot_off = (int64_t(par) * W + R) * pd.max_elems;
 
-  // 1. push my bucket into slot[par][R] of every rank
-  for (int64_t i = gtid; i < nvec; i += gthreads) {
-    const float4 v = reinterpret_cast<const float4*>(bucket)[i];
+  // 1. push my contribution into slot[par][R] of every rank
+  if (src.mode == 0) {
+    for (int64_t i = gtid; i < nvec; i += gthreads) {
+      const float4 v = reinterpret_cast<const float4*>(bucket)[i];
 #pragma unroll
-    for (int p = 0; p < PEER_MAX_WORLD; ++p)
-      if (p < W) reinterpret_cast<float4*>(pd.slots[p] + slot_off)[i] = v;
+      for (int p = 0; p < PEER_MAX_WORLD; ++p)
+        if (p < W) reinterpret_cast<float4*>(pd.slots[p] + slot_off)[i] = v;
+    }
+  } else if (src.mode == 1) {
+    // every column: one thread walks the column's partial rows in order (few rows at the small batches that take this path)
+    for (int64_t i = gtid; i < nvec; i += gthreads) {
+      const int e = int(i) * 4;
+      const int parts = e < OFF_C2W ? src.parts_c1 : (e < OFF_F1W ? src.parts_c2 : src.parts_head);
+      const float* p0 = src.partials + e;
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+      int r = 0;
+      for (; r + 4 <= parts; r += 4) {
+        float4 v[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) v[q] = __ldcg(reinterpret_cast<const float4*>(p0 + size_t(r + q) * P_ARENA));
+#pragma unroll
+        for (int q = 0; q < 4; ++q) { a.x += v[q].x; a.y += v[q].y; a.z += v[q].z; a.w += v[q].w; }
+      }
+      for (; r < parts; ++r) {
+        const float4 v = __ldcg(reinterpret_cast<const float4*>(p0 + size_t(r) * P_ARENA));
+        a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+      }
+      a = peer_zero_pads(a, e);
+#pragma unroll
+      for (int p = 0; p < PEER_MAX_WORLD; ++p)
+        if (p < W) reinterpret_cast<float4*>(pd.slots[p] + slot_off)[i] = a;
+    }
+  } else {
+    // conv1's columns only: the whole CTA sums one column's rows (thread t: rows t, t+512), fixed-order shuffle tree,
+    // then the 16 warp sums in order
+    for (int c = blockIdx.x; c < PEER_C1_COLS; c += gridDim.x) {
+      const float* p0 = src.partials + c * 4;
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int r = tid; r < src.parts_c1; r += PEER_THREADS) {
+        const float4 v = __ldcg(reinterpret_cast<const float4*>(p0 + size_t(r) * P_ARENA));
+        a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        a.x += __shfl_xor_sync(0xffffffffu, a.x, o); a.y += __shfl_xor_sync(0xffffffffu, a.y, o);
+        a.z += __shfl_xor_sync(0xffffffffu, a.z, o); a.w += __shfl_xor_sync(0xffffffffu, a.w, o);
+      }
+      if ((tid & 31) == 0) wsum_s[tid >> 5] = a;
+      __syncthreads();
+      if (tid == 0) {
+        float4 t = wsum_s[0];
+        for (int w = 1; w < PEER_THREADS / 32; ++w) { t.x += wsum_s[w].x; t.y += wsum_s[w].y; t.z += wsum_s[w].z; t.w += wsum_s[w].w; }
+        t = peer_zero_pads(t, c * 4);
+        for (int p = 0; p < W; ++p) reinterpret_cast<float4*>(pd.slots[p] + slot_off)[c] = t;
+      }
+      __syncthreads();
+    }
   }
   __threadfence_system();
   __syncthreads();
@@ -137,6 +211,53 @@ peer_allreduce_kernel(PeerDev pd, const float* __restrict__ bucket, float* __res
       if (out) reinterpret_cast<float4*>(out)[i] = make_float4(go[0], go[1], go[2], go[3]);   // averaged gradient
     }
   }
+}
+
+// The early half of the exchange (PartialSrc mode 2): reduce the fc / conv2 partial rows (columns PEER_C1_COLS .. end) in
+// fixed order and push the sums into slot[par][R] of every rank.  Runs on a side stream beside conv1_wgrad; publishes
+// nothing -- the flag is raised by the final kernel, which is ordered after this one on every rank.
+constexpr int PEER_EARLY_CTAS = 16;
+constexpr int PEER_EARLY_WARPS = 32;
+__global__ void __launch_bounds__(PEER_EARLY_WARPS * 32, 1)
+peer_early_kernel(PeerDev pd, const float* __restrict__ partials, int parts_c2, int parts_head) {
+  __shared__ float4 red[PEER_EARLY_WARPS][33];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const unsigned int e = *((volatile unsigned int*)pd.epoch) + 1u;      // the final kernel of this step bumps it
+  const int par = int(e & 1u), W = pd.world, R = pd.rank;
+  const int64_t slot_off = (int64_t(par) * W + R) * pd.max_elems;
+  const int ncols = P_ARENA / 4 - PEER_C1_COLS;
+  for (int blk = blockIdx.x; blk * 32 < ncols; blk += gridDim.x) {
+    const int col = PEER_C1_COLS + blk * 32 + lane;
+    const int el = col * 4;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (el < P_ARENA) {
+      const int parts = el < OFF_F1W ? parts_c2 : parts_head;
+      const float* p0 = partials + el;
+      for (int r0 = warp; r0 < parts; r0 += 4 * PEER_EARLY_WARPS) {      // rows warp, warp+32, ...: four loads in flight
+        float4 v[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int r = r0 + q * PEER_EARLY_WARPS;
+          v[q] = r < parts ? __ldcg(reinterpret_cast<const float4*>(p0 + size_t(r) * P_ARENA)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) { s.x += v[q].x; s.y += v[q].y; s.z += v[q].z; s.w += v[q].w; }
+      }
+    }
+    red[warp][lane] = s;
+    __syncthreads();
+    if (warp == 0 && el < P_ARENA) {
+      float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int w = 0; w < PEER_EARLY_WARPS; ++w) { const float4 r = red[w][lane]; t.x += r.x; t.y += r.y; t.z += r.z; t.w += r.w; }
+      t = peer_zero_pads(t, el);
+#pragma unroll
+      for (int p = 0; p < PEER_MAX_WORLD; ++p)
+        if (p < W) reinterpret_cast<float4*>(pd.slots[p] + slot_off)[col] = t;
+    }
+    __syncthreads();
+  }
+  __threadfence_system();
 }
 
 static size_t peer_bytes(int world, int64_t max_elems) {
@@ -225,7 +346,7 @@ extern "C" int ddp_peer_allreduce(void* peer, float* bucket, int64_t n, void* st
   if (int rc = peer_check(c, bucket, n)) return rc;
   UpdateConsts k{};
   peer_allreduce_kernel<0, false, false, false><<<PEER_CTAS, PEER_THREADS, 0, static_cast<cudaStream_t>(stream_)>>>(
-      make_dev(c), bucket, bucket, n, nullptr, nullptr, nullptr, k, 1, nullptr);
+      make_dev(c), bucket, bucket, n, nullptr, nullptr, nullptr, k, 1, nullptr, PartialSrc{0, nullptr, 0, 0, 0});
   DDP_CUDA(cudaGetLastError());
   return 0;
 }
@@ -246,7 +367,7 @@ extern "C" int ddp_peer_allreduce_update(void* peer, float* bucket, int64_t n, i
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   const PeerDev d = make_dev(c);
 #define LAUNCH(OPT, H1, H2) peer_allreduce_kernel<OPT, H1, H2, true><<<PEER_CTAS, PEER_THREADS, 0, stream>>>( \
-      d, bucket, wb, n, params, state1, state2, k, step, step_dev)
+      d, bucket, wb, n, params, state1, state2, k, step, step_dev, PartialSrc{0, nullptr, 0, 0, 0})
   switch (opt) {
     case DDP_OPT_SGD: if (need1) LAUNCH(DDP_OPT_SGD, true, false); else LAUNCH(DDP_OPT_SGD, false, false); break;
     case DDP_OPT_ADAM: LAUNCH(DDP_OPT_ADAM, true, true); break;
@@ -258,3 +379,47 @@ extern "C" int ddp_peer_allreduce_update(void* peer, float* bucket, int64_t n, i
   DDP_CUDA(cudaGetLastError());
   return 0;
 }
+
+// ---- the exchange fed directly by the backward's partial gradient rows (common.cuh: PeerExchange) ------------------
+namespace ddp {
+int launch_peer_early(const PeerExchange& px, const float* partials, int parts_c2, int parts_head, cudaStream_t stream) {
+  PeerCtx* c = static_cast<PeerCtx*>(px.peer);
+  DDP_REQUIRE(c && partials, "null peer context or partials");
+  DDP_REQUIRE(c->max_elems >= P_ARENA, "peer context too small for the Net arena");
+  for (int p = 0; p < c->world; ++p) DDP_REQUIRE(c->peer_base[p] != nullptr, "ddp_peer_connect has not been called");
+  peer_early_kernel<<<PEER_EARLY_CTAS, PEER_EARLY_WARPS * 32, 0, stream>>>(make_dev(c), partials, parts_c2, parts_head);
+  DDP_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int launch_peer_final(const PeerExchange& px, const float* partials, int parts_c1, bool have_early, int parts_c2, int parts_head,
+                      float* grad_bucket, cudaStream_t stream) {
+  PeerCtx* c = static_cast<PeerCtx*>(px.peer);
+  DDP_REQUIRE(c && partials && px.params && px.hyper, "null peer context, partials, params or hyper");
+  DDP_REQUIRE(c->max_elems >= P_ARENA, "peer context too small for the Net arena");
+  for (int p = 0; p < c->world; ++p) DDP_REQUIRE(c->peer_base[p] != nullptr, "ddp_peer_connect has not been called");
+  const ddp_hyper_t* h = px.hyper;
+  const int opt = px.opt;
+  const bool need1 = (opt == DDP_OPT_SGD) ? (h->momentum != 0.0) : true;
+  const bool need2 = (opt != DDP_OPT_SGD);
+  DDP_REQUIRE(!need1 || (px.state1 && aligned16(px.state1)), "state1 required for this optimizer");
+  DDP_REQUIRE(!need2 || (px.state2 && aligned16(px.state2)), "state2 required for this optimizer");
+  const UpdateConsts k = make_update_consts(h, 1.0f / float(c->world));
+  float* wb = h->write_back_grad ? grad_bucket : nullptr;
+  const PeerDev d = make_dev(c);
+  const PartialSrc src{have_early ? 2 : 1, partials, parts_c1, parts_c2, parts_head};
+  const int64_t n = P_ARENA;
+#define LAUNCH(OPT, H1, H2) peer_allreduce_kernel<OPT, H1, H2, true><<<PEER_CTAS, PEER_THREADS, 0, stream>>>( \
+      d, nullptr, wb, n, px.params, px.state1, px.state2, k, px.step, px.step_dev, src)
+  switch (opt) {
+    case DDP_OPT_SGD: if (need1) LAUNCH(DDP_OPT_SGD, true, false); else LAUNCH(DDP_OPT_SGD, false, false); break;
+    case DDP_OPT_ADAM: LAUNCH(DDP_OPT_ADAM, true, true); break;
+    case DDP_OPT_ADAMW: LAUNCH(DDP_OPT_ADAMW, true, true); break;
+    case DDP_OPT_ADADELTA: LAUNCH(DDP_OPT_ADADELTA, true, true); break;
+    default: set_error("launch_peer_final: unknown optimizer kind %d", opt); return DDP_EINVAL;
+  }
+#undef LAUNCH
+  DDP_CUDA(cudaGetLastError());
+  return 0;
+}
+}  // namespace ddp

@@ -14,9 +14,12 @@ from . import _native
 
 
 class SyntheticMNIST(torch.utils.data.Dataset):
-    def __init__(self, length=60000, seed=1234, device=None):
+    def __init__(self, length=60000, seed=1234, device=None, first_index=0):
+        """``first_index``: sample i of this dataset is sample ``first_index + i`` of the virtual stream of ``seed`` --
+        a held-out test split is the same seed (same class strokes) with a first_index past the training set."""
         self.length = length
         self.seed = seed
+        self.first_index = int(first_index)
         self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
 
     def __len__(self):
@@ -28,7 +31,9 @@ class SyntheticMNIST(torch.utils.data.Dataset):
         b = indices.numel() if indices is not None else count
         x = torch.empty(b, 1, 28, 28, dtype=torch.float32, device=self.device)
         y = torch.empty(b, dtype=torch.int64, device=self.device)
-        nat.synth_batch(self.seed, indices, base_index, b, x, y)
+        if indices is not None and self.first_index:
+            indices = indices + self.first_index
+        nat.synth_batch(self.seed, indices, base_index + self.first_index, b, x, y)
         return x, y
 
     def batch_u8(self, indices: torch.Tensor = None, base_index: int = 0, count: int = None):
@@ -37,7 +42,9 @@ class SyntheticMNIST(torch.utils.data.Dataset):
         b = indices.numel() if indices is not None else count
         px = torch.empty(b, 784, dtype=torch.uint8, device=self.device)
         y = torch.empty(b, dtype=torch.int64, device=self.device)
-        nat.synth_batch_u8(self.seed, indices, base_index, b, px, y)
+        if indices is not None and self.first_index:
+            indices = indices + self.first_index
+        nat.synth_batch_u8(self.seed, indices, base_index + self.first_index, b, px, y)
         return px, y
 
     @staticmethod

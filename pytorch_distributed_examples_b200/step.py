@@ -70,6 +70,7 @@ class TrainStep:
         # ~3 us faster (measured), so large batches keep them.  DDP_SPLIT_HEAD=1 / DDP_FUSED_HEAD=1 force either.
         self.fused_head = (self.batch <= 2048 or os.environ.get("DDP_FUSED_HEAD", "0") == "1") \
             and os.environ.get("DDP_SPLIT_HEAD", "0") != "1"
+        self.whole_step = os.environ.get("DDP_SPLIT_EXCHANGE", "0") != "1"   # A/B: backward, then a separate peer allreduce + update
         self.graphs = None
         self._fingerprint = None
         self.kernel_launches_per_step = KERNELS_PER_STEP
@@ -87,6 +88,20 @@ class TrainStep:
         nat = _native.get()
         m, g = self.model, self.group
         x, y = self.xs[slot], self.ys[slot]
+        if self.use_peer and self.whole_step:
+            # forward, loss, backward, NVLink exchange and update in ONE call: the partial gradient sums go straight into
+            # the peer exchange, most of them while conv1's weight gradient is still being computed
+            g.bucket = m._grad_arena
+            g.adopted = True
+            g.graph_mode = True
+            g.ensure_state()
+            g.steps += 1
+            hyper = g.hyper()
+            hyper.bump_step_dev = 1
+            nat.net_train_step_peer(m._arena, x, y, m.dropout_seed, 0, self.ws, self.logp, self.losses[slot], self.scratch,
+                                    m._grad_arena, self.comm.peer, g.kind, g.state1, g.state2, hyper, step=g.steps,
+                                    step_dev=g.step_dev, offset_dev=g.step_dev, fused_head=self.fused_head)
+            return
         if self.fused_head:      # forward + backward in one call, the head as ONE kernel (ddp_net_train_fwdbwd)
             nat.net_train_fwdbwd(m._arena, x, y, None, None, m.dropout_seed, 0, self.ws, self.logp, self.losses[slot],
                                  self.scratch, m._grad_arena, offset_dev=g.step_dev)

@@ -189,7 +189,9 @@ def main():
         return torch.cat([v.detach().reshape(-1).float() for v in m.state_dict().values()]).clone()
 
     bn_base, bn_ours = bn_run(False), bn_run(True)
-    assert torch.equal(bn_base, bn_ours), "BufferBroadcast != DDP broadcast_buffers=True"
+    # cuDNN's convolution backward is not bit-reproducible run to run: compare tightly, not bitwise
+    assert (bn_base - bn_ours).abs().max().item() <= 1e-4 * bn_base.abs().max().item(), "BufferBroadcast != DDP broadcast_buffers=True"
+    same_on_all_ranks(bn_ours[-200:], "BatchNorm buffers / head after BufferBroadcast")
     log("DDP comm hooks + BatchNorm buffer broadcast ok")
 
     # 3b. the DDP script's own model with native kernels: pkg.Model under stock DDP + our hook, the reference loop body

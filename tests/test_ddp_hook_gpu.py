@@ -170,5 +170,8 @@ def test_buffer_broadcast_rehomes_batchnorm_buffers_without_changing_the_model(w
         return {k: v.detach().clone() for k, v in m.state_dict().items()}
 
     base, mine = run(False), run(True)
-    for k in base:
-        assert torch.equal(base[k], mine[k]), k
+    for k in base:            # cuDNN's convolution backward is not bit-reproducible run to run: compare tightly, not bitwise
+        if base[k].is_floating_point():
+            torch.testing.assert_close(mine[k], base[k], rtol=1e-4, atol=1e-6, msg=k)
+        else:
+            assert torch.equal(base[k], mine[k]), k
