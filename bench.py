@@ -29,6 +29,7 @@ KERNEL_MACS = {                      # algorithmic MACs per sample of each kerne
     "conv2_dgrad": 320_000, "conv2_wgrad": 320_000, "conv1_wgrad": 144_000, "reduce_partials": 0,
 }
 METRIC = "mnist_cnn_train_samples_per_sec"
+_JSON_OUT = sys.stdout
 OPT = dict(kind="sgd", lr=0.01, momentum=0.9)
 
 
@@ -126,7 +127,7 @@ def reference_arm(args, world, rank):
         "e2e": {"value": r["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    _JSON_OUT.write(json.dumps(line) + "\n"); _JSON_OUT.flush()
 
 
 def workload_config(B, n):
@@ -246,6 +247,12 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries ONE JSON line and nothing else: libraries that write to file descriptor 1 (NCCL's version banner,
+    # torchrun children) are sent to stderr for the duration of the run; the line itself goes to the saved descriptor
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         reference_arm(args, world, rank)
         return
@@ -518,7 +525,7 @@ def main():
         # the reference's W-rank CPU/gloo loop on this box's host cores, W = N, bounded sample
         line["cpu_baseline"] = cpu_reference(N, B, steps=4, warmup=1, budget_s=12.0)
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        _JSON_OUT.write(json.dumps(line) + "\n"); _JSON_OUT.flush()
     if N > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -695,7 +695,12 @@ int launch_bwd_after_head(const float* params, const float* x, int training, int
   bool fork = B <= fork_max_b && !prof_enabled();
   // With a peer exchange attached, large batches push the fc / conv2 gradients to the peers WHILE conv1_wgrad runs
   // (side stream, early kernel), so only conv1's 260 gradients and the flag round trip remain exposed afterwards.
-  const bool early = px != nullptr && !fork && !prof_enabled();
+  // (A/B switch DDP_EARLY_PUSH=1; measured at 2 GPUs, B = 4096: 277 us/step with the early push against 258 us without --
+  //  the side-stream kernel and the smaller conv1_wgrad grid cost more than the hidden exchange saves -- so the default
+  //  is the single final kernel, which reduces the partial rows itself instead of a separate reduce_partials launch.)
+  static int early_env = -1;
+  if (early_env < 0) { const char* e = getenv("DDP_EARLY_PUSH"); early_env = (e && e[0] == '1') ? 1 : 0; }
+  const bool early = px != nullptr && !fork && !prof_enabled() && early_env == 1;
   cudaStream_t wstream = stream;
   cudaEvent_t join_ev = nullptr;
   if (fork) {
@@ -750,8 +755,8 @@ int launch_bwd_after_head(const float* params, const float* x, int training, int
   }
   {
     const int nst1 = (B + W1_NS - 1) / W1_NS;
-    // with the early push in flight leave room for its CTAs: 16 SMs keep one conv1_wgrad CTA instead of two
-    const int cap1 = early_on ? sms * 2 - 16 : sms * 2;
+    // with the early push in flight leave room for its 32 small CTAs: 32 SMs keep one conv1_wgrad CTA instead of two
+    const int cap1 = early_on ? sms * 2 - 32 : sms * 2;
     parts_c1 = nst1 < cap1 ? nst1 : cap1;
     if (parts_c1 > MAX_PARTS) parts_c1 = MAX_PARTS;
     DDP_CUDA(launch_pdl(conv1_wgrad_kernel, dim3(parts_c1), dim3(W1_THREADS), W1_SMEM, stream, !early_on, sc.dp1, ws.idx1, x, sc.partials, B));

@@ -113,28 +113,40 @@ peer_allreduce_kernel(PeerDev pd, const float* __restrict__ bucket, float* __res
         if (p < W) reinterpret_cast<float4*>(pd.slots[p] + slot_off)[i] = v;
     }
   } else if (src.mode == 1) {
-    // every column: one thread walks the column's partial rows in order (few rows at the small batches that take this path)
-    for (int64_t i = gtid; i < nvec; i += gthreads) {
-      const int e = int(i) * 4;
-      const int parts = e < OFF_C2W ? src.parts_c1 : (e < OFF_F1W ? src.parts_c2 : src.parts_head);
-      const float* p0 = src.partials + e;
+    // every column of the arena: 8 lanes share a column (lane j sums the partial rows j, j+8, ..., four loads in flight),
+    // then a fixed-order shuffle tree over the 8; a warp covers 4 columns at a time
+    const int lane = tid & 31, sub = lane & 7;
+    const int64_t gwarp = gtid >> 5, nwarps = gthreads >> 5;
+    for (int64_t c0 = gwarp * 4; c0 < nvec; c0 += nwarps * 4) {
+      const int64_t i = c0 + (lane >> 3);
       float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-      int r = 0;
-      for (; r + 4 <= parts; r += 4) {
-        float4 v[4];
+      const bool live = i < nvec;
+      const int e = live ? int(i) * 4 : 0;
+      if (live) {
+        const int parts = e < OFF_C2W ? src.parts_c1 : (e < OFF_F1W ? src.parts_c2 : src.parts_head);
+        const float* p0 = src.partials + e;
+        for (int r0 = sub; r0 < parts; r0 += 32) {
+          float4 v[4];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) v[q] = __ldcg(reinterpret_cast<const float4*>(p0 + size_t(r + q) * P_ARENA));
+          for (int q = 0; q < 4; ++q) {
+            const int r = r0 + 8 * q;
+            v[q] = r < parts ? __ldcg(reinterpret_cast<const float4*>(p0 + size_t(r) * P_ARENA)) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
 #pragma unroll
-        for (int q = 0; q < 4; ++q) { a.x += v[q].x; a.y += v[q].y; a.z += v[q].z; a.w += v[q].w; }
+          for (int q = 0; q < 4; ++q) { a.x += v[q].x; a.y += v[q].y; a.z += v[q].z; a.w += v[q].w; }
+        }
       }
-      for (; r < parts; ++r) {
-        const float4 v = __ldcg(reinterpret_cast<const float4*>(p0 + size_t(r) * P_ARENA));
-        a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
-      }
-      a = peer_zero_pads(a, e);
 #pragma unroll
-      for (int p = 0; p < PEER_MAX_WORLD; ++p)
-        if (p < W) reinterpret_cast<float4*>(pd.slots[p] + slot_off)[i] = a;
+      for (int o = 4; o > 0; o >>= 1) {
+        a.x += __shfl_xor_sync(0xffffffffu, a.x, o); a.y += __shfl_xor_sync(0xffffffffu, a.y, o);
+        a.z += __shfl_xor_sync(0xffffffffu, a.z, o); a.w += __shfl_xor_sync(0xffffffffu, a.w, o);
+      }
+      if (live && sub == 0) {
+        a = peer_zero_pads(a, e);
+#pragma unroll
+        for (int p = 0; p < PEER_MAX_WORLD; ++p)
+          if (p < W) reinterpret_cast<float4*>(pd.slots[p] + slot_off)[i] = a;
+      }
     }
   } else {
     // conv1's columns only: the whole CTA sums one column's rows (thread t: rows t, t+512), fixed-order shuffle tree,
@@ -216,9 +228,9 @@ peer_allreduce_kernel(PeerDev pd, const float* __restrict__ bucket, float* __res
 // The early half of the exchange (PartialSrc mode 2): reduce the fc / conv2 partial rows (columns PEER_C1_COLS .. end) in
 // fixed order and push the sums into slot[par][R] of every rank.  Runs on a side stream beside conv1_wgrad; publishes
 // nothing -- the flag is raised by the final kernel, which is ordered after this one on every rank.
-constexpr int PEER_EARLY_CTAS = 16;
-constexpr int PEER_EARLY_WARPS = 32;
-__global__ void __launch_bounds__(PEER_EARLY_WARPS * 32, 1)
+constexpr int PEER_EARLY_CTAS = 32;     // small CTAs (256 threads, <= 64 registers): two of them fit beside ONE conv1_wgrad CTA
+constexpr int PEER_EARLY_WARPS = 8;
+__global__ void __launch_bounds__(PEER_EARLY_WARPS * 32, 4)
 peer_early_kernel(PeerDev pd, const float* __restrict__ partials, int parts_c2, int parts_head) {
   __shared__ float4 red[PEER_EARLY_WARPS][33];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -409,7 +421,10 @@ int launch_peer_final(const PeerExchange& px, const float* partials, int parts_c
   const PeerDev d = make_dev(c);
   const PartialSrc src{have_early ? 2 : 1, partials, parts_c1, parts_c2, parts_head};
   const int64_t n = P_ARENA;
-#define LAUNCH(OPT, H1, H2) peer_allreduce_kernel<OPT, H1, H2, true><<<PEER_CTAS, PEER_THREADS, 0, stream>>>( \
+  // fed by partial rows the kernel also does the reduction: 64 co-resident CTAs (they wait on each other only through
+  // the device-local ticket; 64 <= number of SMs) instead of 8
+  const int ctas = have_early ? PEER_CTAS : 64;
+#define LAUNCH(OPT, H1, H2) peer_allreduce_kernel<OPT, H1, H2, true><<<ctas, PEER_THREADS, 0, stream>>>( \
       d, nullptr, wb, n, px.params, px.state1, px.state2, k, px.step, px.step_dev, src)
   switch (opt) {
     case DDP_OPT_SGD: if (need1) LAUNCH(DDP_OPT_SGD, true, false); else LAUNCH(DDP_OPT_SGD, false, false); break;

@@ -70,7 +70,11 @@ class TrainStep:
         # ~3 us faster (measured), so large batches keep them.  DDP_SPLIT_HEAD=1 / DDP_FUSED_HEAD=1 force either.
         self.fused_head = (self.batch <= 2048 or os.environ.get("DDP_FUSED_HEAD", "0") == "1") \
             and os.environ.get("DDP_SPLIT_HEAD", "0") != "1"
-        self.whole_step = os.environ.get("DDP_SPLIT_EXCHANGE", "0") != "1"   # A/B: backward, then a separate peer allreduce + update
+        # A/B switch DDP_WHOLE_STEP=1: ONE call for forward + backward + exchange + update (ddp_net_train_step_peer), the
+        # exchange kernel reducing the backward's partial rows itself.  Measured at 2 GPUs, B = 4096: 256.6 us/step against
+        # 255.7 us for backward -> reduce_partials -> peer allreduce + update, i.e. no gain (what stays exposed is the flag
+        # round trip and the step-to-step skew between the ranks), so the longer-tested sequence stays the default.
+        self.whole_step = os.environ.get("DDP_WHOLE_STEP", "0") == "1"
         self.graphs = None
         self._fingerprint = None
         self.kernel_launches_per_step = KERNELS_PER_STEP
