@@ -756,7 +756,9 @@ int launch_bwd_after_head(const float* params, const float* x, int training, int
   {
     const int nst1 = (B + W1_NS - 1) / W1_NS;
     // with the early push in flight leave room for its 32 small CTAs: 32 SMs keep one conv1_wgrad CTA instead of two
-    const int cap1 = early_on ? sms * 2 - 32 : sms * 2;
+    static int w1_per_sm = -1;
+    if (w1_per_sm < 0) { const char* e = getenv("DDP_W1_CTAS_PER_SM"); w1_per_sm = (e && e[0] == '1') ? 1 : 2; }
+    const int cap1 = early_on ? sms * 2 - 32 : sms * w1_per_sm;
     parts_c1 = nst1 < cap1 ? nst1 : cap1;
     if (parts_c1 > MAX_PARTS) parts_c1 = MAX_PARTS;
     DDP_CUDA(launch_pdl(conv1_wgrad_kernel, dim3(parts_c1), dim3(W1_THREADS), W1_SMEM, stream, !early_on, sc.dp1, ws.idx1, x, sc.partials, B));

@@ -75,9 +75,14 @@ class TrainStep:
         # 255.7 us for backward -> reduce_partials -> peer allreduce + update, i.e. no gain (what stays exposed is the flag
         # round trip and the step-to-step skew between the ranks), so the longer-tested sequence stays the default.
         self.whole_step = os.environ.get("DDP_WHOLE_STEP", "0") == "1"
+        # our kernels per step: conv1_fwd, conv2_fwd, head (1 fused / 2 separate), conv2_dgrad, conv2_wgrad, conv1_wgrad,
+        # reduce_partials, update (fused_update, or the peer allreduce+update kernel) -- ncclAllReduce, when used, is not ours
+        self.kernel_launches_per_step = 8 if self.fused_head else 9
+        if self.use_peer and self.whole_step:
+            self.kernel_launches_per_step -= 1           # the exchange kernel reduces the partial rows itself
         self.graphs = None
         self._fingerprint = None
-        self.kernel_launches_per_step = KERNELS_PER_STEP
+        self.kernel_launches_per_step = KERNELS_PER_STEP   # refined below once the head variant is known
 
     @property
     def x(self):

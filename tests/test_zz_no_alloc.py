@@ -55,3 +55,25 @@ def test_static_scratch_variant_matches_regular_entry_point_twice_in_a_row():
     assert out.tolist() == [1, 3, 5, 7, 9]
     rc = lib.ddp_sampler_indices_static(65537, 1, 0, 1, 0, 0, 0, out.data_ptr(), stream)
     assert rc == -1000 and b"exceeds the built-in scratch" in lib.ddp_last_error()
+
+
+def test_static_scratch_variant_against_the_committed_golden_digest():
+    """An anchor that does not go through the regular entry point: the shard a seeded torch DistributedSampler produced
+    when the fixtures were generated (tests/golden/sampler.pt, oracle/gen_golden.py), by sha256 and by its first and
+    last 16 indices.  n = 60,000, 8 ranks, rank 5, epoch 3 -- the reference's own dataset size (mnist_horovod.py:38-42)."""
+    import hashlib
+    import os
+    fx = torch.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "sampler.pt"), weights_only=False)
+    case = next(c for c in fx["cases"] if c["n"] == 60000 and c["world"] == 8 and c["rank"] == 5)
+    torch.cuda.set_device(0)
+    lib = _native.load_library()
+    assert lib.ddp_set_device(0) == 0
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    out = torch.full((case["len"],), -1, dtype=torch.int64, device="cuda")
+    rc = lib.ddp_sampler_indices_static(case["n"], case["world"], case["rank"], 1, case["seed"], case["epoch"],
+                                        int(case["drop_last"]), out.data_ptr(), stream)
+    assert rc == 0, lib.ddp_last_error()
+    torch.cuda.synchronize()
+    host = out.cpu()
+    assert torch.equal(host[:16], case["head"]) and torch.equal(host[-16:], case["tail"])
+    assert hashlib.sha256(host.numpy().tobytes()).hexdigest() == case["sha256"]
