@@ -20,13 +20,22 @@ template <bool F32>
 __global__ void __launch_bounds__(SY_THREADS)
 synth_kernel(uint64_t seed, const int64_t* __restrict__ indices, int64_t base_index, int64_t batch,
              float* __restrict__ out_x, uint8_t* __restrict__ out_px, int64_t* __restrict__ out_y) {
-  __shared__ uint32_t stroke_s[10 * 49];
+  __shared__ uint4 stroke_s[10 * 49];                  // per (label, block): the 16 stroke offsets (0 or 112) as 16 bytes
   __shared__ float lut_s[256];
   __shared__ uint32_t label_s[SY_S];
   const uint32_t k0 = uint32_t(seed), k1 = uint32_t(seed >> 32);
   const int tid = threadIdx.x;
-  for (int i = tid; i < 10 * 49; i += SY_THREADS)
-    stroke_s[i] = philox4x32_10(uint32_t(i / 49), uint32_t(i % 49), 0x7E3Du, 0x5EEDu, k0, k1).x;
+  for (int i = tid; i < 10 * 49; i += SY_THREADS) {
+    const uint32_t bits = philox4x32_10(uint32_t(i / 49), uint32_t(i % 49), 0x7E3Du, 0x5EEDu, k0, k1).x;
+    uint32_t a[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      a[q] = 0u;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) a[q] |= (((bits >> (4 * q + k)) & 1u) ? 112u : 0u) << (8 * k);
+    }
+    stroke_s[i] = make_uint4(a[0], a[1], a[2], a[3]);
+  }
   if (F32) lut_s[tid] = (float(tid) / 255.0f - 0.1307f) / 0.3081f;      // torchvision's op order, IEEE fp32
   const int64_t ngroups = (batch + SY_S - 1) / SY_S;
   for (int64_t grp = blockIdx.x; grp < ngroups; grp += gridDim.x) {
@@ -40,30 +49,35 @@ synth_kernel(uint64_t seed, const int64_t* __restrict__ indices, int64_t base_in
       if (out_y) out_y[b0 + tid] = int64_t(label);
     }
     __syncthreads();
-    for (int t = tid; t < nvalid * 49; t += SY_THREADS) {
+    const int nwork = nvalid * 49;
+    for (int t0 = 0; t0 < nwork; t0 += SY_THREADS) {         // warp-uniform trip count: the f32 store path shuffles
+      const int t = min(t0 + tid, nwork - 1);                 // tail lanes redo the last block (same bytes, harmless)
       const int sl = t / 49, blk = t % 49;
       const int64_t b = b0 + sl;
       const uint64_t idx = uint64_t(indices ? indices[b] : base_index + b);
       const Philox4 n = philox4x32_10(uint32_t(idx), uint32_t(idx >> 32), uint32_t(blk), 0u, k0, k1);
-      const uint32_t stroke = stroke_s[label_s[sl] * 49 + blk];
-      const uint32_t nz[4] = {n.x, n.y, n.z, n.w};
+      // pixel = (noise byte >> 1) + stroke offset, four pixels per 32-bit word (127 + 112 < 256: no carry between bytes)
+      const uint4 add = stroke_s[label_s[sl] * 49 + blk];
       uint32_t w[4];
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        uint32_t out = 0u;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const uint32_t noise = (nz[q] >> (8 * k)) & 0xffu;
-          const uint32_t px = (noise >> 1) + (((stroke >> (4 * q + k)) & 1u) ? 112u : 0u);
-          out |= px << (8 * k);
-        }
-        w[q] = out;
-      }
+      w[0] = ((n.x >> 1) & 0x7f7f7f7fu) + add.x;
+      w[1] = ((n.y >> 1) & 0x7f7f7f7fu) + add.y;
+      w[2] = ((n.z >> 1) & 0x7f7f7f7fu) + add.z;
+      w[3] = ((n.w >> 1) & 0x7f7f7f7fu) + add.w;
       if (F32) {
-        float4* o = reinterpret_cast<float4*>(out_x + b * IMG_PIX + blk * 16);
+        // 64 output bytes per thread: stored directly, the lanes of one 128-bit store would sit 64 bytes apart (every
+        // 32-byte sector written in two halves by different instructions).  Instead the 4 lanes of a quad take turns:
+        // in turn s they write the four float4 of lane s's block, i.e. 64 contiguous bytes per quad and instruction.
+        const int lane = tid & 31, j = lane & 3, qbase = lane & ~3;
+        float* ob = out_x + b * IMG_PIX + blk * 16;
 #pragma unroll
-        for (int q = 0; q < 4; ++q)
-          o[q] = make_float4(lut_s[w[q] & 0xffu], lut_s[(w[q] >> 8) & 0xffu], lut_s[(w[q] >> 16) & 0xffu], lut_s[w[q] >> 24]);
+        for (int sx = 0; sx < 4; ++sx) {
+          const uint32_t x0 = __shfl_sync(0xffffffffu, w[0], qbase + sx), x1 = __shfl_sync(0xffffffffu, w[1], qbase + sx);
+          const uint32_t x2 = __shfl_sync(0xffffffffu, w[2], qbase + sx), x3 = __shfl_sync(0xffffffffu, w[3], qbase + sx);
+          const unsigned long long p = (unsigned long long)__shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)ob, qbase + sx);
+          const uint32_t wj = j == 0 ? x0 : (j == 1 ? x1 : (j == 2 ? x2 : x3));
+          reinterpret_cast<float4*>(reinterpret_cast<float*>(uintptr_t(p)))[j] =
+              make_float4(lut_s[wj & 0xffu], lut_s[(wj >> 8) & 0xffu], lut_s[(wj >> 16) & 0xffu], lut_s[wj >> 24]);
+        }
       } else {
         *reinterpret_cast<uint4*>(out_px + b * IMG_PIX + blk * 16) = make_uint4(w[0], w[1], w[2], w[3]);
       }
