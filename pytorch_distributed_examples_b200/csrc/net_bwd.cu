@@ -713,10 +713,14 @@ int launch_bwd_after_head(const float* params, const float* x, int training, int
     if (parts_c2 > sms * 3) parts_c2 = sms * 3;      // 3 CTAs/SM: one stages while the others compute
   }
   const bool dense = bwd_dense();
+  static int w2_dense_env = -1, d2_dense_env = -1;
+  if (w2_dense_env < 0) { const char* e = getenv("DDP_W2_DENSE"); w2_dense_env = (e && e[0] == '1') ? 1 : 0; }
+  if (d2_dense_env < 0) { const char* e = getenv("DDP_D2_DENSE"); d2_dense_env = (e && e[0] == '1') ? 1 : 0; }
+  const bool w2_dense = dense || w2_dense_env == 1, d2_dense = dense || d2_dense_env == 1;
   auto launch_wgrad2 = [&]() -> int {
-    if (!dense && wgrad2_tc())
+    if (!w2_dense && wgrad2_tc())
       return launch_conv2_wgrad_tc(sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale, sc.partials, B, &parts_c2, wstream, !fork);
-    if (!dense)
+    if (!w2_dense)
       return launch_conv2_wgrad_sp(sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale, sc.partials, B, &parts_c2, wstream, !fork);
     DDP_CUDA(launch_pdl(conv2_wgrad_kernel, dim3(parts_c2), dim3(W2_THREADS), W2_SMEM, wstream, !fork, sc.da2, ws.a2, ws.idx2, ws.a1,
                         drop_scale, sc.partials, B));
@@ -726,7 +730,7 @@ int launch_bwd_after_head(const float* params, const float* x, int training, int
     if (int rc = launch_wgrad2()) return rc;
     DDP_CUDA(cudaEventRecord(join_ev, wstream));
   }
-  if (!dense) {
+  if (!d2_dense) {
     if (int rc = launch_conv2_dgrad_sp(params, sc.da2, ws.a2, ws.idx2, ws.a1, drop_scale, sc.dp1, B, stream)) return rc;
   } else {
     // warps per sample: 4 while the SMs are mostly empty (latency mode), 1 once one warp per sample fills them
@@ -758,7 +762,11 @@ int launch_bwd_after_head(const float* params, const float* x, int training, int
     // with the early push in flight leave room for its 32 small CTAs: 32 SMs keep one conv1_wgrad CTA instead of two
     static int w1_per_sm = -1;
     if (w1_per_sm < 0) { const char* e = getenv("DDP_W1_CTAS_PER_SM"); w1_per_sm = (e && e[0] == '1') ? 1 : 2; }
-    const int cap1 = early_on ? sms * 2 - 32 : sms * w1_per_sm;
+    int cap1 = early_on ? sms * 2 - 32 : sms * w1_per_sm;
+    // small-batch mode: conv2_wgrad is still running on the side stream when this kernel starts; with two of these CTAs
+    // per SM (64k registers) nothing co-resides and the second wave waits -- one CTA per SM runs beside it
+    // (measured at B = 512 / 768 / 1024: 116.7 / 118.8 / 135.2 -> 108.5 / 108.6 / 129.1 us per step; B = 384 prefers two)
+    if (fork && nst1 > sms + sms / 2) cap1 = sms;
     parts_c1 = nst1 < cap1 ? nst1 : cap1;
     if (parts_c1 > MAX_PARTS) parts_c1 = MAX_PARTS;
     DDP_CUDA(launch_pdl(conv1_wgrad_kernel, dim3(parts_c1), dim3(W1_THREADS), W1_SMEM, stream, !early_on, sc.dp1, ws.idx1, x, sc.partials, B));
