@@ -3,6 +3,7 @@
 //   K_F2  conv2(10->20,5x5)+bias -> Dropout2d -> maxpool2 -> ReLU       a1 -> a2,idx2   (tensor cores: conv2_fwd_tc.cu)
 //   K_F3  fc1+bias -> ReLU -> dropout -> fc2+bias -> log_softmax (-> NLL mean, argmax)
 // K_F1 / K_F3 are fp32 FFMA with register tiling; conv outputs before pooling never leave the SM.
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace ddp {
@@ -325,7 +326,9 @@ int launch_fwd_convs(const float* params, const float* x, const float* mask2d, u
   prof_mark(0, stream);
   {
     int npairs = (B + 1) / 2;
-    int grid = npairs < sms * 2 ? npairs : sms * 2;
+    static int f1_per_sm = -1;
+    if (f1_per_sm < 0) { const char* e = getenv("DDP_F1_CTAS_PER_SM"); f1_per_sm = e ? atoi(e) : 2; if (f1_per_sm < 1 || f1_per_sm > 2) f1_per_sm = 2; }
+    int grid = npairs < sms * f1_per_sm ? npairs : sms * f1_per_sm;
     DDP_CUDA(launch_pdl(conv1_fwd_kernel, dim3(grid), dim3(F1_THREADS), 0, stream, true, params, x, ws.a1, ws.idx1, B));
   }
   prof_mark(1, stream);
