@@ -324,6 +324,103 @@ conv2_dgrad_sp_kernel(const float* __restrict__ params, const float* __restrict_
 }
 
 // ---------------------------------------------------------------------------
+// K_B2d (sparse, channel-stationary).  Same lane mapping, bands and W layout as conv2_dgrad_sp_kernel, other loop order:
+// per band the warp walks the LIVE CHANNELS (ballot over "any of my 4 cells has gradient"), loads the channel's W rows
+// for both vertical phases ONCE (10 LDS.64: the 5 kw taps x {idy = 0, idy = 1}) and then applies the channel's up to four
+// entries of the band from registers -- the entry's (px, phase) only selects one of 16 static FFMA2 groups through
+// warp-uniform branches.  A live channel has ~3.7 live entries per band, so the shared-memory traffic per entry drops
+// from 5 LDS.64 to ~2.7 and there is no list building at all.
+// ---------------------------------------------------------------------------
+template <int X0>
+__device__ __forceinline__ void sd_apply(unsigned long long (&acc)[12], unsigned long long g2, const unsigned long long (&w)[5]) {
+#pragma unroll
+  for (int k = 0; k < 5; ++k) fma2(acc[X0 + k], g2, w[k]);
+}
+template <int PX>
+__device__ __forceinline__ void sd_entry(unsigned long long (&acc)[12], float gb, unsigned id, const unsigned long long (&w0)[5],
+                                         const unsigned long long (&w1)[5]) {
+  if (gb == 0.f) return;                               // warp-uniform: gb was broadcast
+  const unsigned long long g2 = pack2(gb, gb);
+  if (id & 2u) {
+    if (id & 1u) sd_apply<2 * PX + 1>(acc, g2, w1); else sd_apply<2 * PX>(acc, g2, w1);
+  } else {
+    if (id & 1u) sd_apply<2 * PX + 1>(acc, g2, w0); else sd_apply<2 * PX>(acc, g2, w0);
+  }
+}
+__global__ void __launch_bounds__(SD_MAXW * 32, 3)
+conv2_dgrad_cs_kernel(const float* __restrict__ params, const float* __restrict__ da2,
+                      const float* __restrict__ a2, const uint8_t* __restrict__ idx2,
+                      const float* __restrict__ a1, float drop_scale, float* __restrict__ dp1, int B) {
+  __shared__ __align__(16) unsigned long long w_s[SD_W2];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int nthreads = blockDim.x, wpc = nthreads >> 5;
+  pdl_trigger();
+  for (int i = tid; i < SD_W2; i += nthreads) {
+    float v0 = 0.f, v1 = 0.f;
+    if (i < C2 * SD_CO2) {
+      const int co = i / SD_CO2, r = i % SD_CO2, kw = r / 35, khp = (r % 35) / 5, cp = r % 5;
+      if (khp >= 1 && khp <= 5) {
+        const float* w = params + OFF_C2W + co * 250 + (2 * cp) * 25 + (khp - 1) * 5 + kw;
+        v0 = w[0]; v1 = w[25];
+      }
+    }
+    w_s[i] = pack2(v0, v1);
+  }
+  __syncthreads();
+  pdl_wait();                                          // da2 (head_bwd) is read from here on
+  const int ry = lane / 5;                             // 0..5 (6 for the two idle lanes)
+  const unsigned long long* wl = w_s + lane;
+  const int nwarps = gridDim.x * wpc;
+  const int lco = lane < C2 ? lane : 0;                // lane co < 20 fetches its channel's entries
+  for (int b = blockIdx.x * wpc + warp; b < B; b += nwarps) {
+    const float4* a4 = reinterpret_cast<const float4*>(a2 + size_t(b) * A2_PER + lco * 16);
+    const float4* d4 = reinterpret_cast<const float4*>(da2 + size_t(b) * A2_PER + lco * 16);
+    const unsigned* i4 = reinterpret_cast<const unsigned*>(idx2 + size_t(b) * A2_PER + lco * 16);
+    const float* a1b = a1 + size_t(b) * A1_PER;
+    float* dpb = dp1 + size_t(b) * A1_PER;
+    float4 na = a4[0], nd = d4[0];
+    unsigned ni = i4[0];
+    unsigned long long acc[12];
+#pragma unroll
+    for (int x = 0; x < 12; ++x) acc[x] = 0ull;
+#pragma unroll 1
+    for (int py = 0; py < 4; ++py) {
+      float g[4];                                      // this band's 4 entries of channel `lane`
+      g[0] = na.x > 0.f ? nd.x * drop_scale : 0.f;
+      g[1] = na.y > 0.f ? nd.y * drop_scale : 0.f;
+      g[2] = na.z > 0.f ? nd.z * drop_scale : 0.f;
+      g[3] = na.w > 0.f ? nd.w * drop_scale : 0.f;
+      if (lane >= C2) { g[0] = 0.f; g[1] = 0.f; g[2] = 0.f; g[3] = 0.f; }
+      const unsigned ids = ni;
+      if (py < 3) { na = a4[py + 1]; nd = d4[py + 1]; ni = i4[py + 1]; }
+      unsigned live = __ballot_sync(0xffffffffu, (g[0] != 0.f) | (g[1] != 0.f) | (g[2] != 0.f) | (g[3] != 0.f));
+      while (live) {
+        const int co = __ffs(live) - 1;
+        live &= live - 1;
+        const unsigned long long* wp = wl + co * SD_CO2;
+        unsigned long long w0[5], w1[5];               // rows kh = ry (idy = 0) and kh = ry - 1 (idy = 1); zero rows outside
+#pragma unroll
+        for (int k = 0; k < 5; ++k) { w0[k] = wp[k * 35 + 5]; w1[k] = wp[k * 35]; }
+        const unsigned idb = __shfl_sync(0xffffffffu, ids, co);
+        const float g0 = __shfl_sync(0xffffffffu, g[0], co), g1 = __shfl_sync(0xffffffffu, g[1], co);
+        const float g2 = __shfl_sync(0xffffffffu, g[2], co), g3 = __shfl_sync(0xffffffffu, g[3], co);
+        sd_entry<0>(acc, g0, idb & 3u, w0, w1);
+        sd_entry<1>(acc, g1, (idb >> 8) & 3u, w0, w1);
+        sd_entry<2>(acc, g2, (idb >> 16) & 3u, w0, w1);
+        sd_entry<3>(acc, g3, (idb >> 24) & 3u, w0, w1);
+      }
+      // rows 2py, 2py+1 are complete (after the last band: all six rows)
+      sd_emit(acc, lane, 2 * py + ry, lane < (py < 3 ? 10 : 30), a1b, dpb);
+#pragma unroll
+      for (int x = 0; x < 12; ++x) {
+        const unsigned long long v = __shfl_down_sync(0xffffffffu, acc[x], 10);
+        acc[x] = lane < 20 ? v : 0ull;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
 int launch_conv2_wgrad_sp(const float* da2, const float* a2, const uint8_t* idx2, const float* a1, float drop_scale,
                           float* partials, int B, int* parts_out, cudaStream_t stream, bool pdl) {
   static bool done[64] = {false};
@@ -362,8 +459,14 @@ int launch_conv2_dgrad_sp(const float* params, const float* da2, const float* a2
   const int nblk = (B + wpc - 1) / wpc;
   int grid = sms * 3;
   if (grid > nblk) grid = nblk;
-  DDP_CUDA(launch_pdl(conv2_dgrad_sp_kernel, dim3(grid), dim3(wpc * 32), 0, stream, true, params, da2, a2, idx2, a1,
-                      drop_scale, dp1, B));
+  static int lists = -1;                               // A/B switch: DDP_D2_LISTS=1 = the entry-list kernel
+  if (lists < 0) { const char* e = getenv("DDP_D2_LISTS"); lists = (e && e[0] == '1') ? 1 : 0; }
+  if (lists)
+    DDP_CUDA(launch_pdl(conv2_dgrad_sp_kernel, dim3(grid), dim3(wpc * 32), 0, stream, true, params, da2, a2, idx2, a1,
+                        drop_scale, dp1, B));
+  else
+    DDP_CUDA(launch_pdl(conv2_dgrad_cs_kernel, dim3(grid), dim3(wpc * 32), 0, stream, true, params, da2, a2, idx2, a1,
+                        drop_scale, dp1, B));
   return 0;
 }
 
