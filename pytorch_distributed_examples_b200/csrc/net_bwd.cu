@@ -58,11 +58,11 @@ head_bwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
     w2_s[i] = j < F1 ? params[OFF_F2W + c * F1 + j] : 0.f;
   }
   // persistent accumulators
-  float accW1[5][10];                      // fc1.weight rows jg*5.., cols ig*10..
+  unsigned long long accW1[5][5];          // fc1.weight rows jg*5.., cols ig*10.. as packed pairs (fma.rn.f32x2)
 #pragma unroll
   for (int a = 0; a < 5; ++a)
 #pragma unroll
-    for (int c = 0; c < 10; ++c) accW1[a][c] = 0.f;
+    for (int c = 0; c < 5; ++c) accW1[a][c] = 0ull;
   float accW2[2] = {0.f, 0.f};             // fc2.weight element tid, tid+320
   float accB = 0.f;                        // tid<50: fc1.bias[tid]; 64<=tid<74: fc2.bias[tid-64]
   const int jgW = tid >> 5, igW = tid & 31;  // fc1 wgrad mapping
@@ -142,46 +142,44 @@ head_bwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
       const float* dr = dp_s + (jgW * 5) * HB_DPS;
 #pragma unroll 2
       for (int s = 0; s < HT; ++s) {
-        float av[10];
+        unsigned long long av[5];
 #pragma unroll
-        for (int q = 0; q < 5; ++q) {
-          float2 v = *reinterpret_cast<const float2*>(ar + s * HB_A2S + 2 * q);
-          av[2 * q] = v.x; av[2 * q + 1] = v.y;
-        }
+        for (int q = 0; q < 5; ++q) av[q] = *reinterpret_cast<const unsigned long long*>(ar + s * HB_A2S + 2 * q);
 #pragma unroll
         for (int a = 0; a < 5; ++a) {
           const float d = dr[a * HB_DPS + s];
+          const unsigned long long d2 = pack2(d, d);
 #pragma unroll
-          for (int c = 0; c < 10; ++c) accW1[a][c] = fmaf(d, av[c], accW1[a][c]);
+          for (int c = 0; c < 5; ++c) fma2(accW1[a][c], d2, av[c]);
         }
       }
     }
     // fc1 data gradient: da2[s][i] = sum_j dp[s][j] * W1[j][i]
     {
-      float acc[4][8];
+      unsigned long long acc[4][4];
 #pragma unroll
       for (int a = 0; a < 4; ++a)
 #pragma unroll
-        for (int c = 0; c < 8; ++c) acc[a][c] = 0.f;
+        for (int c = 0; c < 4; ++c) acc[a][c] = 0ull;
 #pragma unroll 2
       for (int j = 0; j < F1; ++j) {
-        float4 d = *reinterpret_cast<const float4*>(dp_s + j * HB_DPS + sgD * 4);
-        float4 wa = *reinterpret_cast<const float4*>(w1_s + j * A2_PER + igD * 4);
-        float4 wb = *reinterpret_cast<const float4*>(w1_s + j * A2_PER + 160 + igD * 4);
-        float dv[4] = {d.x, d.y, d.z, d.w};
-        float wv[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+        const float4 d = *reinterpret_cast<const float4*>(dp_s + j * HB_DPS + sgD * 4);
+        const ulonglong2 wa = *reinterpret_cast<const ulonglong2*>(w1_s + j * A2_PER + igD * 4);
+        const ulonglong2 wb = *reinterpret_cast<const ulonglong2*>(w1_s + j * A2_PER + 160 + igD * 4);
+        const unsigned long long dv[4] = {pack2(d.x, d.x), pack2(d.y, d.y), pack2(d.z, d.z), pack2(d.w, d.w)};
+        const unsigned long long wv[4] = {wa.x, wa.y, wb.x, wb.y};
 #pragma unroll
         for (int a = 0; a < 4; ++a)
 #pragma unroll
-          for (int c = 0; c < 8; ++c) acc[a][c] = fmaf(dv[a], wv[c], acc[a][c]);
+          for (int c = 0; c < 4; ++c) fma2(acc[a][c], dv[a], wv[c]);
       }
 #pragma unroll
       for (int a = 0; a < 4; ++a) {
         const int s = sgD * 4 + a;
         if (s < nvalid) {
           float* o = da2 + size_t(b0 + s) * A2_PER + igD * 4;
-          *reinterpret_cast<float4*>(o) = make_float4(acc[a][0], acc[a][1], acc[a][2], acc[a][3]);
-          *reinterpret_cast<float4*>(o + 160) = make_float4(acc[a][4], acc[a][5], acc[a][6], acc[a][7]);
+          *reinterpret_cast<float4*>(o) = make_float4(lo_f(acc[a][0]), hi_f(acc[a][0]), lo_f(acc[a][1]), hi_f(acc[a][1]));
+          *reinterpret_cast<float4*>(o + 160) = make_float4(lo_f(acc[a][2]), hi_f(acc[a][2]), lo_f(acc[a][3]), hi_f(acc[a][3]));
         }
       }
     }
@@ -191,9 +189,8 @@ head_bwd_kernel(const float* __restrict__ params, const float* __restrict__ a2,
 #pragma unroll
   for (int a = 0; a < 5; ++a)
 #pragma unroll
-    for (int c = 0; c < 10; c += 2)     // OFF_F1W and igW*10 are even: 8-byte aligned pairs
-      *reinterpret_cast<float2*>(part + OFF_F1W + (jgW * 5 + a) * A2_PER + igW * 10 + c) =
-          make_float2(accW1[a][c], accW1[a][c + 1]);
+    for (int c = 0; c < 5; ++c)         // OFF_F1W and igW*10 are even: 8-byte aligned pairs
+      *reinterpret_cast<unsigned long long*>(part + OFF_F1W + (jgW * 5 + a) * A2_PER + igW * 10 + 2 * c) = accW1[a][c];
 #pragma unroll
   for (int q = 0; q < 2; ++q) {
     const int e = tid + q * HB_THREADS;
@@ -758,7 +755,10 @@ int launch_bwd_after_head(const float* params, const float* x, int training, int
     DDP_CUDA(cudaEventRecord(ejoin, estream));
   }
   {
-    const int nst1 = (B + W1_NS - 1) / W1_NS;
+    // default: the packed-pair kernel (one sample per stage); DDP_W1_SCALAR=1 keeps the scalar-FFMA kernel for A/B
+    static int w1_scalar = -1;
+    if (w1_scalar < 0) { const char* e = getenv("DDP_W1_SCALAR"); w1_scalar = (e && e[0] == '1') ? 1 : 0; }
+    const int nst1 = w1_scalar ? (B + W1_NS - 1) / W1_NS : (B + 1) / 2;   // the grid policy counts pairs of samples either way
     // with the early push in flight leave room for its 32 small CTAs: 32 SMs keep one conv1_wgrad CTA instead of two
     static int w1_per_sm = -1;
     if (w1_per_sm < 0) { const char* e = getenv("DDP_W1_CTAS_PER_SM"); w1_per_sm = (e && e[0] == '1') ? 1 : 2; }
@@ -769,7 +769,12 @@ int launch_bwd_after_head(const float* params, const float* x, int training, int
     if (fork && nst1 > sms + sms / 2) cap1 = sms;
     parts_c1 = nst1 < cap1 ? nst1 : cap1;
     if (parts_c1 > MAX_PARTS) parts_c1 = MAX_PARTS;
-    DDP_CUDA(launch_pdl(conv1_wgrad_kernel, dim3(parts_c1), dim3(W1_THREADS), W1_SMEM, stream, !early_on, sc.dp1, ws.idx1, x, sc.partials, B));
+    if (w1_scalar) {
+      DDP_CUDA(launch_pdl(conv1_wgrad_kernel, dim3(parts_c1), dim3(W1_THREADS), W1_SMEM, stream, !early_on, sc.dp1, ws.idx1, x, sc.partials, B));
+    } else {
+      if (B <= cap1) parts_c1 = B;                          // few samples: one per CTA before two per CTA
+      if (int rc = launch_conv1_wgrad_pk(sc.dp1, ws.idx1, x, sc.partials, B, parts_c1, stream, !early_on)) return rc;
+    }
   }
   prof_mark(8, stream);
   if (fork) DDP_CUDA(cudaStreamWaitEvent(stream, join_ev, 0));
