@@ -755,7 +755,7 @@ int launch_bwd_after_head(const float* params, const float* x, int training, int
     DDP_CUDA(cudaEventRecord(ejoin, estream));
   }
   {
-    // default: the packed-pair kernel (one sample per stage); DDP_W1_SCALAR=1 keeps the scalar-FFMA kernel for A/B
+    // default: the column-walker kernel on packed pairs (two samples in flight per CTA); DDP_W1_SCALAR=1 keeps the scalar-FFMA kernel for A/B
     static int w1_scalar = -1;
     if (w1_scalar < 0) { const char* e = getenv("DDP_W1_SCALAR"); w1_scalar = (e && e[0] == '1') ? 1 : 0; }
     const int nst1 = w1_scalar ? (B + W1_NS - 1) / W1_NS : (B + 1) / 2;   // the grid policy counts pairs of samples either way
@@ -772,7 +772,6 @@ int launch_bwd_after_head(const float* params, const float* x, int training, int
     if (w1_scalar) {
       DDP_CUDA(launch_pdl(conv1_wgrad_kernel, dim3(parts_c1), dim3(W1_THREADS), W1_SMEM, stream, !early_on, sc.dp1, ws.idx1, x, sc.partials, B));
     } else {
-      if (B <= cap1) parts_c1 = B;                          // few samples: one per CTA before two per CTA
       if (int rc = launch_conv1_wgrad_pk(sc.dp1, ws.idx1, x, sc.partials, B, parts_c1, stream, !early_on)) return rc;
     }
   }
