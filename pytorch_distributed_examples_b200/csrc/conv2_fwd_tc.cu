@@ -11,9 +11,12 @@
 // i.e. +512 bytes on the start address of the (un-swizzled, K-major) shared-memory descriptor.  With the image row
 // as the SLOWEST row index the 8 valid output rows of the 4 samples are rows 0..255 of D: two full 128-row tiles,
 // no discarded rows (a sample-major order needs three tiles per group, a third of them garbage).
-// 3xTF32 with two MMAs per (kh, k-step): A_hi x [B_hi | B_lo] (N=64: hi*hi in columns 0-31, hi*lo in 32-63) and
-// A_lo x B_hi (N=32, accumulating into columns 0-31); the epilogue adds the two column groups.  The MMAs are bound
-// by the shared-memory fetch of the 4 KB A tile (N is tiny), so reading A_hi once instead of twice is worth 27%.
+// 3xTF32 with two MMAs per (kh, k-step).  B rows are packed [B_hi (20) | B_lo (20) | 8 zero rows]:
+//   A_hi x B[0..47]  (N=48): hi*hi in columns 0-19, hi*lo in columns 20-39
+//   A_lo x B[0..31]  (N=32): + lo*hi into columns 0-19; columns 20-31 also receive lo*lo of channels 0-11 (the fourth,
+//                    2^-22-sized term of the exact product: harmless, deterministic, and it lets N be 48+32 instead of 64+32)
+// and the epilogue adds column c and column 20+c.  tf32 MMAs retire about one accumulator column per clock per 128x8
+// tile here, so the MMA time is proportional to the padded N: 80 columns per (kh, k-step) instead of 96.
 //
 // Warp roles (352 threads, 1 CTA/SM, persistent over groups):
 //   warps 0-3  epilogue: tcgen05.ld accumulators -> bias, dropout, 2x2 max-pool (rows oy, oy+1 live in neighbouring warps:
@@ -47,15 +50,15 @@ constexpr int KH_ROWS = G * 8;              // one conv row down = 32 rows of A'
 constexpr int MT = 2;                       // M-tiles per group: D rows (oy < 8, s, ox) = 256
 constexpr int KSTEPS = 7;                   // 56 / 8
 constexpr int NPAD = 32;                    // output channels padded to the MMA N
-constexpr int STAGES = 3;
+constexpr int STAGES = 4;
 constexpr int A_PLANE = ROWS_PAD * 16;      // bytes of one k-chunk plane (4 k values x all rows)
 constexpr int A_HL = 2 * A_PLANE;           // one k-step of hi (or lo): 2 chunks
 constexpr int A_STAGE = 2 * A_HL;           // hi + lo
-constexpr int B_ROWS = 2 * NPAD;            // [B_hi rows 0-31 | B_lo rows 32-63] of one (kh, kstep)
-constexpr int B_PLANE = B_ROWS * 16;        // one k-chunk plane: 1 KB
-constexpr int B_TILE = 2 * B_PLANE;         // one (kh, kstep): 2 KB
-constexpr int SMEM_A = STAGES * A_STAGE;    // 79,872
-constexpr int SMEM_B = 5 * KSTEPS * B_TILE; // 71,680
+constexpr int B_ROWS = 48;                  // [B_hi rows 0-19 | B_lo rows 20-39 | zero rows 40-47] of one (kh, kstep)
+constexpr int B_PLANE = B_ROWS * 16;        // one k-chunk plane: 768 B
+constexpr int B_TILE = 2 * B_PLANE;         // one (kh, kstep): 1.5 KB
+constexpr int SMEM_A = STAGES * A_STAGE;    // 106,496
+constexpr int SMEM_B = 5 * KSTEPS * B_TILE; // 53,760
 constexpr int RAW_S = A1_PER + 8;             // per-sample stride of the raw tile (floats): == 8 mod 32, so the 32 lanes
                                              // (s, ox) of a producer warp read 32 distinct banks
 constexpr int RAW_BYTES = G * RAW_S * 4;     // one group's a1: 23,168 B
@@ -64,7 +67,8 @@ constexpr int SMEM_MISC = 1024;             // barriers, tmem pointer, bias, noi
 constexpr int SMEM_XCH = 4 * C2 * 32 * 4;   // pooling exchange: [epilogue warp][channel][lane]
 constexpr int SMEM_BYTES = SMEM_A + SMEM_B + SMEM_RAW + SMEM_MISC + SMEM_XCH;
 constexpr int THREADS = 320;                // 4 epilogue + 4 producer + 2 MMA-issuer warps
-constexpr int DCOLS = 2 * NPAD;              // accumulator columns per tile: [hi*hi + lo*hi | hi*lo]
+constexpr int DCOLS = 2 * NPAD;              // accumulator column stride per tile (48 used: [hi*hi + lo*hi (20) | hi*lo (20) | pad])
+constexpr int NHL = B_ROWS;                  // N of the A_hi MMA
 constexpr int TMEM_COLS = 256;              // 2 buffers x 2 tiles x 64 columns
 
 using namespace ::ddp::tc;
@@ -86,7 +90,7 @@ conv2_fwd_tc_kernel(const float* __restrict__ params, const float* __restrict__ 
   uint64_t* rfull_bar = tempty_bar + 2;                              // [2] raw a1 tile landed (tx bytes)
   uint64_t* rempty_bar = rfull_bar + 2;                              // [2] producers done reading it
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(rempty_bar + 2);
-  float* bias_s = reinterpret_cast<float*>(misc + 128);              // [32]
+  float* bias_s = reinterpret_cast<float*>(misc + 192);              // [32]  (16 barriers + the TMEM pointer sit below)
   float* noise_s = bias_s + 32;                                      // [2 buffers][G][20]
   float* xch_s = reinterpret_cast<float*>(misc + SMEM_MISC);         // [4 warps][20][32]
 
@@ -96,23 +100,24 @@ conv2_fwd_tc_kernel(const float* __restrict__ params, const float* __restrict__ 
   TC_T0(t_kernel);
 
   // ---- one-time setup: weights -> B (hi, lo), barriers, TMEM ---------------------------------------
-  for (int i = tid; i < 5 * KSTEPS * NPAD * 2; i += THREADS) {         // one 16-byte chunk (4 k) per item
-    const int chunk = i & 1, n = (i >> 1) % NPAD, kj = (i >> 1) / NPAD, j = kj % KSTEPS, kh = kj / KSTEPS;
-    float hi[4], lo[4];
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const int k = j * 8 + chunk * 4 + e;
-      float w = 0.f;
-      if (k < 50 && n < C2) w = params[OFF_C2W + n * 250 + (k % 10) * 25 + kh * 5 + k / 10];
-      split_tf32(w, hi[e], lo[e]);
-    }
-    const int off = (kh * KSTEPS + j) * B_TILE + chunk * B_PLANE + n * 16;
-    *reinterpret_cast<float4*>(b_mat + off) = make_float4(hi[0], hi[1], hi[2], hi[3]);
-    *reinterpret_cast<float4*>(b_mat + off + NPAD * 16) = make_float4(lo[0], lo[1], lo[2], lo[3]);
-  }
-  if (tid < 32) bias_s[tid] = tid < C2 ? params[OFF_C2B + tid] : 0.f;
-  // zero the whole stage ring once: pad rows / pad k stay finite forever
+  // zero B (pad rows, pad k) and the whole stage ring once: pad rows / pad k stay finite forever
+  for (int i = tid; i < SMEM_B / 16; i += THREADS) reinterpret_cast<float4*>(b_mat)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   for (int i = tid; i < SMEM_A / 16; i += THREADS) reinterpret_cast<float4*>(a_ring)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (tid < 32) bias_s[tid] = tid < C2 ? params[OFF_C2B + tid] : 0.f;
+  __syncthreads();
+  // ONE coalesced pass over the 5,000 weights (this prologue is exposed: conv1_fwd's CTAs fill the register file, so the
+  // CTA cannot start before they drain): W[n][ci][kh][kw] -> k = kw*10 + ci, hi into row n, lo into row 20 + n
+#pragma unroll 4
+  for (int i = tid; i < C2 * 250; i += THREADS) {
+    const float w = params[OFF_C2W + i];
+    const int n = i / 250, r = i % 250, ci = r / 25, kh = (r % 25) / 5, kw = r % 5;
+    const int k = kw * 10 + ci;
+    float hi, lo;
+    split_tf32(w, hi, lo);
+    const int off = (kh * KSTEPS + (k >> 3)) * B_TILE + ((k >> 2) & 1) * B_PLANE + n * 16 + (k & 3) * 4;
+    *reinterpret_cast<float*>(b_mat + off) = hi;
+    *reinterpret_cast<float*>(b_mat + off + C2 * 16) = lo;
+  }
   if (tid == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 128); mbar_init(&empty_bar[s], MT); }
     for (int b = 0; b < 2; ++b) {
@@ -207,7 +212,7 @@ conv2_fwd_tc_kernel(const float* __restrict__ params, const float* __restrict__ 
     if (lane == 0) {
       const int t = warp - 8;
       const uint32_t idesc_base = (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(128 >> 4) << 24);   // D f32, A/B tf32 K-major, M=128
-      const uint32_t idesc64 = idesc_base | (uint32_t(DCOLS >> 3) << 17), idesc32 = idesc_base | (uint32_t(NPAD >> 3) << 17);
+      const uint32_t idesc_hl = idesc_base | (uint32_t(NHL >> 3) << 17), idesc32 = idesc_base | (uint32_t(NPAD >> 3) << 17);
       const uint32_t a_base = smem_u32(a_ring), b_base = smem_u32(b_mat);
       uint32_t it = 0, gi = 0;
       for (int grp = blockIdx.x; grp < ngroups; grp += gridDim.x, ++gi) {
@@ -230,8 +235,8 @@ conv2_fwd_tc_kernel(const float* __restrict__ params, const float* __restrict__ 
             for (int kh = 0; kh < 5; ++kh) {
               const uint64_t rows = uint64_t(t * 128 + kh * KH_ROWS);
               const uint64_t bsel = uint64_t((kh * KSTEPS * B_TILE) >> 4);
-              umma_tf32(d, a_hi0 + rows, b0 + bsel, idesc64, (j | kh) ? 1u : 0u);   // hi*hi | hi*lo
-              umma_tf32(d, a_lo0 + rows, b0 + bsel, idesc32, 1u);                   // + lo*hi into columns 0-31
+              umma_tf32(d, a_hi0 + rows, b0 + bsel, idesc_hl, (j | kh) ? 1u : 0u);  // hi*hi (0-19) | hi*lo (20-39)
+              umma_tf32(d, a_lo0 + rows, b0 + bsel, idesc32, 1u);                   // + lo*hi into columns 0-19 (and lo*lo into 20-31)
             }
           }
           umma_commit(&empty_bar[slot]);            // stage reusable once these MMAs have read it
@@ -274,7 +279,7 @@ conv2_fwd_tc_kernel(const float* __restrict__ params, const float* __restrict__ 
         float* mine = xch_s + warp * (C2 * 32);
 #pragma unroll
         for (int co = 0; co < C2; ++co)
-          mine[co * 32 + lane] = (__uint_as_float(acc[co]) + __uint_as_float(acc_hl[co]) + bias_s[co]) * nzs[co];
+          mine[co * 32 + lane] = (__uint_as_float(acc[co]) + __uint_as_float(co < 12 ? acc[C2 + co] : acc_hl[co - 12]) + bias_s[co]) * nzs[co];
         // the pool partner row lives in the neighbouring warp (warps 0|1 and 2|3 pair up); each warp of a pair pools
         // half of the channels: first-max in window scan order (oy,ox), (oy,ox+1), (oy+1,ox), (oy+1,ox+1)
         asm volatile("bar.sync %0, 64;" :: "r"(2 + (warp >> 1)) : "memory");

@@ -350,21 +350,24 @@ __device__ __forceinline__ void sd_entry(unsigned long long (&acc)[12], float gb
 __global__ void __launch_bounds__(SD_MAXW * 32, 3)
 conv2_dgrad_cs_kernel(const float* __restrict__ params, const float* __restrict__ da2,
                       const float* __restrict__ a2, const uint8_t* __restrict__ idx2,
-                      const float* __restrict__ a1, float drop_scale, float* __restrict__ dp1, int B) {
+                      const float* __restrict__ a1, float drop_scale, float* __restrict__ dp1, int B, int wpc) {
+  // wpc = warps per CTA that take samples; at small batches the CTA carries extra warps that only help with the staging
   __shared__ __align__(16) unsigned long long w_s[SD_W2];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int nthreads = blockDim.x, wpc = nthreads >> 5;
+  const int nthreads = blockDim.x;
   pdl_trigger();
-  for (int i = tid; i < SD_W2; i += nthreads) {
-    float v0 = 0.f, v1 = 0.f;
-    if (i < C2 * SD_CO2) {
-      const int co = i / SD_CO2, r = i % SD_CO2, kw = r / 35, khp = (r % 35) / 5, cp = r % 5;
-      if (khp >= 1 && khp <= 5) {
-        const float* w = params + OFF_C2W + co * 250 + (2 * cp) * 25 + (khp - 1) * 5 + kw;
-        v0 = w[0]; v1 = w[25];
-      }
+  // conv2.weight -> [co][kw][kh + 1][cp][c] with zero rows 0 and 6: zero fill, then ONE coalesced pass over the 5,000
+  // weights (a gather per shared-memory word cost 2 uncoalesced loads per item: ~10 us of prologue with 128 threads)
+  for (int i = tid; i < SD_W2; i += nthreads) w_s[i] = 0ull;
+  __syncthreads();
+  {
+    float* wf = reinterpret_cast<float*>(w_s);
+#pragma unroll 4
+    for (int j = tid; j < C2 * 250; j += nthreads) {
+      const float v = params[OFF_C2W + j];
+      const int co = j / 250, r = j % 250, ci = r / 25, t = r % 25, kh = t / 5, kw = t % 5;
+      wf[(co * SD_CO2 + kw * 35 + (kh + 1) * 5 + (ci >> 1)) * 2 + (ci & 1)] = v;
     }
-    w_s[i] = pack2(v0, v1);
   }
   __syncthreads();
   pdl_wait();                                          // da2 (head_bwd) is read from here on
@@ -372,6 +375,7 @@ conv2_dgrad_cs_kernel(const float* __restrict__ params, const float* __restrict_
   const unsigned long long* wl = w_s + lane;
   const int nwarps = gridDim.x * wpc;
   const int lco = lane < C2 ? lane : 0;                // lane co < 20 fetches its channel's entries
+  if (warp >= wpc) return;
   for (int b = blockIdx.x * wpc + warp; b < B; b += nwarps) {
     const float4* a4 = reinterpret_cast<const float4*>(a2 + size_t(b) * A2_PER + lco * 16);
     const float4* d4 = reinterpret_cast<const float4*>(da2 + size_t(b) * A2_PER + lco * 16);
@@ -454,19 +458,22 @@ int launch_conv2_dgrad_sp(const float* params, const float* da2, const float* a2
   const int sms = sm_count();
   const int per_sm = (B + sms - 1) / sms;
   int wpc = (per_sm + 2) / 3;
-  if (wpc < 4) wpc = 4;
+  static int lists = -1;                               // A/B switch: DDP_D2_LISTS=1 = the entry-list kernel
+  if (lists < 0) { const char* e = getenv("DDP_D2_LISTS"); lists = (e && e[0] == '1') ? 1 : 0; }
+  if (wpc < (lists ? 4 : 1)) wpc = lists ? 4 : 1;
   if (wpc > SD_MAXW) wpc = SD_MAXW;
+  // up to 4 samples per SM: ONE CTA per SM (every CTA stages the 20 KB of weights; measured at B = 512: 128 CTAs x 4
+  // sample warps 90 us/step, 256 CTAs x 2 sample warps 94 us)
+  if (!lists && B <= sms * 4) wpc = per_sm;
   const int nblk = (B + wpc - 1) / wpc;
   int grid = sms * 3;
   if (grid > nblk) grid = nblk;
-  static int lists = -1;                               // A/B switch: DDP_D2_LISTS=1 = the entry-list kernel
-  if (lists < 0) { const char* e = getenv("DDP_D2_LISTS"); lists = (e && e[0] == '1') ? 1 : 0; }
   if (lists)
     DDP_CUDA(launch_pdl(conv2_dgrad_sp_kernel, dim3(grid), dim3(wpc * 32), 0, stream, true, params, da2, a2, idx2, a1,
                         drop_scale, dp1, B));
   else
-    DDP_CUDA(launch_pdl(conv2_dgrad_cs_kernel, dim3(grid), dim3(wpc * 32), 0, stream, true, params, da2, a2, idx2, a1,
-                        drop_scale, dp1, B));
+    DDP_CUDA(launch_pdl(conv2_dgrad_cs_kernel, dim3(grid), dim3((wpc < 8 ? 8 : wpc) * 32), 0, stream, true, params, da2, a2, idx2, a1,
+                        drop_scale, dp1, B, wpc));               // >= 8 warps stage the weights
   return 0;
 }
 

@@ -11,7 +11,8 @@ kernels write the gradients into a flat bucket of the same layout.  The wide lay
 (csrc/mlp_gemm.cu), fp32-accurate.  The kernels want a batch that is a multiple of 4 (the weight-gradient GEMM's K is
 the batch and TMA rows are 16-byte aligned): ``model(x)`` pads a ragged last batch with zero rows, which is exact
 (zero rows add nothing to any gradient); ``loss_and_grads`` — the fused path, cross-entropy and its gradient
-computed by the head kernels — insists on a multiple of 4.  No CPU implementation: CPU tensors raise.
+computed by the head kernels — insists on a multiple of 4.  Every autograd forward owns its activation workspace (a small
+per-batch-size pool), so several forwards may be outstanding before their backwards.  No CPU implementation: CPU tensors raise.
 """
 import torch
 import torch.nn as nn
@@ -36,23 +37,28 @@ class _MLPFunction(torch.autograd.Function):
         batch = x.shape[0]
         padded = -(-batch // 4) * 4
         logits = torch.empty(padded, net._shape.out_features, dtype=torch.float32, device=x.device)
-        ws = net._get_workspace(padded)
+        ws = net._take_workspace(padded)          # this forward's own activations: several forwards may be outstanding
         nat.mlp_forward(net._shape, net._arena, _pad_rows(x, padded), None, ws, out_logits=logits)
-        ctx.net, ctx.batch, ctx.padded = net, batch, padded
-        ctx.ws_version = net._ws_version = net._ws_version + 1
+        ctx.net, ctx.batch, ctx.padded, ctx.ws = net, batch, padded, ws
+        net._bucket_lent = False                  # a new forward: the flat gradient bucket may be handed out again
         return logits[:batch]
 
     @staticmethod
     def backward(ctx, dlogits):
         nat = _native.get()
         net = ctx.net
-        if ctx.ws_version != net._ws_version:
-            raise RuntimeError("Model keeps ONE activation workspace: backward must follow its own forward "
-                               "(two forwards before a backward are not supported)")
-        fresh = all(p.grad is None for p in net._param_list)
+        if ctx.ws is None:
+            raise RuntimeError("Model: backward through the same forward twice (retain_graph) is not supported")
+        # the flat bucket becomes p.grad of the FIRST backward node after a zero_grad(); any further node of the same
+        # backward pass (two forwards feeding one loss) or an accumulation step gets a temporary and autograd adds them
+        fresh = not net._bucket_lent and all(p.grad is None for p in net._param_list)
+        if fresh:
+            net._bucket_lent = True
         bucket = net._grad_arena if fresh else torch.empty_like(net._grad_arena)
         nat.mlp_backward(net._shape, net._arena, _pad_rows(dlogits.contiguous(), ctx.padded), None, 1.0, ctx.padded,
-                         net._workspace, bucket)
+                         ctx.ws, bucket)
+        net._give_workspace(ctx.padded, ctx.ws)   # stream-ordered: the next forward's kernels run after this backward's
+        ctx.ws = None
         grads = [bucket[o:o + n].view(p.shape) for p, (o, n) in zip(net._param_list, net._layout)]
         return (None, None, *grads)
 
@@ -67,7 +73,8 @@ class Model(nn.Module):
         self._shape = _native.MLPShape(784, features, hidden_layers, 10)
         self._arena = self._grad_arena = self._workspace = None
         self._workspace_batch = 0
-        self._ws_version = 0
+        self._ws_pool = {}                 # padded batch -> free activation workspaces (autograd forwards take one each)
+        self._bucket_lent = False
         self._layout = None
 
     @property
@@ -98,6 +105,20 @@ class Model(nn.Module):
         self._arena = arena
         self._grad_arena = torch.zeros_like(arena)
         self._workspace, self._workspace_batch = None, 0
+        self._ws_pool = {}
+
+    def _take_workspace(self, batch: int):
+        """A workspace owned by ONE autograd forward until its backward returns it (a forward whose graph is dropped
+        without a backward simply lets its workspace be garbage-collected)."""
+        free = self._ws_pool.setdefault(batch, [])
+        if free:
+            return free.pop()
+        return torch.empty(_native.get().mlp_workspace_bytes(self._shape, batch), dtype=torch.uint8, device=self._arena.device)
+
+    def _give_workspace(self, batch: int, ws):
+        free = self._ws_pool.setdefault(batch, [])
+        if len(free) < 2:
+            free.append(ws)
 
     def _check_arena(self):
         if self._arena is None:
@@ -138,7 +159,6 @@ class Model(nn.Module):
             logits = torch.empty(padded, 10, dtype=torch.float32, device=x.device)
             _native.get().mlp_forward(self._shape, self._arena, _pad_rows(x, padded), None, self._get_workspace(padded),
                                       out_logits=logits)
-            self._ws_version += 1
             return logits[:batch]
         return _MLPFunction.apply(x, self, *self._param_list)
 
@@ -153,7 +173,6 @@ class Model(nn.Module):
         loss = torch.empty(1, dtype=torch.float32, device=x.device)
         nat.mlp_forward(self._shape, self._arena, x, target, ws, out_loss=loss)
         nat.mlp_backward(self._shape, self._arena, None, target, loss_scale, x.shape[0], ws, self._grad_arena)
-        self._ws_version += 1
         for p, (o, n) in zip(self._param_list, self._layout):
             p.grad = self._grad_arena[o:o + n].view(p.shape)
         return loss

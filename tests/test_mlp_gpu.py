@@ -188,6 +188,29 @@ def test_mlp_ragged_batch_is_padded_exactly(native, B):
         assert torch.equal(model(x.cuda()), logits.detach())
 
 
+def test_mlp_two_outstanding_forwards_each_keep_their_activations(native):
+    """Two forwards before one backward (a second micro-batch, or an evaluation pass inside the training step): every
+    autograd forward owns its activation workspace, so the summed loss back-propagates through both correctly."""
+    import pytorch_distributed_examples_b200 as pkg
+    from oracle import mlp_oracle, synth_oracle
+    torch.manual_seed(3)
+    ref = mlp_oracle.OracleMLP(2, 128)
+    sd = {k: v.detach().clone() for k, v in ref.state_dict().items()}
+    xn, yn = synth_oracle.synth_batch(9, np.arange(96))
+    x, y = torch.from_numpy(xn), torch.from_numpy(yn)
+    xa, xb, ya, yb = x[:64], x[64:], y[:64], y[64:]
+    ref = ref.double()
+    (torch.nn.functional.cross_entropy(ref(xa.double()), ya) + 0.5 * torch.nn.functional.cross_entropy(ref(xb.double()), yb)).backward()
+    model = pkg.Model(2, 128); model.load_state_dict(sd); model = model.cuda()
+    la, lb = model(xa.cuda()), model(xb.cuda())                      # second forward BEFORE the first one's backward
+    with torch.no_grad():
+        model(xb.cuda())                                             # and an inference pass in between
+    (torch.nn.functional.cross_entropy(la, ya.cuda()) + 0.5 * torch.nn.functional.cross_entropy(lb, yb.cuda())).backward()
+    for (k, p), (_, q) in zip(model.named_parameters(), ref.named_parameters()):
+        scale = q.grad.abs().max().item()
+        assert (p.grad.double().cpu() - q.grad).abs().max().item() <= 1e-5 * scale + 4 * scale / 64, k
+
+
 @pytest.mark.parametrize("H,Fe,B", [(1, 100, 36), (2, 36, 64), (0, 260, 132)])
 def test_mlp_odd_shapes_against_oracle(native, H, Fe, B):
     """Feature counts that are multiples of 4 but not of the 32 / 128 tile sizes, and batches that are not multiples of
