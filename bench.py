@@ -523,7 +523,11 @@ def main():
         pass
     if rank == 0 and not args.no_extras:
         # the reference's W-rank CPU/gloo loop on this box's host cores, W = N, bounded sample
-        line["cpu_baseline"] = cpu_reference(N, B, steps=4, warmup=1, budget_s=12.0)
+        try:
+            line["cpu_baseline"] = cpu_reference(N, B, steps=4, warmup=1, budget_s=12.0)
+        except Exception as exc:          # a host-side hiccup of the CPU job must not cost the measured GPU line
+            line["cpu_baseline"] = {"value": None, "unit": "samples/s", "cores": None, "kind": "port",
+                                    "sample": "failed", "error": repr(exc)[:400]}
     if rank == 0:
         _JSON_OUT.write(json.dumps(line) + "\n"); _JSON_OUT.flush()
     if N > 1:

@@ -45,6 +45,19 @@ def host_cores() -> int:
 
 
 def _free_port() -> int:
+    """A rendezvous port that is free NOW and lies below the kernel's ephemeral range (32768+): a port handed out by
+    bind(0) sits inside that range and may be taken by an outgoing connection of the GPU job (NCCL / TCPStore sockets of
+    8 ranks) before the CPU job's rank 0 listens on it -- seen once as EADDRINUSE at N = 8."""
+    import random
+    rng = random.Random(os.getpid() * 7919 + time.time_ns())
+    for _ in range(200):
+        port = rng.randrange(15000, 29000)
+        with socket.socket() as s:
+            try:
+                s.bind(("127.0.0.1", port))
+            except OSError:
+                continue
+            return port
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
         return s.getsockname()[1]
@@ -114,7 +127,20 @@ def _worker(args):
 
 def time_reference_ddp(world: int, batch: int, steps: int, warmup: int, threads_per_rank: int, model: str = "cnn",
                        opt: dict | None = None, timeout: float = 900.0) -> dict:
-    """Launch the W-rank gloo job and return rank 0's result dict (global samples/s, ms/step, threads per rank)."""
+    """Launch the W-rank gloo job and return rank 0's result dict (global samples/s, ms/step, threads per rank).
+    A rendezvous that loses its port to another process is retried on a fresh port."""
+    last = None
+    for _attempt in range(4):
+        try:
+            return _time_reference_ddp_once(world, batch, steps, warmup, threads_per_rank, model, opt, timeout)
+        except RuntimeError as exc:
+            last = exc
+            if "EADDRINUSE" not in str(exc) and "address already in use" not in str(exc).lower():
+                raise
+    raise last
+
+
+def _time_reference_ddp_once(world, batch, steps, warmup, threads_per_rank, model, opt, timeout) -> dict:
     opt = dict(opt or {})
     port = _free_port()
     spec = json.dumps(dict(model=model, batch=int(batch), steps=int(steps), warmup=int(warmup),
