@@ -45,6 +45,7 @@ struct PeerDev {                          // passed by value to the kernel
   unsigned int* flags[PEER_MAX_WORLD];    // each: [2][W][PEER_FLAG_STRIDE]
   unsigned int* epoch;                    // local
   unsigned int* ticket;                   // local
+  unsigned long long* ll[PEER_MAX_WORLD]; // each: [2][W][max_elems] (value, epoch) words of the flag-in-data protocol
 };
 
 __device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
@@ -97,6 +98,9 @@ peer_allreduce_kernel(PeerDev pd, const float* __restrict__ bucket, float* __res
     }
   }
   __syncthreads();
+  // launched as a programmatic dependent of the kernel that produces the bucket / the partial rows: everything above read
+  // only state of the PREVIOUS exchange.  No launch_dependents here: the next kernel of the step reads the parameters.
+  pdl_wait();
   const unsigned int e = epoch_s;
   const int par = int(e & 1u);
   const int W = pd.world, R = pd.rank;
@@ -225,6 +229,112 @@ peer_allreduce_kernel(PeerDev pd, const float* __restrict__ bucket, float* __res
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Flag-in-data variant of the one-shot exchange (default for the bucket-fed call; DDP_PEER_LL=0 keeps the kernel above).
+// Every 8-byte word a rank pushes carries (value, epoch): the receiver polls the DATA words themselves, so there is no
+// separate flag, no system-scope fence and no "last CTA publishes" ticket between the stores and the wait -- the exposed
+// cost is ONE one-way NVLink store latency instead of store -> fence.sys -> ticket -> fence.sys -> flag -> poll
+// (three serialized round trips in the kernel above).  64-bit scalar stores are single-copy atomic, the epoch alternates
+// two slot sets exactly as above, a rank's own contribution never goes through memory, and the sum runs in rank order,
+// so the result is bit-identical on every rank.  Twice the bytes on the wire (175 KB per peer for the CNN): irrelevant.
+// ---------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void st_ll2(unsigned long long* p, unsigned long long a, unsigned long long b) {
+  asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" :: "l"(p), "l"(a), "l"(b) : "memory");
+}
+__device__ __forceinline__ void ld_ll2(const unsigned long long* p, unsigned long long& a, unsigned long long& b) {
+  asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+}
+template <int OPT, bool HAS1, bool HAS2, bool UPDATE>
+__global__ void __launch_bounds__(PEER_THREADS, 1)
+peer_ll_kernel(PeerDev pd, const float* __restrict__ bucket, float* __restrict__ out, int64_t n,
+               float* __restrict__ params, float* __restrict__ state1, float* __restrict__ state2,
+               UpdateConsts kc, int64_t step, const int64_t* __restrict__ step_dev) {
+  __shared__ UpdateConsts ks;
+  __shared__ unsigned int epoch_s;
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    epoch_s = *((volatile unsigned int*)pd.epoch) + 1u;   // bumped by the last CTA to finish, after every CTA has read it
+    if (UPDATE) {
+      UpdateConsts k = kc;
+      finish_consts(k, OPT, step_dev ? (*step_dev + 1) : step);
+      ks = k;
+    }
+  }
+  __syncthreads();
+  pdl_wait();                                             // the bucket is the previous kernel's output
+  const unsigned int e = epoch_s;
+  const unsigned long long etag = (unsigned long long)e << 32;
+  const int par = int(e & 1u);
+  const int W = pd.world, R = pd.rank;
+  const int64_t nvec = (n + 3) >> 2;
+  const int64_t gtid = int64_t(blockIdx.x) * PEER_THREADS + tid, gthreads = int64_t(gridDim.x) * PEER_THREADS;
+  const int64_t my_off = (int64_t(par) * W + R) * pd.max_elems;
+  // 1. push (value, epoch) words into slot[par][R] of every OTHER rank
+  for (int64_t i = gtid; i < nvec; i += gthreads) {
+    const float4 v = reinterpret_cast<const float4*>(bucket)[i];
+    const unsigned long long q0 = etag | __float_as_uint(v.x), q1 = etag | __float_as_uint(v.y);
+    const unsigned long long q2 = etag | __float_as_uint(v.z), q3 = etag | __float_as_uint(v.w);
+#pragma unroll
+    for (int p = 0; p < PEER_MAX_WORLD; ++p)
+      if (p < W && p != R) {
+        unsigned long long* dst = pd.ll[p] + my_off + 4 * i;
+        st_ll2(dst, q0, q1);
+        st_ll2(dst + 2, q2, q3);
+      }
+  }
+  // 2. rank-ordered sum of the W contributions as they arrive + (optional) update
+  const unsigned long long* base = pd.ll[R] + int64_t(par) * W * pd.max_elems;
+  for (int64_t i = gtid; i < nvec; i += gthreads) {
+    const float4 mine = reinterpret_cast<const float4*>(bucket)[i];
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int s = 0; s < PEER_MAX_WORLD; ++s)
+      if (s < W) {
+        float4 v = mine;
+        if (s != R) {
+          const unsigned long long* src = base + int64_t(s) * pd.max_elems + 4 * i;
+          unsigned long long a, b, c, d;
+          unsigned int spins = 0;
+          for (;;) {
+            ld_ll2(src, a, b);
+            ld_ll2(src + 2, c, d);
+            if (unsigned(a >> 32) == e && unsigned(b >> 32) == e && unsigned(c >> 32) == e && unsigned(d >> 32) == e) break;
+            if (++spins > (1u << 26)) __trap();           // a lost peer must abort the launch, not hang the GPU
+          }
+          v = make_float4(__uint_as_float(unsigned(a)), __uint_as_float(unsigned(b)), __uint_as_float(unsigned(c)),
+                          __uint_as_float(unsigned(d)));
+        }
+        if (s == 0) acc = v; else { acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w; }
+      }
+    if (!UPDATE) {
+      reinterpret_cast<float4*>(out)[i] = acc;
+    } else {
+      const UpdateConsts k = ks;
+      float4 pv = ld4(params + i * 4);
+      float4 s1v = HAS1 ? ld4(state1 + i * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+      float4 s2v = HAS2 ? ld4(state2 + i * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+      float g[4] = {acc.x, acc.y, acc.z, acc.w}, p[4] = {pv.x, pv.y, pv.z, pv.w};
+      float s1[4] = {s1v.x, s1v.y, s1v.z, s1v.w}, s2[4] = {s2v.x, s2v.y, s2v.z, s2v.w}, go[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) update_one<OPT>(g[j], p[j], s1[j], s2[j], go[j], k);
+      st4(params + i * 4, make_float4(p[0], p[1], p[2], p[3]));
+      if (HAS1) st4(state1 + i * 4, make_float4(s1[0], s1[1], s1[2], s1[3]));
+      if (HAS2) st4(state2 + i * 4, make_float4(s2[0], s2[1], s2[2], s2[3]));
+      if (out) reinterpret_cast<float4*>(out)[i] = make_float4(go[0], go[1], go[2], go[3]);   // averaged gradient
+    }
+  }
+  // 3. off the critical path: the last CTA to finish bumps the epoch (and the step counter); every CTA read both at its start
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();
+    if (atomicAdd(pd.ticket, 1u) == gridDim.x - 1) {
+      *pd.ticket = 0u;
+      *pd.epoch = e;
+      if (UPDATE && kc.bump_step && step_dev) *const_cast<int64_t*>(step_dev) += 1;
+    }
+  }
+}
+
 // The early half of the exchange (PartialSrc mode 2): reduce the fc / conv2 partial rows (columns PEER_C1_COLS .. end) in
 // fixed order and push the sums into slot[par][R] of every rank.  Runs on a side stream beside conv1_wgrad; publishes
 // nothing -- the flag is raised by the final kernel, which is ordered after this one on every rank.
@@ -272,8 +382,16 @@ peer_early_kernel(PeerDev pd, const float* __restrict__ partials, int parts_c2, 
   __threadfence_system();
 }
 
+static size_t peer_legacy_bytes(int world, int64_t max_elems) {
+  return (size_t(2) * world * max_elems * 4 + size_t(2) * world * PEER_FLAG_STRIDE * 4 + 256 + 255) & ~size_t(255);
+}
 static size_t peer_bytes(int world, int64_t max_elems) {
-  return size_t(2) * world * max_elems * 4 + size_t(2) * world * PEER_FLAG_STRIDE * 4 + 256;
+  return peer_legacy_bytes(world, max_elems) + size_t(2) * world * max_elems * 8;     // + the flag-in-data slots
+}
+static bool peer_ll_enabled() {            // A/B switch: DDP_PEER_LL=0 = separate flags + fences (the first protocol)
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("DDP_PEER_LL"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v == 1;
 }
 static PeerDev make_dev(const PeerCtx* c) {
   PeerDev d{};
@@ -286,6 +404,8 @@ static PeerDev make_dev(const PeerCtx* c) {
   char* tail = c->local_base + slots_bytes + size_t(2) * c->world * PEER_FLAG_STRIDE * 4;
   d.epoch = reinterpret_cast<unsigned int*>(tail);
   d.ticket = reinterpret_cast<unsigned int*>(tail + 128);
+  for (int p = 0; p < c->world; ++p)
+    d.ll[p] = reinterpret_cast<unsigned long long*>(c->peer_base[p] + peer_legacy_bytes(c->world, c->max_elems));
   return d;
 }
 
@@ -357,6 +477,10 @@ extern "C" int ddp_peer_allreduce(void* peer, float* bucket, int64_t n, void* st
   PeerCtx* c = static_cast<PeerCtx*>(peer);
   if (int rc = peer_check(c, bucket, n)) return rc;
   UpdateConsts k{};
+  if (peer_ll_enabled())
+    peer_ll_kernel<0, false, false, false><<<PEER_CTAS, PEER_THREADS, 0, static_cast<cudaStream_t>(stream_)>>>(
+        make_dev(c), bucket, bucket, n, nullptr, nullptr, nullptr, k, 1, nullptr);
+  else
   peer_allreduce_kernel<0, false, false, false><<<PEER_CTAS, PEER_THREADS, 0, static_cast<cudaStream_t>(stream_)>>>(
       make_dev(c), bucket, bucket, n, nullptr, nullptr, nullptr, k, 1, nullptr, PartialSrc{0, nullptr, 0, 0, 0});
   DDP_CUDA(cudaGetLastError());
@@ -378,8 +502,17 @@ extern "C" int ddp_peer_allreduce_update(void* peer, float* bucket, int64_t n, i
   float* wb = h->write_back_grad ? bucket : nullptr;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   const PeerDev d = make_dev(c);
-#define LAUNCH(OPT, H1, H2) peer_allreduce_kernel<OPT, H1, H2, true><<<PEER_CTAS, PEER_THREADS, 0, stream>>>( \
-      d, bucket, wb, n, params, state1, state2, k, step, step_dev, PartialSrc{0, nullptr, 0, 0, 0})
+  const ddp::PartialSrc nosrc{0, nullptr, 0, 0, 0};
+  const float* bucket_c = bucket;
+  const bool ll = peer_ll_enabled();
+  // flag-in-data kernel: one float4 per thread when the bucket allows it (the CNN's 5,462 vectors: 11 CTAs), at most 32 CTAs
+  int ll_ctas = int(((n + 3) / 4 + PEER_THREADS - 1) / PEER_THREADS);
+  if (ll_ctas < 1) ll_ctas = 1;
+  if (ll_ctas > 32) ll_ctas = 32;
+#define LAUNCH(OPT, H1, H2) do { if (ll) DDP_CUDA(ddp::launch_pdl(peer_ll_kernel<OPT, H1, H2, true>, dim3(ll_ctas), dim3(PEER_THREADS), 0, \
+      stream, true, d, bucket_c, wb, n, params, state1, state2, k, step, step_dev)); \
+    else DDP_CUDA(ddp::launch_pdl(peer_allreduce_kernel<OPT, H1, H2, true>, dim3(PEER_CTAS), dim3(PEER_THREADS), 0, \
+      stream, true, d, bucket_c, wb, n, params, state1, state2, k, step, step_dev, nosrc)); } while (0)
   switch (opt) {
     case DDP_OPT_SGD: if (need1) LAUNCH(DDP_OPT_SGD, true, false); else LAUNCH(DDP_OPT_SGD, false, false); break;
     case DDP_OPT_ADAM: LAUNCH(DDP_OPT_ADAM, true, true); break;
@@ -424,8 +557,9 @@ int launch_peer_final(const PeerExchange& px, const float* partials, int parts_c
   // fed by partial rows the kernel also does the reduction: 64 co-resident CTAs (they wait on each other only through
   // the device-local ticket; 64 <= number of SMs) instead of 8
   const int ctas = have_early ? PEER_CTAS : 64;
-#define LAUNCH(OPT, H1, H2) peer_allreduce_kernel<OPT, H1, H2, true><<<ctas, PEER_THREADS, 0, stream>>>( \
-      d, nullptr, wb, n, px.params, px.state1, px.state2, k, px.step, px.step_dev, src)
+  const float* no_bucket = nullptr;
+#define LAUNCH(OPT, H1, H2) DDP_CUDA(launch_pdl(peer_allreduce_kernel<OPT, H1, H2, true>, dim3(ctas), dim3(PEER_THREADS), 0, \
+      stream, true, d, no_bucket, wb, n, px.params, px.state1, px.state2, k, px.step, px.step_dev, src))
   switch (opt) {
     case DDP_OPT_SGD: if (need1) LAUNCH(DDP_OPT_SGD, true, false); else LAUNCH(DDP_OPT_SGD, false, false); break;
     case DDP_OPT_ADAM: LAUNCH(DDP_OPT_ADAM, true, true); break;
