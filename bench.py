@@ -369,6 +369,15 @@ def main():
         "gpu_launches": step.kernel_launches_per_step * K,
         "final_loss": loss_final,
     }
+    if N > 1:
+        # data parallelism's invariant, checked on the final state of the timed job: every replica holds bit-identical
+        # parameters (min and max over ranks of an exact integer checksum of the parameter bits agree)
+        bits = model._arena.view(torch.int32).to(torch.int64)
+        chk = torch.stack([bits.sum(), (bits * torch.arange(1, bits.numel() + 1, device=bits.device)).sum()])
+        lo, hi = chk.clone(), chk.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        line["replicas_bit_identical"] = bool(torch.equal(lo, hi))
+        assert line["replicas_bit_identical"], "replicas diverged: the gradient exchange is broken"
     if N > 1:    # which exchange ran: the one-shot NVLink peer-memory allreduce fused with the update, or ncclAllReduce + fused update
         line["collective"] = "nvlink-peer-memory one-shot allreduce fused with the update" if step.use_peer \
             else "ncclAllReduce + fused update"

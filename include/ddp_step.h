@@ -224,9 +224,11 @@ int ddp_broadcast(void* comm, void* buf, int64_t nbytes, int root, void* stream)
  * For latency-bound buckets on ONE node (world <= 8): replaces ncclAllReduce + ddp_fused_update for the
  * gradient averaging hvd.DistributedOptimizer.step() / DDP perform every step
  * (ref: horovod/mnist_horovod.py:53,64 ; pytorch_elastic/mnist_ddp_elastic.py:58).  Each rank pushes its
- * bucket into every peer's receive slot through cudaIpc-mapped NVLink addresses, publishes an epoch flag,
- * waits for the W flags addressed to it, sums the W slots in rank order (replicas stay bit-identical) and
- * applies the optimizer rule — one kernel.  The receive buffers are communicator resources allocated by
+ * bucket into every peer's receive slot through cudaIpc-mapped NVLink addresses as 64-bit (value, epoch)
+ * words, polls its own slots until every word carries this step's epoch, sums the W contributions in rank
+ * order (replicas stay bit-identical) and applies the optimizer rule — one kernel, no fences, one one-way
+ * NVLink latency exposed.  (Environment DDP_PEER_LL=0 selects the first protocol: plain data + a separate
+ * epoch flag behind system-scope fences.)  The receive buffers are communicator resources allocated by
  * ddp_peer_create (the one place this library calls cudaMalloc); handles travel through the host's
  * rendezvous store: create -> local_handle -> (exchange) -> connect.  n % 4 == 0, n <= max_elems.
  * Every rank must launch the call for the same step; do not overlap two calls on one communicator.      */
