@@ -27,7 +27,10 @@ def main():
     ap.add_argument("--batch_size", type=int, default=128)            # ref :52
     ap.add_argument("--train_samples", type=int, default=60000)
     ap.add_argument("--test_samples", type=int, default=10000)
+    ap.add_argument("--seed", type=int, default=None, help="fix the initial weights and the dropout stream (the reference does not seed)")
     args = ap.parse_args()
+    if args.seed is not None:
+        torch.manual_seed(args.seed)
 
     hvd.init()                                                                                      # ref :35
     model = Net().cuda()                                                                            # ref :38

@@ -11,6 +11,7 @@ on the device (there is no network for the MNIST download); the loop body is the
 import argparse
 
 import _common  # noqa: F401
+import torch
 import torch.nn.functional as F
 import torch.optim as optim
 
@@ -23,7 +24,10 @@ def main():
     ap.add_argument("--batch_size", type=int, default=1024)       # ref :44
     ap.add_argument("--train_samples", type=int, default=60000)   # MNIST's training-set size
     ap.add_argument("--log_every", type=int, default=5)           # ref :65
+    ap.add_argument("--seed", type=int, default=None, help="fix the initial weights and the dropout stream (the reference does not seed)")
     args = ap.parse_args()
+    if args.seed is not None:
+        torch.manual_seed(args.seed)
 
     hvd.init()                                                                                    # ref :28
     train_dataset = SyntheticMNIST(args.train_samples)                                            # ref :38
