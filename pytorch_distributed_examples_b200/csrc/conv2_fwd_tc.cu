@@ -18,13 +18,13 @@
 // and the epilogue adds column c and column 20+c.  tf32 MMAs retire about one accumulator column per clock per 128x8
 // tile here, so the MMA time is proportional to the padded N: 80 columns per (kh, k-step) instead of 96.
 //
-// Warp roles (352 threads, 1 CTA/SM, persistent over groups):
+// Warp roles (320 threads, 1 CTA/SM, persistent over groups):
 //   warps 0-3  epilogue: tcgen05.ld accumulators -> bias, dropout, 2x2 max-pool (rows oy, oy+1 live in neighbouring warps:
 //              exchanged through shared memory), ReLU -> a2, idx2
 //   warps 4-7  producers: the group's raw a1 (23 KB) arrives by ONE cp.async.bulk (TMA engine, mbarrier complete_tx),
 //              prefetched a group ahead; producers read it from smem, split into tf32 hi / lo, 16-byte STS into the ring
 //   warps 8-9  one elected lane each issues the tcgen05.mma / tcgen05.commit of one M-tile; warp 8 owns the TMEM allocation
-// Pipelines: full/empty mbarriers over a 3-stage ring of k-steps (producer <-> MMA) and tmem_full/tmem_empty
+// Pipelines: full/empty mbarriers over a 4-stage ring of k-steps (producer <-> MMA) and tmem_full/tmem_empty
 // over two accumulator buffers (MMA <-> epilogue), so the epilogue of group g overlaps the MMAs of group g+1.
 #include "common.cuh"
 #include "tc_common.cuh"
