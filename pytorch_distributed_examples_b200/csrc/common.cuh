@@ -132,8 +132,8 @@ int launch_conv2_dgrad_sp(const float* params, const float* da2, const float* a2
                           float drop_scale, float* dp1, int B, cudaStream_t stream);
 int launch_conv2_wgrad_tc(const float* da2, const float* a2, const uint8_t* idx2, const float* a1, float drop_scale,
                           float* partials, int B, int* parts_out, cudaStream_t stream, bool pdl);   // conv2_wgrad_tc.cu
-// conv1 weight gradient on packed channel pairs (conv1_wgrad_pk.cu); `parts` CTAs, one partial row each
-int launch_conv1_wgrad_pk(const float* dp1, const uint8_t* idx1, const float* x, float* partials, int B, int parts,
+// conv1 weight gradient on packed channel pairs (conv1_wgrad_col.cu); `parts` CTAs, one partial row each
+int launch_conv1_wgrad_col(const float* dp1, const uint8_t* idx1, const float* x, float* partials, int B, int parts,
                           cudaStream_t stream, bool pdl);
 bool wgrad2_tc();                        // api.cu: true when DDP_W2_TC=1 (A/B switch: the tcgen05 conv2 weight gradient; default is the sparse FFMA2 kernel, which is faster)
 bool bwd_dense();                        // api.cu: true when DDP_BWD_DENSE=1 (A/B switch: the dense conv2 backward kernels)

@@ -140,7 +140,7 @@ conv1_wgrad_col_kernel(const float* __restrict__ dp1, const uint8_t* __restrict_
   }
 }
 
-int launch_conv1_wgrad_pk(const float* dp1, const uint8_t* idx1, const float* x, float* partials, int B, int parts,
+int launch_conv1_wgrad_col(const float* dp1, const uint8_t* idx1, const float* x, float* partials, int B, int parts,
                           cudaStream_t stream, bool pdl) {
   static bool attr_done[64] = {false};
   int dev = 0;

@@ -772,7 +772,7 @@ int launch_bwd_after_head(const float* params, const float* x, int training, int
     if (w1_scalar) {
       DDP_CUDA(launch_pdl(conv1_wgrad_kernel, dim3(parts_c1), dim3(W1_THREADS), W1_SMEM, stream, !early_on, sc.dp1, ws.idx1, x, sc.partials, B));
     } else {
-      if (int rc = launch_conv1_wgrad_pk(sc.dp1, ws.idx1, x, sc.partials, B, parts_c1, stream, !early_on)) return rc;
+      if (int rc = launch_conv1_wgrad_col(sc.dp1, ws.idx1, x, sc.partials, B, parts_c1, stream, !early_on)) return rc;
     }
   }
   prof_mark(8, stream);
