@@ -1,3 +1,8 @@
+"""Per-role clock64 counters of conv2_fwd_tc (setup / producer / MMA issuer / epilogue, waits and work) on one GPU.
+Needs the instrumented build of the library next to the shipped one:
+    nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -DDDP_TC_TIMING -shared -Xcompiler -fPIC \
+         -I<nccl include> pytorch_distributed_examples_b200/csrc/*.cu -o pytorch_distributed_examples_b200/lib/libddp_step_dbg.so -ldl
+The counters cost a global read-modify-write each, so the instrumented kernel's total is not a benchmark number."""
 import ctypes, os, sys, torch
 os.environ["DDP_LIB_PATH"] = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "pytorch_distributed_examples_b200/lib/libddp_step_dbg.so")
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
