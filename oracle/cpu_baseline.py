@@ -177,17 +177,24 @@ def _time_reference_ddp_once(world, batch, steps, warmup, threads_per_rank, mode
 
 def bounded_reference_run(world: int, batch: int, steps: int, warmup: int, threads_per_rank: int, budget_s: float,
                           model: str = "cnn", opt: dict | None = None) -> dict:
-    """`time_reference_ddp` on a BOUNDED sample of the workload: a short probe sizes the per-rank slice of the
-    batch so that `warmup + steps` steps fit in `budget_s` seconds; steps and warm-up are kept as asked.
+    """`time_reference_ddp` on a BOUNDED sample of the workload: short probes size the per-rank slice of the
+    batch so that `warmup + steps` steps fit in `budget_s` seconds (as large as fits: small slices under-state what the
+    CPU reaches on the full batch); steps and warm-up are kept as asked.
     The result carries `sample_batch` (per-rank samples per step actually run) beside the full `batch`."""
+    q = 64 if model == "cnn" else 16
     probe_b = min(batch, 128 if model == "cnn" else 32)
-    probe = time_reference_ddp(world, probe_b, 2, 1, threads_per_rank, model, opt)
-    per_rank_rate = probe["samples_per_s"] / world
     sample_b = batch
-    need = batch * (steps + warmup) / max(per_rank_rate, 1e-9)
-    if need > budget_s:
-        q = 64 if model == "cnn" else 16
-        sample_b = max(q, int(batch * budget_s / need) // q * q)
+    for _ in range(3):                      # the CPU's samples/s grows with the batch: re-probe at the size just chosen
+        probe = time_reference_ddp(world, probe_b, 2, 1, threads_per_rank, model, opt)
+        per_rank_rate = probe["samples_per_s"] / world
+        need = batch * (steps + warmup) / max(per_rank_rate, 1e-9)
+        if need <= budget_s:
+            sample_b = batch
+            break
+        sample_b = min(batch, max(q, int(batch * budget_s / need) // q * q))
+        if sample_b <= probe_b + probe_b // 2:
+            break
+        probe_b = sample_b
     r = time_reference_ddp(world, sample_b, steps, warmup, threads_per_rank, model, opt)
     r["sample_batch"] = sample_b
     r["full_batch"] = batch
