@@ -24,7 +24,8 @@ from . import _native
 from .net import Net
 from .optim import FusedUpdater
 
-KERNELS_PER_STEP = 2 + 1 + 4 + 1   # conv forward x2, fused head, backward x3 + reduce, fused update (also advances the step counter)
+KERNELS_PER_STEP = 2 + 1 + 4 + 1   # small-batch chain: conv forward x2, fused head, backward x3 + reduce, fused update (also advances the
+                                   # step counter); with the head as two kernels (B > 2048) it is 9 -- TrainStep.kernel_launches_per_step
 
 
 class TrainStep:
@@ -82,7 +83,6 @@ class TrainStep:
             self.kernel_launches_per_step -= 1           # the exchange kernel reduces the partial rows itself
         self.graphs = None
         self._fingerprint = None
-        self.kernel_launches_per_step = KERNELS_PER_STEP   # refined below once the head variant is known
 
     @property
     def x(self):
